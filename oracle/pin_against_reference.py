@@ -1,0 +1,302 @@
+"""Pin the CPU oracle against the LIVE reference modules and write golden vectors.
+
+TEST INFRASTRUCTURE ONLY - see ``oracle/__init__.py``.
+
+Runs only in the build container (needs ``/root/reference``); the GPU box never
+executes this file.  It imports the reference package through a symlink
+(``/tmp/refpkg/nano_qwen3tts_vllm`` -> ``/root/reference/nano-qwen3tts-vllm``),
+with ``TORCHDYNAMO_DISABLE=1`` (inductor's CPU build is broken in this image) and
+a world-size-1 gloo group (``layers/linear.py:23-24`` calls ``dist.get_rank()``),
+feeds seeded inputs to the reference's own modules, asserts that ``oracle.ops`` /
+``oracle.model`` reproduce every output BIT-EXACTLY, and stores inputs + reference
+outputs under ``tests/golden/*.pt`` for the CPU and GPU test-suites.
+
+Two reference ops are CUDA-only (Triton ``store_kvcache``, flash-attn): for the
+model-level vectors ``Attention.forward`` is replaced by the oracle restatement of
+``layers/attention.py:73-96`` - those two ops stay "parity unpinned" here and are
+cross-checked against the flash-attn wheel on the GPU box instead.
+
+    TORCHDYNAMO_DISABLE=1 python oracle/pin_against_reference.py
+"""
+from __future__ import annotations
+
+import os
+import sys
+import types
+
+os.environ.setdefault("TORCHDYNAMO_DISABLE", "1")
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+REF_SRC = "/root/reference/nano-qwen3tts-vllm"
+BF16 = torch.bfloat16
+
+
+def import_reference():
+    link_dir = "/tmp/refpkg"
+    os.makedirs(link_dir, exist_ok=True)
+    link = os.path.join(link_dir, "nano_qwen3tts_vllm")
+    if not os.path.islink(link):
+        os.symlink(REF_SRC, link)
+    sys.path.insert(0, link_dir)
+    if not dist.is_initialized():
+        dist.init_process_group("gloo", init_method="tcp://127.0.0.1:29731", world_size=1, rank=0)
+
+
+def eq(a, b, what):
+    assert a.dtype == b.dtype and a.shape == b.shape, (what, a.dtype, b.dtype, a.shape, b.shape)
+    if not torch.equal(a, b):
+        d = (a.float() - b.float()).abs().max().item()
+        raise AssertionError(f"oracle != reference for {what}: max abs diff {d}")
+
+
+def randn(gen, *shape, std=1.0, dtype=BF16):
+    return (torch.randn(*shape, generator=gen) * std).to(dtype)
+
+
+def pin_ops():
+    from oracle import ops
+    from nano_qwen3tts_vllm.layers.layernorm import Qwen3TTSRMSNorm
+    from nano_qwen3tts_vllm.layers.rotary_embedding import get_rope
+    from nano_qwen3tts_vllm.layers.activation import Silu
+    from nano_qwen3tts_vllm.layers.sampler import Sampler
+
+    g = torch.Generator().manual_seed(20261104)
+    out = {}
+
+    # ---- RMSNorm (hidden and per-head shapes) -------------- layernorm.py:18-41
+    for name, shape in (("rms_hidden", (7, 2048)), ("rms_head", (5, 16, 128)), ("rms_1024", (3, 1024))):
+        x = randn(g, *shape, std=1.5)
+        res = randn(g, *shape, std=0.7)
+        m = Qwen3TTSRMSNorm(shape[-1], eps=1e-6).to(BF16)
+        m.weight.data = (1 + 0.05 * torch.randn(shape[-1], generator=g)).to(BF16)
+        y = m(x)
+        y2, r2 = m(x, res)
+        eq(ops.rmsnorm(x, m.weight.data, 1e-6), y, name)
+        oy2, or2 = ops.add_rmsnorm(x, res, m.weight.data, 1e-6)
+        eq(oy2, y2, name + ".add"); eq(or2, r2, name + ".add.res")
+        out[name] = dict(x=x, res=res, w=m.weight.data.clone(), eps=1e-6, y=y, y_add=y2, res_add=r2)
+
+    # ---- RoPE ------------------------------------------ rotary_embedding.py:101-237
+    t = 9
+    q = randn(g, t, 16, 128)
+    k = randn(g, t, 8, 128)
+    pos = torch.tensor([0, 1, 2, 63, 64, 577, 1023, 4095, 4351], dtype=torch.int64)
+    rope1 = get_rope(128, 128, 32768, 1e6, None)
+    rq, rk = rope1(pos, q, k)
+    oq, ok = ops.rope(pos, q, k, rope1.inv_freq)
+    eq(oq, rq, "rope1d.q"); eq(ok, rk, "rope1d.k")
+    out["rope_1d"] = dict(q=q, k=k, positions=pos, theta=1e6, inv_freq=rope1.inv_freq.clone(), q_out=rq, k_out=rk)
+    for inter in (True, False):
+        sc = {"mrope_section": [24, 20, 20], "interleaved": inter}
+        ropem = get_rope(128, 128, 32768, 1e6, sc)
+        modality = ops.mrope_dim_modality(128, sc["mrope_section"], inter)
+        # (a) what the runner really feeds: 1-D positions (talker_mode_runner.py:134)
+        rq, rk = ropem(pos, q, k)
+        oq, ok = ops.rope(pos, q, k, ropem.inv_freq, 1.0, modality)
+        eq(oq, rq, f"mrope{inter}.1d.q"); eq(ok, rk, f"mrope{inter}.1d.k")
+        eq(oq, out["rope_1d"]["q_out"], "mrope collapses to 1-D rope")
+        # (b) three distinct rows [3, 1, T]
+        pos3 = torch.stack([pos, pos // 2 + 3, pos // 3 + 11])
+        rq3, rk3 = ropem(pos3.unsqueeze(1), q, k)
+        oq3, ok3 = ops.rope(pos3, q, k, ropem.inv_freq, 1.0, modality)
+        eq(oq3, rq3, f"mrope{inter}.3d.q"); eq(ok3, rk3, f"mrope{inter}.3d.k")
+        out[f"mrope_{'interleaved' if inter else 'sectioned'}"] = dict(
+            q=q, k=k, positions3=pos3, mrope_section=[24, 20, 20], interleaved=inter,
+            modality=torch.tensor(modality, dtype=torch.int32), inv_freq=ropem.inv_freq.clone(),
+            q_out=rq3, k_out=rk3)
+
+    # ---- SiLU / gated product --------------- activation.py:12-13, share.py:131-135
+    gate = randn(g, 6, 3072, std=2.0)
+    up = randn(g, 6, 3072, std=1.0)
+    s = Silu()(gate)
+    eq(ops.silu(gate), s, "silu")
+    eq(ops.silu_and_mul(gate, up), s * up, "silu_and_mul eager")
+    out["silu"] = dict(gate=gate, up=up, silu=s, silu_mul_eager=s * up,
+                       silu_mul_fused=ops.silu_and_mul(gate, up, fused_rounding=True))
+
+    # ---- Sampler ------------------------------------------------ sampler.py:15-24
+    sampler = Sampler()
+    for name, (b, v, temp, topk) in dict(talker=(6, 3072, 1.0, 50), predictor=(5, 2048, 0.9, 50),
+                                         greedy=(4, 3072, 1.0, 1)).items():
+        logits = randn(g, b, v, std=3.0)
+        logits[0, 100:140] = logits[0, 7]          # ties straddling the k-th value are kept
+        temps = torch.full((b,), temp, dtype=torch.float32)
+        temps[-1] = 0.5
+        torch.manual_seed(4242)
+        ref_idx = sampler(logits, temps, top_k=topk)
+        torch.manual_seed(4242)
+        noise = torch.empty(b, v, dtype=torch.float32).exponential_(1)   # what multinomial draws
+        probs = ops.topk_probs(logits, temps, topk)
+        idx = ops.sample_from_probs(probs, noise)
+        eq(idx, ref_idx, "sampler." + name)
+        out["sampler_" + name] = dict(logits=logits, temperatures=temps, noise=noise, top_k=topk,
+                                      probs=probs, index=ref_idx)
+    return out
+
+
+# ------------------------------------------------------------------ model level
+def small_dims():
+    from oracle.model import StackDims
+    talker = StackDims(hidden_size=256, intermediate_size=512, num_hidden_layers=2, vocab_size=3072,
+                       rope_theta=1e6, mrope_section=[24, 20, 20], mrope_interleaved=True, page_size=256)
+    predictor = StackDims(hidden_size=128, intermediate_size=384, num_hidden_layers=2, vocab_size=2048,
+                          rope_theta=1e6, page_size=256)
+    return talker, predictor
+
+
+def ns_config(d, **extra):
+    rope_scaling = None
+    if d.mrope_section is not None:
+        rope_scaling = {"mrope_section": d.mrope_section, "interleaved": d.mrope_interleaved}
+    return types.SimpleNamespace(
+        vocab_size=d.vocab_size, hidden_size=d.hidden_size, intermediate_size=d.intermediate_size,
+        num_hidden_layers=d.num_hidden_layers, num_attention_heads=d.num_attention_heads,
+        num_key_value_heads=d.num_key_value_heads, head_dim=d.head_dim, rms_norm_eps=d.rms_norm_eps,
+        rope_theta=d.rope_theta, rope_scaling=rope_scaling, attention_bias=False,
+        max_position_embeddings=32768, hidden_act="silu", **extra)
+
+
+def patch_reference_attention(stack_of):
+    """Replace the CUDA-only body of Attention.forward (attention.py:73-96) by the
+    oracle restatement, keeping the reference's own Context plumbing."""
+    from oracle import ops
+    from nano_qwen3tts_vllm.layers import attention as ref_attn
+    from nano_qwen3tts_vllm.utils.context import get_context
+
+    def forward(self, q, k, v):
+        ctx = get_context()
+        if self.k_cache.numel() and self.v_cache.numel():
+            ops.store_kvcache(k, v, self.k_cache, self.v_cache, ctx.slot_mapping)
+        if ctx.is_prefill:
+            return ops.varlen_attn_prefill(q, k, v, ctx.cu_seqlens_q, ctx.cu_seqlens_k, self.scale,
+                                           self.k_cache, self.v_cache, ctx.block_tables)
+        return ops.paged_attn_decode(q, self.k_cache, self.v_cache, ctx.context_lens, ctx.block_tables, self.scale)
+
+    ref_attn.Attention.forward = forward
+
+
+def bind_kv(model, kv_cache):
+    """engine/model_runner/base.py:158-164."""
+    layer_id = 0
+    for module in model.modules():
+        if hasattr(module, "k_cache") and hasattr(module, "v_cache"):
+            module.k_cache = kv_cache[0, layer_id]
+            module.v_cache = kv_cache[1, layer_id]
+            layer_id += 1
+
+
+def pin_models():
+    from oracle import model as om
+    from nano_qwen3tts_vllm.models.qwen3_tts_talker import Qwen3TTSTalkerForCausalLM
+    from nano_qwen3tts_vllm.models.qwen3_tts_predictor import Qwen3TTSCodePredictorForCausalLM
+    from nano_qwen3tts_vllm.utils.context import set_context, reset_context
+
+    td, pd = small_dims()
+    seed = 1234
+    tw, pw = om.synthetic_weights(td, pd, seed=seed, text_vocab=64, text_hidden=96)
+    torch.set_default_dtype(BF16)                       # base.py:55
+    tcfg = ns_config(td, text_vocab_size=64, text_hidden_size=96, num_code_groups=16)
+    pcfg = ns_config(pd, num_code_groups=16, talker_hidden_size=td.hidden_size)
+    ref_t = Qwen3TTSTalkerForCausalLM(tcfg)
+    ref_p = Qwen3TTSCodePredictorForCausalLM(pcfg, tcfg)
+    torch.set_default_dtype(torch.float32)
+    full_sd = {"talker." + k: v for k, v in tw.items()}
+    full_sd.update({"talker.code_predictor." + k: v for k, v in pw.items()})
+    ref_t.load_state_dict(full_sd)
+    ref_p.load_state_dict(full_sd)
+    patch_reference_attention(None)
+
+    nblk = 8
+    o_t = om.Talker(td, tw, nblk)
+    o_p = om.Predictor(pd, pw, nblk, td.hidden_size)
+    bind_kv(ref_t, torch.zeros_like(o_t.stack.kv_cache))
+    bind_kv(ref_p, torch.zeros_like(o_p.stack.kv_cache))
+
+    g = torch.Generator().manual_seed(777)
+    out = dict(seed=seed, num_blocks=nblk)
+    with torch.inference_mode():
+        # ---- talker prefill: two ragged sequences, non-contiguous pages
+        lens = [11, 6]
+        tables = [[5], [2]]
+        prompts = [randn(g, n, td.hidden_size, std=0.05) for n in lens]
+        pos, ctx = om.prefill_layout(lens, tables, 256)
+        set_context(True, ctx.cu_seqlens_q, ctx.cu_seqlens_k, max(lens), max(lens), ctx.slot_mapping, None, None)
+        h = ref_t(torch.cat(prompts, 0), pos)
+        logits = ref_t.compute_logits(h)
+        hid = h[ctx.cu_seqlens_q[1:].long() - 1]
+        reset_context()
+        ol, oh = o_t.prefill(prompts, tables)
+        eq(ol, logits, "talker.prefill.logits"); eq(oh, hid, "talker.prefill.hidden")
+        out["talker_prefill"] = dict(prompts=prompts, tables=tables, logits=logits, hidden=hid)
+        # ---- talker decode: 3 steps (position = len, slot = len-1: talker_mode_runner.py:126-128)
+        steps = []
+        cur = list(lens)
+        for _ in range(3):
+            cur = [n + 1 for n in cur]
+            emb = randn(g, 2, td.hidden_size, std=0.05)
+            pos, ctx = om.decode_layout(cur, tables, 256, talker=True)
+            set_context(False, slot_mapping=ctx.slot_mapping, context_lens=ctx.context_lens, block_tables=ctx.block_tables)
+            h = ref_t(emb, pos)
+            logits = ref_t.compute_logits(h)
+            reset_context()
+            ol, oh = o_t.decode(emb, cur, tables)
+            eq(ol, logits, "talker.decode.logits"); eq(oh, h, "talker.decode.hidden")
+            steps.append(dict(embeds=emb, seq_lens=list(cur), logits=logits, hidden=h))
+        out["talker_decode"] = steps
+        eq(o_t.stack.kv_cache, torch.stack([torch.stack([m.self_attn.attn.k_cache for m in ref_t.model.layers]),
+                                            torch.stack([m.self_attn.attn.v_cache for m in ref_t.model.layers])]),
+           "talker.kv_cache")
+        out["talker_kv_pages"] = o_t.stack.kv_cache[:, :, [5, 2], :16].clone()
+
+        # ---- predictor prefill (2 tokens / seq) and decode with per-seq generation_steps
+        b = 3
+        ptables = [[1], [4], [0]]
+        pin = [randn(g, 2, td.hidden_size, std=0.5) for _ in range(b)]
+        pos, ctx = om.prefill_layout([2] * b, ptables, 256)
+        set_context(True, ctx.cu_seqlens_q, ctx.cu_seqlens_k, 2, 2, ctx.slot_mapping, None, None)
+        emb = ref_p.get_input_embeddings(None, torch.cat(pin, 0).unsqueeze(0), [0] * b)   # predictor.py:89-91
+        h = ref_p(emb.view(-1, emb.size(-1)), pos)
+        logits = ref_p.compute_logits(h, [0] * b)
+        reset_context()
+        ol = o_p.prefill(pin, ptables)
+        eq(ol, logits, "predictor.prefill.logits")
+        out["predictor_prefill"] = dict(inputs=pin, tables=ptables, logits=logits)
+        steps = []
+        plens = [2] * b
+        for gstep in (1, 2, 14):
+            plens = [n + 1 for n in plens]
+            toks = torch.randint(0, pd.vocab_size, (b,), generator=g).tolist()
+            gsteps = [gstep] * b
+            pos, ctx = om.decode_layout(plens, ptables, 256, talker=False)
+            set_context(False, slot_mapping=ctx.slot_mapping, context_lens=ctx.context_lens, block_tables=ctx.block_tables)
+            emb = ref_p.get_input_embeddings(torch.tensor(toks), None, gsteps)
+            h = ref_p(emb, pos)
+            logits = ref_p.compute_logits(h, gsteps)
+            reset_context()
+            ol = o_p.decode(toks, gsteps, plens, ptables)
+            eq(ol, logits, f"predictor.decode.g{gstep}")
+            steps.append(dict(tokens=toks, gen_steps=gsteps, seq_lens=list(plens), logits=logits))
+        out["predictor_decode"] = steps
+    return out
+
+
+def main():
+    import_reference()
+    os.makedirs(GOLDEN, exist_ok=True)
+    ops_vec = pin_ops()
+    torch.save(ops_vec, os.path.join(GOLDEN, "ops.pt"))
+    print("ops pinned:", ", ".join(ops_vec))
+    model_vec = pin_models()
+    torch.save(model_vec, os.path.join(GOLDEN, "models.pt"))
+    print("models pinned:", ", ".join(k for k in model_vec))
+    for f in sorted(os.listdir(GOLDEN)):
+        print(f, os.path.getsize(os.path.join(GOLDEN, f)), "bytes")
+
+
+if __name__ == "__main__":
+    main()
