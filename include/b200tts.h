@@ -1,0 +1,180 @@
+/*
+ * b200tts.h - C ABI of libb200tts.so: the Qwen3-TTS decode hot path as hand-written
+ * sm_100a CUDA kernels (paged KV write, paged GQA attention for decode and varlen
+ * prefill, RMSNorm, q/k-norm + RoPE, SiLU*mul, top-k sampler, frame-loop gathers).
+ *
+ * The reference (tsdocode/nano-qwen3tts-vllm) has no FFI: its "operator API" for this
+ * path is a set of Python callables.  Each entry point below replaces the arithmetic
+ * of one of them; citations are file:line under /root/reference/nano-qwen3tts-vllm/.
+ * The Python modules in nano-qwen3tts-vllm_b200/layers/ keep the reference's names and
+ * signatures and call these through ctypes.
+ *
+ * Contract common to every entry point
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless named host_*;
+ *   - bf16 tensors are `const void*` / `void*` to 2-byte bfloat16, row-major, innermost
+ *     stride 1; `*_stride` arguments are in ELEMENTS;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - no allocation, no synchronisation, no host read of device memory: every call is
+ *     capturable in a CUDA graph; scratch comes from the caller (`*_workspace_bytes`);
+ *   - returns B2TTS_OK or a negative B2TTS_E* code; b2tts_last_error() gives a
+ *     thread-local message.  Nothing throws, nothing calls exit().
+ *   - rows with slot -1 / context length 0 are CUDA-graph padding and are skipped
+ *     (talker_mode_runner.py:97-100, base.py:166-170).
+ */
+#ifndef B200TTS_H
+#define B200TTS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B2TTS_API __attribute__((visibility("default")))
+#else
+#define B2TTS_API
+#endif
+
+#define B2TTS_OK            0
+#define B2TTS_EINVAL       -1   /* bad size / null pointer / inconsistent arguments      */
+#define B2TTS_EALIGN       -2   /* pointer or stride not 16-byte aligned                 */
+#define B2TTS_EUNSUPPORTED -3   /* shape outside what the sm_100a kernels are built for  */
+#define B2TTS_ECUDA        -4   /* CUDA launch error (message carries cudaGetErrorString) */
+#define B2TTS_EWORKSPACE   -5   /* workspace too small                                   */
+
+/* rounding modes of the element-wise kernels (see DESIGN.md "rounding points") */
+#define B2TTS_ROUND_EAGER 0   /* the reference's Python source evaluated op by op in bf16 */
+#define B2TTS_ROUND_FUSED 1   /* what torch-inductor emits for the same source on a GPU:
+                                  fp32 throughout, one rounding at the store            */
+
+B2TTS_API int         b2tts_version(void);                 /* ABI version, bumped on any signature change */
+B2TTS_API const char* b2tts_last_error(void);              /* thread-local, never NULL */
+/* SM count / max dynamic smem of the current device (host query, cached). */
+B2TTS_API int         b2tts_device_info(int* sm_count, int* max_smem_bytes, int* cc_major, int* cc_minor);
+
+/* ---- a1: paged KV write --------------------------------------------------------------
+ * replaces store_kvcache_kernel / store_kvcache          layers/attention.py:10-30, 33-54
+ * key,value [n_tokens, kv_dim] with row strides; caches [num_slots, kv_dim] contiguous
+ * (the reference asserts k_cache.stride(1) == D, :52); slot_mapping[i] == -1 skips row i. */
+B2TTS_API int b2tts_store_kvcache(const void* key, const void* value,
+                        int64_t key_row_stride, int64_t value_row_stride,
+                        void* k_cache, void* v_cache, const int32_t* slot_mapping,
+                        int n_tokens, int kv_dim, void* stream);
+
+/* ---- a2: paged GQA decode attention ---------------------------------------------------
+ * replaces flash_attn_with_kvcache(q.unsqueeze(1), k_cache, v_cache, cache_seqlens,
+ *          block_table, softmax_scale, causal=True)        layers/attention.py:92-95
+ * q [batch, num_heads, head_dim] (row stride q_row_stride), caches
+ * [num_pages, page_size, num_kv_heads, head_dim], block_table [batch, bt_stride] int32
+ * (entries beyond ceil(len/page) are never read, -1 allowed), context_lens [batch] int32
+ * INCLUDING the token written this step.  out [batch, num_heads, head_dim] bf16.
+ * max_ctx bounds the split-KV grid (capacity of the block table in tokens). */
+B2TTS_API size_t b2tts_paged_attn_decode_workspace_bytes(int batch, int num_heads, int head_dim, int max_ctx);
+B2TTS_API int b2tts_paged_attn_decode(const void* q, int64_t q_row_stride,
+                            const void* k_cache, const void* v_cache,
+                            const int32_t* block_table, int bt_stride,
+                            const int32_t* context_lens,
+                            void* out, void* workspace, size_t workspace_bytes,
+                            int batch, int num_heads, int num_kv_heads, int head_dim,
+                            int page_size, float scale, int max_ctx, void* stream);
+
+/* ---- a3: varlen causal prefill attention ----------------------------------------------
+ * replaces flash_attn_varlen_func(q, k, v, cu_seqlens_q/k, max_seqlen_q/k, softmax_scale,
+ *          causal=True, block_table)                       layers/attention.py:78-91
+ * q [total_q, num_heads, head_dim], k,v [total_k, num_kv_heads, head_dim] packed, row
+ * strides in elements; cu_seqlens_* [num_seqs+1] int32.  Causal mask is bottom-right
+ * aligned (query i of a sequence sees keys 0 .. len_k-len_q+i).  When block_table is
+ * non-NULL (prefix-cache hit, attention.py:79-80) k,v are the paged caches
+ * [num_pages, page_size, kv_heads, head_dim] and are read through block_table. */
+B2TTS_API int b2tts_varlen_attn_prefill(const void* q, int64_t q_row_stride,
+                              const void* k, int64_t k_row_stride,
+                              const void* v, int64_t v_row_stride,
+                              const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                              void* out, int num_seqs, int total_q,
+                              int max_seqlen_q, int max_seqlen_k,
+                              int num_heads, int num_kv_heads, int head_dim, float scale,
+                              const int32_t* block_table, int bt_stride, int page_size,
+                              void* stream);
+
+/* ---- a4: RMSNorm ----------------------------------------------------------------------
+ * replaces Qwen3TTSRMSNorm.rms_forward / add_rms_forward    layers/layernorm.py:18-27, 30-41
+ * x [rows, cols] (row stride x_row_stride), w [cols]; y [rows, cols] contiguous.
+ * add variant: sum = f32(x)+f32(res); res_out = bf16(sum); norm uses the fp32 sum
+ * (layernorm.py:35-38) or, with round_sum_first != 0, the bf16-rounded sum - which is
+ * what the decoder layer's `residual + hidden` followed by rms_forward computes
+ * (models/qwen3_tts_share.py:171-173).  y/res_out may alias x/res. */
+B2TTS_API int b2tts_rmsnorm(const void* x, int64_t x_row_stride, const void* w, void* y,
+                  int rows, int cols, float eps, int rounding, void* stream);
+B2TTS_API int b2tts_add_rmsnorm(const void* x, const void* res, const void* w, void* y, void* res_out,
+                      int rows, int cols, float eps, int rounding, int round_sum_first,
+                      void* stream);
+
+/* ---- a4+a5+a1 fused: per-head q/k RMSNorm + RoPE (+ paged KV write) ---------------------
+ * replaces q_norm, k_norm, rotary_emb and store_kvcache as called from
+ * Qwen3TTSAttention.forward                       models/qwen3_tts_share.py:96-106
+ *   RotaryEmbedding.forward / TalkerRotaryEmbedding.forward / apply_*_rotary_pos_emb
+ *                                                 layers/rotary_embedding.py:11-212
+ * q [n, heads, 128], k,v [n, kv_heads, 128] with row strides (they may be slices of one
+ * fused QKV GEMM output).  q_out [n, heads*128] and k_out [n, kv_heads*128] contiguous
+ * (may alias q / k when the strides match).  q_weight/k_weight NULL skips the norm
+ * (plain RoPE, the rotary_emb.forward surface).  positions int64 [3 or 1][n]
+ * (pos_row_stride = 0 for 1-D); inv_freq fp32 [head_dim/2]; modality int32 [head_dim/2]
+ * selects the position row per frequency (NULL = row 0).  cos/sin are computed in fp32,
+ * scaled by attention_scaling, rounded to bf16, and the rotation is three bf16-rounded
+ * ops exactly as the reference's eager expression (rotary_embedding.py:33-34).
+ * slot_mapping NULL skips the cache write; otherwise K (normed+rotated) and V (raw) rows
+ * go to k_cache/v_cache[slot] and slot -1 is skipped. */
+B2TTS_API int b2tts_qknorm_rope_kvwrite(const void* q, int64_t q_row_stride,
+                              const void* k, int64_t k_row_stride,
+                              const void* v, int64_t v_row_stride,
+                              void* q_out, void* k_out,
+                              const void* q_weight, const void* k_weight, float eps,
+                              const int64_t* positions, int64_t pos_row_stride,
+                              const float* inv_freq, const int32_t* modality,
+                              float attention_scaling,
+                              const int32_t* slot_mapping, void* k_cache, void* v_cache,
+                              int n_tokens, int num_heads, int num_kv_heads, int head_dim,
+                              int rounding, void* stream);
+
+/* ---- a6: SiLU and the gated product ------------------------------------------------------
+ * replaces Silu.forward (layers/activation.py:12-13) and `act_fn(gate) * up`
+ * (models/qwen3_tts_share.py:131-135).  gate, up [rows, inter] with a common row stride
+ * (two halves of a fused gate_up GEMM output); up == NULL computes silu(gate) only. */
+B2TTS_API int b2tts_silu_and_mul(const void* gate, const void* up, int64_t in_row_stride,
+                       void* out, int rows, int inter, int rounding, void* stream);
+
+/* ---- a8: sampler ---------------------------------------------------------------------------
+ * replaces Sampler.forward                                  layers/sampler.py:15-24
+ * logits [batch, vocab] bf16 (or fp32 when logits_fp32 != 0), temperatures [batch] fp32,
+ * noise [batch, vocab] fp32 = the Exp(1) draws torch.multinomial makes
+ * (`empty_like(probs).exponential_(1)`), out_index [batch] int64 = argmax(softmax(topk-masked
+ * logits / T) / noise).  Values tied with the k-th largest are kept (`logits < kth`).
+ * top_p is accepted and, like the reference, ignored unless apply_top_p != 0.
+ * probs_out (optional, fp32 [batch, vocab]) receives the softmax for inspection. */
+B2TTS_API int b2tts_topk_sample(const void* logits, int64_t logits_row_stride, int logits_fp32,
+                      const float* temperatures, const float* noise,
+                      int64_t* out_index, float* probs_out,
+                      int batch, int vocab, int top_k, float top_p, int apply_top_p,
+                      void* stream);
+
+/* ---- a9 / frame-loop gathers ------------------------------------------------------------------
+ * b2tts_gather_rows: out[i] = tables[table_index[i]][row_index[i]]  (bf16 rows of `cols`)
+ *   replaces the per-sequence loop codec_embedding[g_i-1](id_i)   models/qwen3_tts_predictor.py:94-98
+ *   tables = base pointer of a stacked [num_tables, rows_per_table, cols] tensor;
+ *   table_index NULL = table 0; an index < 0 writes a zero row.
+ * b2tts_codec_embed_sum: out[i] = bf16(sum_{c<ncb} f32(E_c[codes[i,c]])) + extra[i]
+ *   replaces the 16-codebook gather-sum + trailing-text add        interface.py:1276-1286 */
+B2TTS_API int b2tts_gather_rows(const void* tables, int64_t table_stride, int rows_per_table,
+                      const int64_t* row_index, const int32_t* table_index,
+                      void* out, int64_t out_row_stride, int n, int cols, void* stream);
+B2TTS_API int b2tts_codec_embed_sum(const void* table0, const void* tables_rest, int64_t table_stride,
+                          const int64_t* codes, int64_t codes_row_stride,
+                          const void* extra, int64_t extra_row_stride,
+                          void* out, int n, int num_codebooks, int cols, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200TTS_H */

@@ -1,0 +1,314 @@
+"""ctypes binding of ``lib/libb200tts.so`` (C ABI: ``include/b200tts.h``).
+
+This is the ONLY route from Python to the hot-path arithmetic.  There is no CPU fallback and no
+alternative backend: if the library is missing or a call fails, a ``RuntimeError`` is raised
+(it surfaces through the workers' existing ``except`` -> empty-result path,
+workers/talker_worker.py:139-144 in the reference).
+
+Every wrapper takes torch CUDA tensors, checks dtype/contiguity, and passes raw device pointers
+plus ``torch.cuda.current_stream().cuda_stream`` so the launches are capturable by
+``torch.cuda.graph``.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_int64, c_size_t, c_void_p
+
+import torch
+
+from . import _build
+
+ROUND_EAGER = 0
+ROUND_FUSED = 1
+
+_lib = None
+
+
+class NativeLibraryError(RuntimeError):
+    pass
+
+
+def _load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if not os.path.exists(path):
+        raise NativeLibraryError(
+            f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no fallback path.")
+    lib = ctypes.CDLL(path)
+    P, I, L, F, Z = c_void_p, c_int, c_int64, c_float, c_size_t
+    sig = {
+        "b2tts_version": (I, []),
+        "b2tts_last_error": (c_char_p, []),
+        "b2tts_device_info": (I, [P, P, P, P]),
+        "b2tts_store_kvcache": (I, [P, P, L, L, P, P, P, I, I, P]),
+        "b2tts_paged_attn_decode_workspace_bytes": (Z, [I, I, I, I]),
+        "b2tts_paged_attn_decode": (I, [P, L, P, P, P, I, P, P, P, Z, I, I, I, I, I, F, I, P]),
+        "b2tts_varlen_attn_prefill": (I, [P, L, P, L, P, L, P, P, P, I, I, I, I, I, I, I, F, P, I, I, P]),
+        "b2tts_rmsnorm": (I, [P, L, P, P, I, I, F, I, P]),
+        "b2tts_add_rmsnorm": (I, [P, P, P, P, P, I, I, F, I, I, P]),
+        "b2tts_qknorm_rope_kvwrite": (I, [P, L, P, L, P, L, P, P, P, P, F, P, L, P, P, F, P, P, P, I, I, I, I, I, P]),
+        "b2tts_silu_and_mul": (I, [P, P, L, P, I, I, I, P]),
+        "b2tts_topk_sample": (I, [P, L, I, P, P, P, P, I, I, I, F, I, P]),
+        "b2tts_gather_rows": (I, [P, L, I, P, P, P, L, I, I, P]),
+        "b2tts_codec_embed_sum": (I, [P, P, L, P, L, P, L, P, I, I, I, P]),
+        "b2tts_gemm_bf16_workspace_bytes": (Z, [I, I, I]),
+        "b2tts_gemm_bf16": (I, [P, L, P, P, P, L, I, I, I, P, Z, P]),
+    }
+    for name, (res, args) in sig.items():
+        if not hasattr(lib, name):
+            if name.startswith("b2tts_gemm"):
+                continue
+            raise NativeLibraryError(f"{path} does not export {name}; rebuild the library")
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def lib():
+    return _load()
+
+
+def exported_symbols() -> list[str]:
+    """Names declared in include/b200tts.h (used by the CPU-side ABI test)."""
+    import re
+    with open(os.path.join(_build.INCLUDE, "b200tts.h")) as f:
+        return sorted(set(re.findall(r"\b(b2tts_[a-z0-9_]+)\s*\(", f.read())))
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        msg = _load().b2tts_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"libb200tts {what} failed (code {rc}): {msg}")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _cuda(t: torch.Tensor, dtype, name: str):
+    if not t.is_cuda:
+        raise RuntimeError(f"libb200tts: `{name}` must be a CUDA tensor (there is no CPU path)")
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f"libb200tts: `{name}` must be {dtype}, got {t.dtype}")
+    return t
+
+
+BF16, I32, I64, F32 = torch.bfloat16, torch.int32, torch.int64, torch.float32
+
+
+# ------------------------------------------------------------------------------------------ a1
+def store_kvcache(key, value, k_cache, v_cache, slot_mapping):
+    """key/value [N, kv_heads, hd] (inner dims contiguous, any row stride); caches
+    [blocks, page, kv_heads, hd]; slot_mapping [N] int32."""
+    _cuda(key, BF16, "key"); _cuda(value, BF16, "value"); _cuda(k_cache, BF16, "k_cache")
+    _cuda(v_cache, BF16, "v_cache"); _cuda(slot_mapping, I32, "slot_mapping")
+    n = key.shape[0]
+    d = key.shape[-1] * key.shape[-2] if key.dim() == 3 else key.shape[-1]
+    _check(_load().b2tts_store_kvcache(key.data_ptr(), value.data_ptr(), key.stride(0), value.stride(0),
+                                       k_cache.data_ptr(), v_cache.data_ptr(), slot_mapping.data_ptr(),
+                                       n, d, _stream()), "store_kvcache")
+
+
+# ------------------------------------------------------------------------------------------ a2
+def paged_attn_decode_workspace_bytes(batch, num_heads, head_dim, max_ctx) -> int:
+    return int(_load().b2tts_paged_attn_decode_workspace_bytes(batch, num_heads, head_dim, max_ctx))
+
+
+def paged_attn_decode(q, k_cache, v_cache, block_table, context_lens, scale, max_ctx, out=None, workspace=None):
+    """q [B, heads, hd] (row stride free); returns out [B, heads, hd] bf16."""
+    _cuda(q, BF16, "q"); _cuda(k_cache, BF16, "k_cache"); _cuda(v_cache, BF16, "v_cache")
+    _cuda(block_table, I32, "block_table"); _cuda(context_lens, I32, "context_lens")
+    b, h, hd = q.shape
+    page, kvh = k_cache.shape[1], k_cache.shape[2]
+    if out is None:
+        out = torch.empty(b, h, hd, dtype=BF16, device=q.device)
+    need = paged_attn_decode_workspace_bytes(b, h, hd, max_ctx)
+    if need and (workspace is None or workspace.numel() * workspace.element_size() < need):
+        workspace = torch.empty(need, dtype=torch.uint8, device=q.device)
+    wbytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    _check(_load().b2tts_paged_attn_decode(q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
+                                           block_table.data_ptr(), block_table.stride(0), context_lens.data_ptr(),
+                                           out.data_ptr(), _ptr(workspace), wbytes, b, h, kvh, hd, page,
+                                           float(scale), int(max_ctx), _stream()), "paged_attn_decode")
+    return out
+
+
+# ------------------------------------------------------------------------------------------ a3
+def varlen_attn_prefill(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, scale,
+                        block_table=None, out=None):
+    """q [T, heads, hd]; k, v packed [Tk, kv_heads, hd] or (with block_table) the paged caches."""
+    _cuda(q, BF16, "q"); _cuda(k, BF16, "k"); _cuda(v, BF16, "v")
+    _cuda(cu_seqlens_q, I32, "cu_seqlens_q"); _cuda(cu_seqlens_k, I32, "cu_seqlens_k")
+    t, h, hd = q.shape
+    if out is None:
+        out = torch.empty(t, h, hd, dtype=BF16, device=q.device)
+    nseq = cu_seqlens_q.numel() - 1
+    if block_table is not None:
+        _cuda(block_table, I32, "block_table")
+        page, kvh = k.shape[1], k.shape[2]
+        ks = vs = kvh * hd
+        bt_ptr, bt_stride = block_table.data_ptr(), block_table.stride(0)
+    else:
+        kvh, page = k.shape[1], 0
+        ks, vs = k.stride(0), v.stride(0)
+        bt_ptr, bt_stride = None, 0
+    _check(_load().b2tts_varlen_attn_prefill(q.data_ptr(), q.stride(0), k.data_ptr(), ks, v.data_ptr(), vs,
+                                             cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), out.data_ptr(),
+                                             nseq, t, int(max_seqlen_q), int(max_seqlen_k), h, kvh, hd, float(scale),
+                                             bt_ptr, bt_stride, page, _stream()), "varlen_attn_prefill")
+    return out
+
+
+# ------------------------------------------------------------------------------------------ a4
+def rmsnorm(x, weight, eps, rounding=ROUND_EAGER, out=None):
+    _cuda(x, BF16, "x"); _cuda(weight, BF16, "weight")
+    cols = x.shape[-1]
+    x2 = x.reshape(-1, cols) if x.is_contiguous() else x
+    if x2.dim() != 2 or x2.stride(1) != 1:
+        x2 = x.contiguous().view(-1, cols)
+    if out is None:
+        out = torch.empty(x.shape, dtype=BF16, device=x.device)
+    _check(_load().b2tts_rmsnorm(x2.data_ptr(), x2.stride(0), weight.data_ptr(), out.data_ptr(),
+                                 x2.shape[0], cols, float(eps), rounding, _stream()), "rmsnorm")
+    return out
+
+
+def add_rmsnorm(x, residual, weight, eps, rounding=ROUND_EAGER, round_sum_first=False, out=None, res_out=None):
+    _cuda(x, BF16, "x"); _cuda(residual, BF16, "residual"); _cuda(weight, BF16, "weight")
+    cols = x.shape[-1]
+    x2, r2 = x.contiguous().view(-1, cols), residual.contiguous().view(-1, cols)
+    if out is None:
+        out = torch.empty(x.shape, dtype=BF16, device=x.device)
+    if res_out is None:
+        res_out = torch.empty(x.shape, dtype=BF16, device=x.device)
+    _check(_load().b2tts_add_rmsnorm(x2.data_ptr(), r2.data_ptr(), weight.data_ptr(), out.data_ptr(),
+                                     res_out.data_ptr(), x2.shape[0], cols, float(eps), rounding,
+                                     int(bool(round_sum_first)), _stream()), "add_rmsnorm")
+    return out, res_out
+
+
+# ------------------------------------------------------------------------------ a4+a5(+a1) fused
+def qknorm_rope_kvwrite(q, k, v, q_weight, k_weight, eps, positions, inv_freq, *, modality=None,
+                        attention_scaling=1.0, slot_mapping=None, k_cache=None, v_cache=None,
+                        q_out=None, k_out=None, want_k_out=True, rounding=ROUND_EAGER):
+    """q [N, heads, 128], k/v [N, kv_heads, 128] (row strides free).  Returns (q_out, k_out)."""
+    _cuda(q, BF16, "q"); _cuda(k, BF16, "k")
+    _cuda(positions, I64, "positions"); _cuda(inv_freq, F32, "inv_freq")
+    n, h, hd = q.shape
+    kvh = k.shape[1]
+    if q_out is None:
+        q_out = torch.empty(n, h, hd, dtype=BF16, device=q.device)
+    if k_out is None and want_k_out:
+        k_out = torch.empty(n, kvh, hd, dtype=BF16, device=q.device)
+    pos_stride = positions.stride(0) if positions.dim() == 2 else 0
+    if v is not None:
+        _cuda(v, BF16, "v")
+    if slot_mapping is not None:
+        _cuda(slot_mapping, I32, "slot_mapping")
+    if modality is not None:
+        _cuda(modality, I32, "modality")
+    _check(_load().b2tts_qknorm_rope_kvwrite(
+        q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), _ptr(v), 0 if v is None else v.stride(0),
+        q_out.data_ptr(), _ptr(k_out), _ptr(q_weight), _ptr(k_weight), float(eps),
+        positions.data_ptr(), pos_stride, inv_freq.data_ptr(), _ptr(modality), float(attention_scaling),
+        _ptr(slot_mapping), _ptr(k_cache), _ptr(v_cache), n, h, kvh, hd, rounding, _stream()), "qknorm_rope_kvwrite")
+    return q_out, k_out
+
+
+# ------------------------------------------------------------------------------------------ a6
+def silu_and_mul(gate, up, rounding=ROUND_EAGER, out=None):
+    """gate/up [rows, inter] with a common row stride (halves of a fused gate_up output).
+    ``up=None`` computes silu(gate)."""
+    _cuda(gate, BF16, "gate")
+    inter = gate.shape[-1]
+    g2 = gate if gate.dim() == 2 else gate.reshape(-1, inter)
+    if g2.stride(1) != 1:
+        g2 = g2.contiguous()
+    u2 = None
+    if up is not None:
+        _cuda(up, BF16, "up")
+        u2 = up if up.dim() == 2 else up.reshape(-1, inter)
+        if u2.stride(1) != 1 or u2.stride(0) != g2.stride(0):
+            g2, u2 = g2.contiguous(), u2.contiguous()
+    if out is None:
+        out = torch.empty(gate.shape, dtype=BF16, device=gate.device)
+    _check(_load().b2tts_silu_and_mul(g2.data_ptr(), _ptr(u2), g2.stride(0), out.data_ptr(), g2.shape[0], inter,
+                                      rounding, _stream()), "silu_and_mul")
+    return out
+
+
+# ------------------------------------------------------------------------------------------ a8
+def topk_sample(logits, temperatures, noise, top_k=50, out=None, probs_out=None):
+    """logits [B, V] bf16 or fp32; temperatures [B] fp32; noise [B, V] fp32 Exp(1) draws."""
+    _cuda(logits, None, "logits"); _cuda(temperatures, F32, "temperatures"); _cuda(noise, F32, "noise")
+    if logits.dtype not in (BF16, F32):
+        raise RuntimeError(f"libb200tts: logits must be bf16 or fp32, got {logits.dtype}")
+    b, v = logits.shape
+    if logits.stride(1) != 1:
+        logits = logits.contiguous()
+    if not noise.is_contiguous():
+        noise = noise.contiguous()
+    if out is None:
+        out = torch.empty(b, dtype=I64, device=logits.device)
+    _check(_load().b2tts_topk_sample(logits.data_ptr(), logits.stride(0), int(logits.dtype == F32),
+                                     temperatures.data_ptr(), noise.data_ptr(), out.data_ptr(), _ptr(probs_out),
+                                     b, v, int(min(top_k, v)), 1.0, 0, _stream()), "topk_sample")
+    return out
+
+
+# ------------------------------------------------------------------------------------------ a9
+def gather_rows(tables, row_index, table_index=None, out=None):
+    """tables [num_tables, rows, cols] (or [rows, cols]); out[i] = tables[table_index[i]][row_index[i]]."""
+    _cuda(tables, BF16, "tables"); _cuda(row_index, I64, "row_index")
+    if tables.dim() == 2:
+        tables = tables.unsqueeze(0)
+    nt, rows, cols = tables.shape
+    n = row_index.numel()
+    if out is None:
+        out = torch.empty(n, cols, dtype=BF16, device=tables.device)
+    if table_index is not None:
+        _cuda(table_index, I32, "table_index")
+    _check(_load().b2tts_gather_rows(tables.data_ptr(), tables.stride(0), rows, row_index.data_ptr(),
+                                     _ptr(table_index), out.data_ptr(), out.stride(0), n, cols, _stream()),
+           "gather_rows")
+    return out
+
+
+def codec_embed_sum(table0, tables_rest, codes, extra=None, out=None):
+    """table0 [V0, cols]; tables_rest [ncb-1, V, cols]; codes [n, ncb] int64; extra [n, cols] or [1, cols]."""
+    _cuda(table0, BF16, "table0"); _cuda(codes, I64, "codes")
+    n, ncb = codes.shape
+    cols = table0.shape[-1]
+    if out is None:
+        out = torch.empty(n, cols, dtype=BF16, device=table0.device)
+    es = 0
+    if extra is not None:
+        _cuda(extra, BF16, "extra")
+        es = extra.stride(0) if extra.shape[0] == n else 0      # one row broadcasts
+    _check(_load().b2tts_codec_embed_sum(table0.data_ptr(), _ptr(tables_rest),
+                                         0 if tables_rest is None else tables_rest.stride(0),
+                                         codes.data_ptr(), codes.stride(0), _ptr(extra), es, out.data_ptr(),
+                                         n, ncb, cols, _stream()), "codec_embed_sum")
+    return out
+
+
+# ------------------------------------------------------------------------------------------ a7
+def has_gemm() -> bool:
+    return hasattr(_load(), "b2tts_gemm_bf16")
+
+
+def device_info():
+    sm, smem, maj, mnr = c_int(), c_int(), c_int(), c_int()
+    _check(_load().b2tts_device_info(ctypes.byref(sm), ctypes.byref(smem), ctypes.byref(maj), ctypes.byref(mnr)),
+           "device_info")
+    return {"sm_count": sm.value, "max_smem": smem.value, "cc": (maj.value, mnr.value)}

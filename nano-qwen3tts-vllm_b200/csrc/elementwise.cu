@@ -1,0 +1,144 @@
+// elementwise.cu - a6 SiLU / SiLU*mul, a9 row gathers and the frame-loop codebook embedding sum.
+// Streaming 16-byte vector passes; grids are sized to cover the data once (no reuse to tile for).
+#include "common.cuh"
+
+namespace b2 {
+
+__device__ __forceinline__ float silu_f(float g) { return g / (1.0f + expf(-g)); }
+
+template <bool EAGER, bool MUL>
+__global__ void __launch_bounds__(256)
+silu_mul_kernel(const __nv_bfloat16* __restrict__ gate, const __nv_bfloat16* __restrict__ up, int64_t in_stride,
+                __nv_bfloat16* __restrict__ out, int rows, int inter) {
+  const int nvec = inter >> 3;
+  const int64_t total = (int64_t)rows * nvec;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int row = (int)(i / nvec), v = (int)(i % nvec);
+    const uint4 g = ldg_nc_v4(gate + (int64_t)row * in_stride + 8 * v);
+    uint4 u = make_uint4(0, 0, 0, 0);
+    if (MUL) u = ldg_nc_v4(up + (int64_t)row * in_stride + 8 * v);
+    const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
+    const uint32_t uw[4] = {u.x, u.y, u.z, u.w};
+    uint32_t ow[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float a = silu_f(bf16lo(gw[e])), b = silu_f(bf16hi(gw[e]));
+      if (MUL) {
+        if (EAGER) { a = rbf(a); b = rbf(b); }       // eager: silu rounds, then the product rounds
+        a *= bf16lo(uw[e]);
+        b *= bf16hi(uw[e]);
+      }
+      ow[e] = pack_bf16(a, b);
+    }
+    stg_v4(out + (int64_t)row * inter + 8 * v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+  }
+}
+
+// out[i] = tables[table_index[i]][row_index[i]]; one warp per output row.
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const __nv_bfloat16* __restrict__ tables, int64_t table_stride, int rows_per_table,
+                   const int64_t* __restrict__ row_index, const int32_t* __restrict__ table_index,
+                   __nv_bfloat16* __restrict__ out, int64_t out_stride, int n, int cols) {
+  const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= n) return;
+  const int64_t r = __ldg(row_index + i);
+  const int t = table_index ? __ldg(table_index + i) : 0;
+  const bool ok = r >= 0 && r < rows_per_table && t >= 0;
+  const __nv_bfloat16* src = tables + (int64_t)t * table_stride + r * cols;
+  __nv_bfloat16* dst = out + (int64_t)i * out_stride;
+  for (int v = lane; v < (cols >> 3); v += 32) stg_v4(dst + 8 * v, ok ? ldg_v4(src + 8 * v) : make_uint4(0, 0, 0, 0));
+}
+
+// out[i] = bf16( bf16(sum_c f32(E_c[codes[i,c]])) + extra[i] ): interface.py:1276-1286 - the
+// 16-codebook sum is one fp32 accumulate rounded once (`codec_hiddens.sum(1)` on bf16), then a
+// bf16 add of the trailing-text / pad embedding.  One CTA per row, a 16-byte vector per thread.
+__global__ void __launch_bounds__(256)
+codec_embed_sum_kernel(const __nv_bfloat16* __restrict__ table0, const __nv_bfloat16* __restrict__ tables_rest,
+                       int64_t table_stride, const int64_t* __restrict__ codes, int64_t codes_stride,
+                       const __nv_bfloat16* __restrict__ extra, int64_t extra_stride,
+                       __nv_bfloat16* __restrict__ out, int ncb, int cols) {
+  const int i = blockIdx.x;
+  for (int v = threadIdx.x; v < (cols >> 3); v += blockDim.x) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int c = 0; c < ncb; ++c) {
+      const int64_t code = __ldg(codes + (int64_t)i * codes_stride + c);
+      const __nv_bfloat16* row = (c == 0 ? table0 : tables_rest + (int64_t)(c - 1) * table_stride) + code * cols;
+      const uint4 r = ldg_v4(row + 8 * v);
+      acc[0] += bf16lo(r.x); acc[1] += bf16hi(r.x); acc[2] += bf16lo(r.y); acc[3] += bf16hi(r.y);
+      acc[4] += bf16lo(r.z); acc[5] += bf16hi(r.z); acc[6] += bf16lo(r.w); acc[7] += bf16hi(r.w);
+    }
+    if (extra) {
+      const uint4 e = ldg_v4(extra + (int64_t)i * extra_stride + 8 * v);
+      acc[0] = rbf(acc[0]) + bf16lo(e.x); acc[1] = rbf(acc[1]) + bf16hi(e.x);
+      acc[2] = rbf(acc[2]) + bf16lo(e.y); acc[3] = rbf(acc[3]) + bf16hi(e.y);
+      acc[4] = rbf(acc[4]) + bf16lo(e.z); acc[5] = rbf(acc[5]) + bf16hi(e.z);
+      acc[6] = rbf(acc[6]) + bf16lo(e.w); acc[7] = rbf(acc[7]) + bf16hi(e.w);
+    }
+    uint4 o;
+    o.x = pack_bf16(acc[0], acc[1]); o.y = pack_bf16(acc[2], acc[3]);
+    o.z = pack_bf16(acc[4], acc[5]); o.w = pack_bf16(acc[6], acc[7]);
+    stg_v4(out + (int64_t)i * cols + 8 * v, o);
+  }
+}
+
+}  // namespace b2
+
+extern "C" int b2tts_silu_and_mul(const void* gate, const void* up, int64_t in_row_stride,
+                                  void* out, int rows, int inter, int rounding, void* stream) {
+  using namespace b2;
+  B2_REQUIRE(rows >= 0 && inter > 0, B2TTS_EINVAL, "silu_and_mul: rows=%d inter=%d", rows, inter);
+  if (rows == 0) return B2TTS_OK;
+  B2_REQUIRE(gate && out, B2TTS_EINVAL, "silu_and_mul: null pointer");
+  B2_REQUIRE(inter % 8 == 0 && in_row_stride % 8 == 0 && aligned16(gate) && aligned16(up) && aligned16(out),
+             B2TTS_EALIGN, "silu_and_mul: inter/stride must be multiples of 8 and pointers 16-byte aligned");
+  B2_REQUIRE(rounding == B2TTS_ROUND_EAGER || rounding == B2TTS_ROUND_FUSED, B2TTS_EINVAL, "silu_and_mul: rounding %d", rounding);
+  const int64_t total = (int64_t)rows * (inter >> 3);
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  auto g = static_cast<const __nv_bfloat16*>(gate);
+  auto u = static_cast<const __nv_bfloat16*>(up);
+  auto o = static_cast<__nv_bfloat16*>(out);
+  if (!up) silu_mul_kernel<true, false><<<(int)blocks, 256, 0, st>>>(g, u, in_row_stride, o, rows, inter);
+  else if (rounding == B2TTS_ROUND_EAGER) silu_mul_kernel<true, true><<<(int)blocks, 256, 0, st>>>(g, u, in_row_stride, o, rows, inter);
+  else silu_mul_kernel<false, true><<<(int)blocks, 256, 0, st>>>(g, u, in_row_stride, o, rows, inter);
+  B2_CHECK_LAUNCH("silu_and_mul");
+  return B2TTS_OK;
+}
+
+extern "C" int b2tts_gather_rows(const void* tables, int64_t table_stride, int rows_per_table,
+                                 const int64_t* row_index, const int32_t* table_index,
+                                 void* out, int64_t out_row_stride, int n, int cols, void* stream) {
+  using namespace b2;
+  B2_REQUIRE(n >= 0 && cols > 0 && rows_per_table > 0, B2TTS_EINVAL, "gather_rows: n=%d cols=%d rows=%d", n, cols, rows_per_table);
+  if (n == 0) return B2TTS_OK;
+  B2_REQUIRE(tables && row_index && out, B2TTS_EINVAL, "gather_rows: null pointer");
+  B2_REQUIRE(cols % 8 == 0 && table_stride % 8 == 0 && out_row_stride % 8 == 0 && aligned16(tables) && aligned16(out),
+             B2TTS_EALIGN, "gather_rows: cols/strides must be multiples of 8 and pointers 16-byte aligned");
+  gather_rows_kernel<<<(n + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(tables), table_stride, rows_per_table, row_index, table_index,
+      static_cast<__nv_bfloat16*>(out), out_row_stride, n, cols);
+  B2_CHECK_LAUNCH("gather_rows");
+  return B2TTS_OK;
+}
+
+extern "C" int b2tts_codec_embed_sum(const void* table0, const void* tables_rest, int64_t table_stride,
+                                     const int64_t* codes, int64_t codes_row_stride,
+                                     const void* extra, int64_t extra_row_stride,
+                                     void* out, int n, int num_codebooks, int cols, void* stream) {
+  using namespace b2;
+  B2_REQUIRE(n >= 0 && cols > 0 && num_codebooks >= 1, B2TTS_EINVAL, "codec_embed_sum: n=%d cols=%d ncb=%d", n, cols, num_codebooks);
+  if (n == 0) return B2TTS_OK;
+  B2_REQUIRE(table0 && codes && out && (num_codebooks == 1 || tables_rest), B2TTS_EINVAL, "codec_embed_sum: null pointer");
+  B2_REQUIRE(cols % 8 == 0 && table_stride % 8 == 0 && extra_row_stride % 8 == 0 && aligned16(table0) &&
+                 aligned16(tables_rest) && aligned16(extra) && aligned16(out),
+             B2TTS_EALIGN, "codec_embed_sum: cols/strides must be multiples of 8 and pointers 16-byte aligned");
+  codec_embed_sum_kernel<<<n, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(table0), static_cast<const __nv_bfloat16*>(tables_rest), table_stride, codes,
+      codes_row_stride, static_cast<const __nv_bfloat16*>(extra), extra_row_stride, static_cast<__nv_bfloat16*>(out),
+      num_codebooks, cols);
+  B2_CHECK_LAUNCH("codec_embed_sum");
+  return B2TTS_OK;
+}
