@@ -120,8 +120,9 @@ B2TTS_API int b2tts_add_rmsnorm(const void* x, const void* res, const void* w, v
  * fused QKV GEMM output).  q_out [n, heads*128] and k_out [n, kv_heads*128] contiguous
  * (may alias q / k when the strides match).  q_weight/k_weight NULL skips the norm
  * (plain RoPE, the rotary_emb.forward surface).  positions int64 [3 or 1][n]
- * (pos_row_stride = 0 for 1-D); inv_freq fp32 [head_dim/2]; modality int32 [head_dim/2]
- * selects the position row per frequency (NULL = row 0).  cos/sin are computed in fp32,
+ * (pos_row_stride = 0 for 1-D); inv_freq fp32 [head_dim/2]; modality int32 [head_dim]
+ * selects the position row per cos/sin column (NULL = row 0; columns f and head_dim/2+f share
+ * frequency f but may read different rows, rotary_embedding.py:73-80).  cos/sin are computed in fp32,
  * scaled by attention_scaling, rounded to bf16, and the rotation is three bf16-rounded
  * ops exactly as the reference's eager expression (rotary_embedding.py:33-34).
  * slot_mapping NULL skips the cache write; otherwise K (normed+rotated) and V (raw) rows

@@ -153,16 +153,27 @@ qknorm_rope_kvwrite_kernel(const QkRopeParams p) {
   const int kv_dim = p.num_kv_heads * HD;
   const int slot = p.slot_mapping ? __ldg(p.slot_mapping + tok) : -1;
 
-  // cos/sin of this lane's two frequencies (2l, 2l+1): fp32 angle, fp32 cos/sin, bf16 result
-  float c[2], s[2];
+  // cos/sin of this lane's columns {2l, 2l+1} (c1/s1) and {64+2l, 64+2l+1} (c2/s2): fp32 angle,
+  // fp32 cos/sin, bf16 result.  Columns f and 64+f share frequency f but - in the sectioned M-RoPE
+  // branch (rotary_embedding.py:73-80) - not necessarily the position row, so the two halves keep
+  // their own cos/sin; with 1-D positions (modality NULL) they are computed once.
+  float c1[2], s1[2], c2[2], s2[2];
 #pragma unroll
   for (int e = 0; e < 2; ++e) {
     const int fi = 2 * lane + e;
-    const int mrow = p.modality ? __ldg(p.modality + fi) : 0;
-    const float pos = (float)__ldg(p.positions + (int64_t)mrow * p.pos_row_stride + tok);
-    const float ang = pos * __ldg(p.inv_freq + fi);
-    c[e] = rbf(cosf(ang) * p.attention_scaling);
-    s[e] = rbf(sinf(ang) * p.attention_scaling);
+    const float f = __ldg(p.inv_freq + fi);
+    const int m1 = p.modality ? __ldg(p.modality + fi) : 0;
+    const float a1 = (float)__ldg(p.positions + (int64_t)m1 * p.pos_row_stride + tok) * f;
+    c1[e] = rbf(cosf(a1) * p.attention_scaling);
+    s1[e] = rbf(sinf(a1) * p.attention_scaling);
+    const int m2 = p.modality ? __ldg(p.modality + HD / 2 + fi) : 0;
+    if (m2 != m1) {
+      const float a2 = (float)__ldg(p.positions + (int64_t)m2 * p.pos_row_stride + tok) * f;
+      c2[e] = rbf(cosf(a2) * p.attention_scaling);
+      s2[e] = rbf(sinf(a2) * p.attention_scaling);
+    } else {
+      c2[e] = c1[e]; s2[e] = s1[e];
+    }
   }
 
   const int total = p.num_heads + p.num_kv_heads;
@@ -187,8 +198,8 @@ qknorm_rope_kvwrite_kernel(const QkRopeParams p) {
     float o1[2], o2[2];
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
-      o1[e] = rbf(x1[e] * c[e]) + rbf(-x2[e] * s[e]);     // rotate_half: first half pairs with -x2
-      o2[e] = rbf(x2[e] * c[e]) + rbf(x1[e] * s[e]);
+      o1[e] = rbf(x1[e] * c1[e]) + rbf(-x2[e] * s1[e]);   // rotate_half: first half pairs with -x2
+      o2[e] = rbf(x2[e] * c2[e]) + rbf(x1[e] * s2[e]);
     }
     const uint32_t y1 = pack_bf16(o1[0], o1[1]), y2 = pack_bf16(o2[0], o2[1]);
     __nv_bfloat16* dst = nullptr;
