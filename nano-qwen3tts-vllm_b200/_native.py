@@ -56,6 +56,7 @@ def _load():
         "b2tts_gather_rows": (I, [P, L, I, P, P, P, L, I, I, P]),
         "b2tts_codec_embed_sum": (I, [P, P, L, P, L, P, L, P, I, I, I, P]),
         "b2tts_gemm_bf16_workspace_bytes": (Z, [I, I, I]),
+        "b2tts_gemm_bf16_supported": (I, [I, I, I]),
         "b2tts_gemm_bf16": (I, [P, L, P, P, P, L, I, I, I, P, Z, P]),
     }
     for name, (res, args) in sig.items():
@@ -312,3 +313,25 @@ def device_info():
     _check(_load().b2tts_device_info(ctypes.byref(sm), ctypes.byref(smem), ctypes.byref(maj), ctypes.byref(mnr)),
            "device_info")
     return {"sm_count": sm.value, "max_smem": smem.value, "cc": (maj.value, mnr.value)}
+
+
+def gemm_supported(m: int, n: int, k: int) -> bool:
+    return has_gemm() and bool(_load().b2tts_gemm_bf16_supported(int(m), int(n), int(k)))
+
+
+def gemm_bf16(x, weight, bias=None, out=None, workspace_fn=None):
+    """y[M,N] = x[M,K] @ weight[N,K]^T (+ bias[N]); bf16 in/out, fp32 accumulate."""
+    _cuda(x, BF16, "x"); _cuda(weight, BF16, "weight")
+    m, k = x.shape
+    n = weight.shape[0]
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    if out is None:
+        out = torch.empty(m, n, dtype=BF16, device=x.device)
+    need = int(_load().b2tts_gemm_bf16_workspace_bytes(m, n, k))
+    ws = None
+    if need:
+        ws = workspace_fn(x.device, need) if workspace_fn else torch.empty(need, dtype=torch.uint8, device=x.device)
+    _check(_load().b2tts_gemm_bf16(x.data_ptr(), x.stride(0), weight.data_ptr(), _ptr(bias), out.data_ptr(),
+                                   out.stride(0), m, n, k, _ptr(ws), need, _stream()), "gemm_bf16")
+    return out

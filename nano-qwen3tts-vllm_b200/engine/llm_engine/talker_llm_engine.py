@@ -1,0 +1,55 @@
+"""``TalkerLLMEngine`` step API (reference engine/llm_engine/talker_llm_engine.py:86-134)."""
+from __future__ import annotations
+
+import torch
+
+from ...sampling_params import SamplingParams
+from ..model_runner.talker_mode_runner import TalkerModeModelRunner
+from ..scheduler import TalkerScheduler
+from ..sequence import Sequence
+from .base import LLMEngine
+
+
+class TalkerLLMEngine(LLMEngine):
+    runner_cls = TalkerModeModelRunner
+    scheduler_cls = TalkerScheduler
+
+    def add_request(self, inputs_embeds: list[torch.Tensor], sampling_params: SamplingParams | list[SamplingParams],
+                    request_id: str | None = None):
+        """New ``request_id`` -> a prefill of ``inputs_embeds[i] [1, T, H]``; known ``request_id`` ->
+        the tensor is the next decode input of that stream."""
+        if not isinstance(sampling_params, list):
+            sampling_params = [sampling_params] * len(inputs_embeds)
+        for emb, sp in zip(inputs_embeds, sampling_params):
+            emb = self._to_device(emb)
+            if request_id is not None and request_id in self.scheduler.request_id_to_seq:
+                self.scheduler.request_id_to_seq[request_id].decode_input_embeds = emb
+                return
+            seq = Sequence([], input_embeds=emb, sampling_params=sp, request_id=request_id)
+            if request_id is not None:
+                self.scheduler.request_id_to_seq[request_id] = seq
+            self.scheduler.add(seq)
+
+    def _step(self):
+        seqs, is_prefill = self.scheduler.schedule()
+        if not seqs:
+            return None, 0, []
+        token_ids, hidden = self.model_runner.call("run", seqs, is_prefill)
+        self.scheduler.postprocess(seqs, token_ids, hidden)
+        return seqs, (sum(len(s) for s in seqs) if is_prefill else -len(seqs)), seqs
+
+    def step(self):
+        seqs, num_tokens, _ = self._step()
+        if seqs is None:
+            return [], 0
+        return [(s.request_id, s.seq_id, s.completion_token_ids, s.last_hidden_state) for s in seqs if s.is_finished], \
+            num_tokens
+
+    def step_with_outputs(self):
+        seqs, num_tokens, _ = self._step()
+        if seqs is None:
+            return [], 0, []
+        outputs = [(s.request_id, s.seq_id, s.completion_token_ids, s.last_hidden_state) for s in seqs if s.is_finished]
+        outputs_all = [(s.request_id, s.seq_id, s.completion_token_ids, s.last_hidden_state, s.is_finished)
+                       for s in seqs]
+        return outputs, num_tokens, outputs_all

@@ -1,0 +1,91 @@
+"""Multi-codebook code predictor (models/qwen3_tts_predictor.py:14-125 of the reference).
+
+The 15 codec embeddings and 15 LM heads are single stacked tensors so that the per-sequence
+Python loops of the reference (``codec_embedding[g_i-1](id_i)``, ``lm_head[g_i](h_i)``,
+qwen3_tts_predictor.py:94-95,119-121) become one gather kernel with a per-row table index and one
+GEMM per distinct generation step present in the batch (one, in practice: sequences of a burst
+step together)."""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from .. import _native as nat
+from ..config import StackConfig
+from ..layers.linear import ReplicatedLinear, linear
+from .qwen3_tts_share import DecoderStack, load_reference_weights
+
+
+class Qwen3TTSCodePredictorModel(DecoderStack):
+    def __init__(self, config: StackConfig, talker_config: StackConfig, rounding: int = nat.ROUND_EAGER):
+        super().__init__(config, rounding)
+        n = config.num_code_groups - 1
+        # [n, vocab, talker_hidden]: embeddings live in the TALKER's width (predictor.py:24-27)
+        self.codec_embedding = nn.Parameter(torch.empty(n, config.vocab_size, talker_config.hidden_size),
+                                            requires_grad=False)
+
+    def forward(self, input_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
+        return self.run_layers(input_embeds, positions)
+
+
+class Qwen3TTSCodePredictorForCausalLM(nn.Module):
+    def __init__(self, config: StackConfig, talker_config: StackConfig, rounding: int = nat.ROUND_EAGER):
+        super().__init__()
+        self.config = config
+        self.model = Qwen3TTSCodePredictorModel(config, talker_config, rounding)
+        self.vocab_size = config.vocab_size
+        n = config.num_code_groups - 1
+        self.lm_head = nn.Parameter(torch.empty(n, config.vocab_size, config.hidden_size), requires_grad=False)
+        if config.hidden_size != talker_config.hidden_size:
+            self.small_to_mtp_projection = ReplicatedLinear(talker_config.hidden_size, config.hidden_size, bias=True)
+        else:
+            self.small_to_mtp_projection = None
+
+    @staticmethod
+    def convert_state_dict(state_dict: dict) -> dict:
+        pre = "talker.code_predictor."
+        return {k[len(pre):]: v for k, v in state_dict.items() if k.startswith(pre)}
+
+    def load_state_dict(self, state_dict, strict=True):
+        sd = self.convert_state_dict(state_dict)
+        if not sd:                                   # already converted
+            sd = dict(state_dict)
+        rest = {}
+        for k, v in sd.items():
+            parts = k.split(".")
+            if k.startswith("model.codec_embedding.") and parts[2].isdigit():
+                self.model.codec_embedding.data[int(parts[2])].copy_(v)
+            elif k.startswith("lm_head.") and parts[1].isdigit():
+                self.lm_head.data[int(parts[1])].copy_(v)
+            else:
+                rest[k] = v
+        return load_reference_weights(self, rest, strict=strict)
+
+    def get_input_embeddings(self, input_ids, input_embeds, generation_steps):
+        """Prefill: the [hidden, embed(code0)] rows pass through.  Decode: row i is
+        ``codec_embedding[generation_steps[i]-1][input_ids[i]]``."""
+        if input_embeds is not None and input_embeds.shape[-2] > 1:
+            return input_embeds
+        steps = generation_steps if torch.is_tensor(generation_steps) else \
+            torch.tensor(generation_steps, dtype=torch.int32, device=input_ids.device)
+        return nat.gather_rows(self.model.codec_embedding, input_ids.view(-1), (steps - 1).to(torch.int32))
+
+    def forward(self, inputs_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
+        if self.small_to_mtp_projection is not None:
+            inputs_embeds = self.small_to_mtp_projection(inputs_embeds)
+        return self.model(inputs_embeds, positions)
+
+    def compute_logits(self, hidden_states: torch.Tensor, generation_steps: list[int]) -> torch.Tensor:
+        """hidden_states [num_seqs * len, H] -> logits of the LAST position of every sequence through
+        head ``generation_steps[i]`` (all sequences have equal length, predictor.py:118,124)."""
+        nseq = len(generation_steps)
+        per = hidden_states.shape[0] // nseq
+        last = hidden_states.view(nseq, per, -1)[:, -1, :]
+        uniq = sorted(set(generation_steps))
+        if len(uniq) == 1:
+            return linear(last, self.lm_head[uniq[0]])
+        out = torch.empty(nseq, self.vocab_size, dtype=hidden_states.dtype, device=hidden_states.device)
+        for g in uniq:
+            idx = torch.tensor([i for i, s in enumerate(generation_steps) if s == g], device=out.device)
+            out[idx] = linear(last[idx], self.lm_head[g])
+        return out

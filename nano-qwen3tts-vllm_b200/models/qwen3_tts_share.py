@@ -1,0 +1,157 @@
+"""Decoder-layer building blocks shared by the talker and the code predictor
+(models/qwen3_tts_share.py:17-176 of the reference), re-cut for the B200 kernels:
+
+  reference per layer (~37 launches)                     here (9 launches)
+  ---------------------------------------------------    ----------------------------------------
+  residual add, input RMSNorm                            add+RMSNorm (sum rounded to bf16 first)
+  q_proj, k_proj, v_proj (3 GEMMs)                       one QKV GEMM over the merged weight
+  q_norm, k_norm, ~20 eager RoPE ops, store_kvcache      one fused q/k-norm + RoPE + paged KV write
+  flash_attn_with_kvcache | flash_attn_varlen_func       paged decode | varlen prefill attention
+  o_proj                                                 o GEMM
+  residual add, post-attention RMSNorm                   add+RMSNorm
+  gate_proj, up_proj, silu*mul                           one gate_up GEMM, one SiLU*mul
+  down_proj                                              down GEMM
+
+Rounding points are the reference's (DESIGN.md "rounding points"); the state-dict keys of the
+reference (``self_attn.{q,k,v,o}_proj.weight`` ...) are accepted by ``load_reference_weights`` and
+merged at load time."""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from .. import _native as nat
+from ..config import StackConfig
+from ..layers.activation import SiluAndMul
+from ..layers.attention import Attention
+from ..layers.layernorm import Qwen3TTSRMSNorm
+from ..layers.linear import MergedColumnParallelLinear, QKVParallelLinear, RowParallelLinear
+from ..layers.rotary_embedding import get_rope
+from ..utils.context import get_context
+
+
+class Qwen3TTSAttention(nn.Module):
+    def __init__(self, config: StackConfig, rounding: int = nat.ROUND_EAGER) -> None:
+        super().__init__()
+        self.num_heads = config.num_attention_heads
+        self.num_kv_heads = config.num_key_value_heads
+        self.head_dim = config.head_dim
+        self.q_size = self.num_heads * self.head_dim
+        self.kv_size = self.num_kv_heads * self.head_dim
+        self.scaling = self.head_dim ** -0.5                              # qwen3_tts_share.py:37
+        self.eps = config.rms_norm_eps
+        self.rounding = rounding
+        self.qkv_proj = QKVParallelLinear(config.hidden_size, self.head_dim, self.num_heads, self.num_kv_heads)
+        self.o_proj = RowParallelLinear(self.q_size, config.hidden_size)
+        self.q_norm = Qwen3TTSRMSNorm(self.head_dim, eps=self.eps, rounding=rounding)
+        self.k_norm = Qwen3TTSRMSNorm(self.head_dim, eps=self.eps, rounding=rounding)
+        self.rotary_emb = get_rope(self.head_dim, self.head_dim, config.max_position_embeddings, config.rope_theta,
+                                   config.rope_scaling)
+        self.attn = Attention(self.num_heads, self.head_dim, self.scaling, self.num_kv_heads)
+
+    def forward(self, positions: torch.Tensor, hidden_states: torch.Tensor) -> torch.Tensor:
+        ctx = get_context()
+        n = hidden_states.shape[0]
+        qkv = self.qkv_proj(hidden_states)
+        q = qkv[:, :self.q_size].view(n, self.num_heads, self.head_dim)
+        k = qkv[:, self.q_size:self.q_size + self.kv_size].view(n, self.num_kv_heads, self.head_dim)
+        v = qkv[:, self.q_size + self.kv_size:].view(n, self.num_kv_heads, self.head_dim)
+        have_cache = self.attn.k_cache.numel() > 0
+        packed_kv = ctx.is_prefill and ctx.block_tables is None           # prefill attends to the projections
+        rope = self.rotary_emb
+        q_rot, k_rot = nat.qknorm_rope_kvwrite(
+            q, k, v, self.q_norm.weight, self.k_norm.weight, self.eps, positions, rope.inv_freq,
+            modality=rope.modality if positions.dim() > 1 else None, attention_scaling=rope.attention_scaling,
+            slot_mapping=ctx.slot_mapping if have_cache else None,
+            k_cache=self.attn.k_cache if have_cache else None, v_cache=self.attn.v_cache if have_cache else None,
+            want_k_out=packed_kv or not have_cache, rounding=self.rounding)
+        o = self.attn.attend(q_rot, k_rot, v)
+        return self.o_proj(o.view(n, self.q_size))
+
+
+class Qwen3TTSTalkerTextMLP(nn.Module):
+    def __init__(self, config: StackConfig, rounding: int = nat.ROUND_EAGER) -> None:
+        super().__init__()
+        self.gate_up_proj = MergedColumnParallelLinear(config.hidden_size, [config.intermediate_size] * 2)
+        self.down_proj = RowParallelLinear(config.intermediate_size, config.hidden_size)
+        self.act_fn = SiluAndMul(rounding)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self.down_proj(self.act_fn(self.gate_up_proj(x)))
+
+
+class Qwen3TTSDecoderLayer(nn.Module):
+    def __init__(self, config: StackConfig, rounding: int = nat.ROUND_EAGER) -> None:
+        super().__init__()
+        self.self_attn = Qwen3TTSAttention(config, rounding)
+        self.mlp = Qwen3TTSTalkerTextMLP(config, rounding)
+        self.input_layernorm = Qwen3TTSRMSNorm(config.hidden_size, eps=config.rms_norm_eps, rounding=rounding)
+        self.post_attention_layernorm = Qwen3TTSRMSNorm(config.hidden_size, eps=config.rms_norm_eps, rounding=rounding)
+        self.eps = config.rms_norm_eps
+        self.rounding = rounding
+
+    def forward(self, positions: torch.Tensor, hidden_states: torch.Tensor, residual: torch.Tensor | None):
+        """Returns (block output, residual stream).  ``residual + hidden`` is rounded to bf16 before the
+        norm, which is what the reference's separate add + rms_forward computes
+        (qwen3_tts_share.py:163-176)."""
+        if residual is None:
+            residual = hidden_states
+            hidden_states = self.input_layernorm(hidden_states)
+        else:
+            hidden_states, residual = nat.add_rmsnorm(hidden_states, residual, self.input_layernorm.weight, self.eps,
+                                                      self.rounding, round_sum_first=True)
+        hidden_states = self.self_attn(positions, hidden_states)
+        hidden_states, residual = nat.add_rmsnorm(hidden_states, residual, self.post_attention_layernorm.weight,
+                                                  self.eps, self.rounding, round_sum_first=True)
+        hidden_states = self.mlp(hidden_states)
+        return hidden_states, residual
+
+
+class DecoderStack(nn.Module):
+    """``layers`` + final ``norm`` (Qwen3TTSTalkerModel / Qwen3TTSCodePredictorModel bodies)."""
+
+    def __init__(self, config: StackConfig, rounding: int = nat.ROUND_EAGER) -> None:
+        super().__init__()
+        self.config = config
+        self.rounding = rounding
+        self.layers = nn.ModuleList([Qwen3TTSDecoderLayer(config, rounding) for _ in range(config.num_hidden_layers)])
+        self.norm = Qwen3TTSRMSNorm(config.hidden_size, eps=config.rms_norm_eps, rounding=rounding)
+
+    def run_layers(self, input_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
+        hidden_states, residual = input_embeds, None
+        for layer in self.layers:
+            hidden_states, residual = layer(positions, hidden_states, residual)
+        out, _ = nat.add_rmsnorm(hidden_states, residual, self.norm.weight, self.config.rms_norm_eps, self.rounding,
+                                 round_sum_first=True)
+        return out
+
+
+_MERGED = {"q_proj": ("qkv_proj", 0), "k_proj": ("qkv_proj", 1), "v_proj": ("qkv_proj", 2),
+           "gate_proj": ("gate_up_proj", 0), "up_proj": ("gate_up_proj", 1)}
+
+
+def load_reference_weights(module: nn.Module, state_dict: dict, strict: bool = True) -> list[str]:
+    """Load a state dict that uses the reference's (converted) key names into ``module``, merging
+    q/k/v and gate/up shards into the fused parameters.  Returns the keys that were not consumed."""
+    params = dict(module.named_parameters())
+    unused = []
+    for name, w in state_dict.items():
+        target, shard = name, None
+        for src, (dst, sid) in _MERGED.items():
+            if f".{src}." in name:
+                target, shard = name.replace(f".{src}.", f".{dst}."), sid
+                break
+        p = params.get(target)
+        if p is None:
+            unused.append(name)
+            continue
+        loader = getattr(p, "weight_loader", None)
+        if shard is not None:
+            loader(p, w, shard)
+        elif loader is not None:
+            loader(p, w)
+        else:
+            p.data.copy_(w)
+    if strict and unused:
+        raise KeyError(f"unexpected keys: {unused[:8]}{'...' if len(unused) > 8 else ''}")
+    return unused
