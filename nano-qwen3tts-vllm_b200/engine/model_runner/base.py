@@ -43,8 +43,9 @@ class StepLayout:
             self.offsets[name] = (off, nbytes, dt, w)
             off += (nbytes + 15) // 16 * 16
         self.nbytes = off
-        self.host = torch.empty(off, dtype=torch.uint8).pin_memory() if torch.cuda.is_available() \
-            else torch.empty(off, dtype=torch.uint8)
+        self.host = torch.zeros(off, dtype=torch.uint8)
+        if torch.cuda.is_available():
+            self.host = self.host.pin_memory()
         self.dev = torch.zeros(off, dtype=torch.uint8, device=device)
         hn = self.host.numpy()
         self.h, self.d = {}, {}
@@ -58,6 +59,7 @@ class StepLayout:
         self.h["slot_mapping"][:] = -1
         self.h["block_tables"][:] = -1
         self.h["temperatures"][:] = 1.0
+        self.h["gen_steps"][:] = 1
         self.upload()
 
     def upload(self):
@@ -149,10 +151,9 @@ class ModelRunner:
                                     c.num_key_value_heads, c.head_dim, dtype=BF16, device=self.device)
         ws_bytes = nat.paged_attn_decode_workspace_bytes(1, c.num_attention_heads, c.head_dim,
                                                          self.max_blocks * self.block_size)
-        for bs in (1, 2, 4, 8, 16, 32, 64, 128, 256, 512):
-            if bs <= self.max_bs:
-                ws_bytes = max(ws_bytes, nat.paged_attn_decode_workspace_bytes(
-                    bs, c.num_attention_heads, c.head_dim, self.max_blocks * self.block_size))
+        for bs in range(1, self.max_bs + 1):
+            ws_bytes = max(ws_bytes, nat.paged_attn_decode_workspace_bytes(
+                bs, c.num_attention_heads, c.head_dim, self.max_blocks * self.block_size))
         self.attn_workspace = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=self.device)
         layer_id = 0
         for module in self.model.modules():
