@@ -51,6 +51,8 @@ extern "C" {
 
 B2TTS_API int         b2tts_version(void);                 /* ABI version, bumped on any signature change */
 B2TTS_API const char* b2tts_last_error(void);              /* thread-local, never NULL */
+/* Kernels launched (or recorded into a CUDA graph under capture) by this library in this process. */
+B2TTS_API unsigned long long b2tts_launch_count(void);
 /* SM count / max dynamic smem of the current device (host query, cached). */
 B2TTS_API int         b2tts_device_info(int* sm_count, int* max_smem_bytes, int* cc_major, int* cc_minor);
 
@@ -174,6 +176,17 @@ B2TTS_API int b2tts_codec_embed_sum(const void* table0, const void* tables_rest,
                           const int64_t* codes, int64_t codes_row_stride,
                           const void* extra, int64_t extra_row_stride,
                           void* out, int n, int num_codebooks, int cols, void* stream);
+
+/* ---- a12 on the device: decode batch layout -------------------------------------------------------
+ * replaces the host loops of prepare_decode / prepare_decode_talker
+ *                          engine/model_runner/base.py:218-234, talker_mode_runner.py:116-140
+ * seq_lens [n] int32 (device) = tokens of each stream INCLUDING the one decoded this step, 0 =
+ * inactive row.  Writes context_lens = len, slot = block_table[i][(len-1)/page]*page + (len-1)%page,
+ * positions = len-1+position_offset (1 = talker quirk, 0 = predictor); inactive rows get slot -1,
+ * context 0.  advance != 0 then adds `advance` to the active seq_lens (next step's length). */
+B2TTS_API int b2tts_decode_layout(int32_t* seq_lens, const int32_t* block_table, int bt_stride, int page_size,
+                        int position_offset, int advance, int64_t* positions, int32_t* slot_mapping,
+                        int32_t* context_lens, int n, void* stream);
 
 #ifdef __cplusplus
 }

@@ -44,6 +44,7 @@ def _load():
         "b2tts_version": (I, []),
         "b2tts_last_error": (c_char_p, []),
         "b2tts_device_info": (I, [P, P, P, P]),
+        "b2tts_launch_count": (ctypes.c_ulonglong, []),
         "b2tts_store_kvcache": (I, [P, P, L, L, P, P, P, I, I, P]),
         "b2tts_paged_attn_decode_workspace_bytes": (Z, [I, I, I, I]),
         "b2tts_paged_attn_decode": (I, [P, L, P, P, P, I, P, P, P, Z, I, I, I, I, I, F, I, P]),
@@ -55,6 +56,7 @@ def _load():
         "b2tts_topk_sample": (I, [P, L, I, P, P, P, P, I, I, I, F, I, P]),
         "b2tts_gather_rows": (I, [P, L, I, P, P, P, L, I, I, P]),
         "b2tts_codec_embed_sum": (I, [P, P, L, P, L, P, L, P, I, I, I, P]),
+        "b2tts_decode_layout": (I, [P, P, I, I, I, I, P, P, P, I, P]),
         "b2tts_gemm_bf16_workspace_bytes": (Z, [I, I, I]),
         "b2tts_gemm_bf16_supported": (I, [I, I, I]),
         "b2tts_gemm_bf16": (I, [P, L, P, P, P, L, I, I, I, P, Z, P]),
@@ -303,9 +305,24 @@ def codec_embed_sum(table0, tables_rest, codes, extra=None, out=None):
     return out
 
 
+def decode_layout(seq_lens, block_table, page_size, position_offset, advance, positions, slot_mapping, context_lens):
+    """Device-side prepare_decode: see include/b200tts.h.  All tensors are device tensors, updated in place."""
+    _cuda(seq_lens, I32, "seq_lens"); _cuda(block_table, I32, "block_table"); _cuda(positions, I64, "positions")
+    _cuda(slot_mapping, I32, "slot_mapping"); _cuda(context_lens, I32, "context_lens")
+    n = seq_lens.numel()
+    _check(_load().b2tts_decode_layout(seq_lens.data_ptr(), block_table.data_ptr(), block_table.stride(0),
+                                       int(page_size), int(position_offset), int(advance), positions.data_ptr(),
+                                       slot_mapping.data_ptr(), context_lens.data_ptr(), n, _stream()), "decode_layout")
+
+
 # ------------------------------------------------------------------------------------------ a7
 def has_gemm() -> bool:
     return hasattr(_load(), "b2tts_gemm_bf16")
+
+
+def launch_count() -> int:
+    """Kernels this library has launched (or recorded under graph capture) in this process."""
+    return int(_load().b2tts_launch_count())
 
 
 def device_info():

@@ -20,6 +20,9 @@ int cuda_fail(cudaError_t e, const char* what) {
   return B2TTS_ECUDA;
 }
 
+static unsigned long long g_launches = 0;
+void count_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); }
+
 int sm_count() {
   // per-device constant cache (the only global state the library keeps)
   static int cached[64] = {0};
@@ -40,6 +43,8 @@ extern "C" {
 int b2tts_version(void) { return 1; }
 
 const char* b2tts_last_error(void) { return b2::g_err; }
+
+unsigned long long b2tts_launch_count(void) { return __atomic_load_n(&b2::g_launches, __ATOMIC_RELAXED); }
 
 int b2tts_device_info(int* sm_count, int* max_smem_bytes, int* cc_major, int* cc_minor) {
   int dev = 0;

@@ -22,8 +22,11 @@ int cuda_fail(cudaError_t e, const char* what);
     }                                          \
   } while (0)
 
+void count_launch();
+
 #define B2_CHECK_LAUNCH(what)                           \
   do {                                                  \
+    b2::count_launch();                                 \
     cudaError_t e__ = cudaGetLastError();               \
     if (e__ != cudaSuccess) return b2::cuda_fail(e__, what); \
   } while (0)

@@ -142,3 +142,44 @@ extern "C" int b2tts_codec_embed_sum(const void* table0, const void* tables_rest
   B2_CHECK_LAUNCH("codec_embed_sum");
   return B2TTS_OK;
 }
+
+// ---- a12 on the device: the decode layout of prepare_decode / prepare_decode_talker
+// (engine/model_runner/base.py:218-234, talker_mode_runner.py:116-140) computed from a device-resident
+// sequence-length vector, so that a frame loop can run without the host touching the layout.
+// seq_lens[i] = tokens of stream i INCLUDING the one decoded this step (0 = inactive row):
+//   context_lens[i] = len;  slot[i] = block_table[i][(len-1)/page]*page + (len-1)%page;
+//   positions[i]    = len - 1 + position_offset   (offset 1 for the talker, 0 for the predictor);
+// then, if advance != 0, seq_lens[i] += advance for active rows (the next step's length).
+namespace b2 {
+__global__ void decode_layout_kernel(int32_t* __restrict__ seq_lens, const int32_t* __restrict__ block_table,
+                                     int bt_stride, int page, int position_offset, int advance,
+                                     int64_t* __restrict__ positions, int32_t* __restrict__ slot_mapping,
+                                     int32_t* __restrict__ context_lens, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int len = seq_lens[i];
+  if (len <= 0) {
+    positions[i] = 0; slot_mapping[i] = -1; context_lens[i] = 0;
+    return;
+  }
+  const int t = len - 1;
+  const int pg = block_table[(int64_t)i * bt_stride + t / page];
+  positions[i] = (int64_t)t + position_offset;
+  slot_mapping[i] = pg < 0 ? -1 : pg * page + t % page;
+  context_lens[i] = len;
+  if (advance) seq_lens[i] = len + advance;
+}
+}  // namespace b2
+
+extern "C" int b2tts_decode_layout(int32_t* seq_lens, const int32_t* block_table, int bt_stride, int page_size,
+                                   int position_offset, int advance, int64_t* positions, int32_t* slot_mapping,
+                                   int32_t* context_lens, int n, void* stream) {
+  using namespace b2;
+  B2_REQUIRE(n >= 0 && page_size > 0 && bt_stride > 0, B2TTS_EINVAL, "decode_layout: n=%d page=%d bt_stride=%d", n, page_size, bt_stride);
+  if (n == 0) return B2TTS_OK;
+  B2_REQUIRE(seq_lens && block_table && positions && slot_mapping && context_lens, B2TTS_EINVAL, "decode_layout: null pointer");
+  decode_layout_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      seq_lens, block_table, bt_stride, page_size, position_offset, advance, positions, slot_mapping, context_lens, n);
+  B2_CHECK_LAUNCH("decode_layout");
+  return B2TTS_OK;
+}

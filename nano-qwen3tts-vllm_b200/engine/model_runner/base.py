@@ -104,7 +104,12 @@ class ModelRunner:
     def hidden_in(self) -> int:
         return self.stack_config.hidden_size
 
-    def load_model(self, state_dict: dict | None):
+    def load_model(self, state_dict: dict | str | None):
+        if isinstance(state_dict, str) and state_dict.startswith("random"):     # "random" | "random:<seed>"
+            from ...models.qwen3_tts_share import random_init_
+            seed = int(state_dict.split(":")[1]) if ":" in state_dict else 1234
+            random_init_(self.model, seed + (0 if self.is_talker else 1))
+            return
         if state_dict is None and self.config.model:
             import os
             path = os.path.join(self.config.model, "model.safetensors")
@@ -118,6 +123,7 @@ class ModelRunner:
     # ------------------------------------------------------------------ init
     def post_init(self):
         self.sampler = Sampler()
+        self.top_k = 50        # the reference never forwards SamplingParams.top_k; 1 = greedy
         self.layout = StepLayout(self.max_bs, self.max_blocks, self.device)
         self.allocate_kv_cache()
         self.graphs: dict[int, torch.cuda.CUDAGraph] = {}

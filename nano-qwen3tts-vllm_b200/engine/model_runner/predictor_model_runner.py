@@ -53,6 +53,6 @@ class PredictorModelRunner(ModelRunner):
     def run(self, seqs: list[Sequence], is_prefill: bool) -> list[int]:
         logits = self.run_model(seqs, is_prefill)
         temperatures = self.layout.d["temperatures"][:len(seqs)] if not is_prefill else self.prepare_sample(seqs)
-        token_ids = self.sampler(logits, temperatures).tolist()
+        token_ids = self.sampler(logits, temperatures, top_k=self.top_k).tolist()
         reset_context()
         return token_ids

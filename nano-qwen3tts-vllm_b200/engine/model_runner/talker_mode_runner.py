@@ -66,6 +66,6 @@ class TalkerModeModelRunner(ModelRunner):
     def run(self, seqs: list[Sequence], is_prefill: bool):
         logits, hidden = self.run_model(seqs, is_prefill)
         temperatures = self.layout.d["temperatures"][:len(seqs)] if not is_prefill else self.prepare_sample(seqs)
-        token_ids = self.sampler(logits, temperatures).tolist()              # the step's one device sync
+        token_ids = self.sampler(logits, temperatures, top_k=self.top_k).tolist()              # the step's one device sync
         reset_context()
         return token_ids, hidden.clone()

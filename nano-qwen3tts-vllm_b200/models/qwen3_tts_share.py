@@ -155,3 +155,18 @@ def load_reference_weights(module: nn.Module, state_dict: dict, strict: bool = T
     if strict and unused:
         raise KeyError(f"unexpected keys: {unused[:8]}{'...' if len(unused) > 8 else ''}")
     return unused
+
+
+@torch.no_grad()
+def random_init_(module: nn.Module, seed: int = 1234, std: float = 0.02) -> None:
+    """Random-init weights in place on the module's device (every BASELINE config uses random
+    weights): matrices / embeddings N(0, std^2) (``initializer_range``, config.py:299,484), norm weights
+    1 + N(0, std^2), biases 0 - the distribution of SURVEY.md section 8d."""
+    gen = torch.Generator(device=next(module.parameters()).device).manual_seed(seed)
+    for name, p in module.named_parameters():
+        if name.endswith("bias"):
+            p.zero_()
+        elif "norm" in name and p.dim() == 1:
+            p.copy_(1.0 + torch.randn(p.shape, generator=gen, device=p.device, dtype=torch.float32) * std)
+        else:
+            p.copy_(torch.randn(p.shape, generator=gen, device=p.device, dtype=torch.float32) * std)
