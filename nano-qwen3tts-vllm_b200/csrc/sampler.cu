@@ -70,15 +70,33 @@ topk_sample_kernel(const void* __restrict__ logits, int64_t row_stride, const fl
         if ((key & himask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
       }
       __syncthreads();
-      if (tid == 0) {
-        uint32_t rem = sel_remaining, d = 255;
-        for (;; --d) {                              // walk bins from the largest digit down
-          const uint32_t c = hist[d];
-          if (c >= rem || d == 0) break;
-          rem -= c;
+      if (warp == 0) {
+        // bins walked from the largest digit down: lane l owns bins [255-8l-7, 255-8l]; an exclusive
+        // warp scan of the per-lane totals finds the lane, 8 sequential steps find the bin.
+        const uint32_t rem = sel_remaining;
+        uint32_t c[8], tot = 0;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { c[e] = hist[255 - (8 * lane + e)]; tot += c[e]; }
+        uint32_t incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
         }
-        sel_prefix = prefix | (d << shift);
-        sel_remaining = rem;
+        const uint32_t excl = incl - tot;
+        // the owning lane: first lane whose inclusive count reaches rem (lane 31 if none: digit 0)
+        const uint32_t hit = __ballot_sync(0xffffffffu, incl >= rem);
+        const int owner = hit ? __ffs(hit) - 1 : 31;
+        if (lane == owner) {
+          uint32_t left = rem - excl, d = 255 - 8 * lane;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            if (c[e] >= left || (lane == 31 && e == 7)) { d = 255 - (8 * lane + e); break; }
+            left -= c[e];
+          }
+          sel_prefix = prefix | (d << shift);
+          sel_remaining = left;
+        }
       }
       __syncthreads();
     }

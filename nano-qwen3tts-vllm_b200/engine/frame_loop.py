@@ -129,7 +129,7 @@ class DeviceFrameLoop:
             lay = self.p_dec[g - 1]
             emb = nat.gather_rows(predictor.model.codec_embedding[g - 1], self.codes_t[g])
             set_context(False, slot_mapping=lay["slots"], context_lens=lay["ctx"], block_tables=self.p_tables,
-                        max_context_len=self.page)
+                        max_context_len=g + 2)           # exact: no split-KV, no combine launch
             h = predictor(emb, lay["pos"])
             self._sample(linear(h, predictor.lm_head[g]), self.p_temp, self.codes_t[g + 1])
         # ---- emit the frame, build the next talker input                       interface.py:1269-1286

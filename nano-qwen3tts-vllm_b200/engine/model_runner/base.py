@@ -243,7 +243,11 @@ class ModelRunner:
     def set_decode_context(self, rows: int):
         d = self.layout.d
         set_context(False, slot_mapping=d["slot_mapping"][:rows], context_lens=d["context_lens"][:rows],
-                    block_tables=d["block_tables"][:rows], max_context_len=self.max_blocks * self.block_size)
+                    block_tables=d["block_tables"][:rows], max_context_len=self.decode_max_context())
+
+    def decode_max_context(self) -> int:
+        """Upper bound of a decode context; only sizes the split-KV grid (any length stays correct)."""
+        return self.max_blocks * self.block_size
 
     def pick_graph(self, n: int) -> int | None:
         if self.enforce_eager:

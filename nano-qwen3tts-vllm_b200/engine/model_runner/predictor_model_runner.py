@@ -25,6 +25,9 @@ class PredictorModelRunner(ModelRunner):
             return sorted(self.config.graph_batch_sizes)
         return list(range(1, 16)) + list(range(16, self.max_bs + 1, 16))     # predictor_model_runner.py:173
 
+    def decode_max_context(self) -> int:
+        return 32          # 2 prompt rows + 15 codes: one KV tile pair, never worth a split-KV grid
+
     def decode_body(self, rows: int) -> torch.Tensor:
         d = self.layout.d
         emb = self.model.get_input_embeddings(d["last_tokens"][:rows], None, d["gen_steps"][:rows])
