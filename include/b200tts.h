@@ -188,6 +188,41 @@ B2TTS_API int b2tts_decode_layout(int32_t* seq_lens, const int32_t* block_table,
                         int position_offset, int advance, int64_t* positions, int32_t* slot_mapping,
                         int32_t* context_lens, int n, void* stream);
 
+/* ---- a7: the projections (weight-streaming tcgen05 GEMM) -------------------------------------------
+ * replaces F.linear in ColumnParallelLinear / RowParallelLinear.forward   layers/linear.py:72-73, 149-153
+ *   (q/k/v and gate/up as ONE GEMM each over a merged weight: models/qwen3_tts_share.py:85-87, 126-134),
+ *   nn.Linear small_to_mtp_projection / lm_head[g]                 models/qwen3_tts_predictor.py:54-61,
+ *   ParallelLMHead's F.linear                                      layers/embed_head.py:61
+ * y[m, n] = x[m, k] @ W[n, k]^T, bf16 in/out, fp32 accumulate in TMEM, 1 <= m <= 256, n % 128 == 0,
+ * k % 64 == 0.  W is passed PRE-PACKED: b2tts_gemm_pack_weight() re-tiles a row-major [n, k] weight
+ * once at load time into [n/128][k/64] tiles of 16 KiB (the K-major SWIZZLE_128B shared-memory image
+ * of a UMMA operand), b2tts_gemm_packed_bytes(n, k) bytes.  B2TTS_PACK_GATE_UP packs a merged
+ * [gate; up] weight (n = 2 * intermediate) so that every 8 consecutive tile rows hold 4 gate features
+ * and the 4 matching up features - required by the SiLU*mul epilogue.
+ * epilogue: B2TTS_GEMM_BIAS      out[m, n]   = bf16(acc + bias)              (bias may be NULL)
+ *           B2TTS_GEMM_RESIDUAL  out[m, n]   = bf16(bf16(acc) + residual)    (qwen3_tts_share.py:171,175;
+ *                                              out may alias residual)
+ *           B2TTS_GEMM_SILU_MUL  out[m, n/2] = silu(bf16(gate)) * bf16(up)   (qwen3_tts_share.py:131-135;
+ *                                              `rounding` as b2tts_silu_and_mul)
+ * splits: K-split = cluster size (1,2,4,8,16; 0 = choose so that tiles * splits fill the SMs); the
+ * partial sums are exchanged through distributed shared memory and added in a fixed order.
+ * pdl != 0 launches with programmatic stream serialization: the weight stream starts while the
+ * previous kernel on the stream is still running (every kernel of this library that is launched
+ * this way executes griddepcontrol.wait before touching its inputs/outputs). */
+#define B2TTS_GEMM_BIAS     0
+#define B2TTS_GEMM_RESIDUAL 1
+#define B2TTS_GEMM_SILU_MUL 2
+#define B2TTS_PACK_PLAIN    0
+#define B2TTS_PACK_GATE_UP  1
+B2TTS_API int    b2tts_gemm_bf16_supported(int m, int n, int k);
+B2TTS_API size_t b2tts_gemm_packed_bytes(int n, int k);
+B2TTS_API int    b2tts_gemm_pack_weight(const void* weight, int64_t weight_row_stride, void* packed,
+                                        int n, int k, int mode, void* stream);
+B2TTS_API int    b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void* w_packed,
+                                 const void* bias, const void* residual, int64_t residual_row_stride,
+                                 void* out, int64_t out_row_stride, int m, int n, int k,
+                                 int epilogue, int rounding, int splits, int pdl, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,14 +57,13 @@ def _load():
         "b2tts_gather_rows": (I, [P, L, I, P, P, P, L, I, I, P]),
         "b2tts_codec_embed_sum": (I, [P, P, L, P, L, P, L, P, I, I, I, P]),
         "b2tts_decode_layout": (I, [P, P, I, I, I, I, P, P, P, I, P]),
-        "b2tts_gemm_bf16_workspace_bytes": (Z, [I, I, I]),
         "b2tts_gemm_bf16_supported": (I, [I, I, I]),
-        "b2tts_gemm_bf16": (I, [P, L, P, P, P, L, I, I, I, P, Z, P]),
+        "b2tts_gemm_packed_bytes": (Z, [I, I]),
+        "b2tts_gemm_pack_weight": (I, [P, L, P, I, I, I, P]),
+        "b2tts_gemm_bf16": (I, [P, L, P, P, P, L, P, L, I, I, I, I, I, I, I, P]),
     }
     for name, (res, args) in sig.items():
         if not hasattr(lib, name):
-            if name.startswith("b2tts_gemm"):
-                continue
             raise NativeLibraryError(f"{path} does not export {name}; rebuild the library")
         fn = getattr(lib, name)
         fn.restype = res
@@ -316,8 +315,13 @@ def decode_layout(seq_lens, block_table, page_size, position_offset, advance, po
 
 
 # ------------------------------------------------------------------------------------------ a7
+GEMM_BIAS, GEMM_RESIDUAL, GEMM_SILU_MUL = 0, 1, 2
+PACK_PLAIN, PACK_GATE_UP = 0, 1
+GEMM_MAX_M = 256
+
+
 def has_gemm() -> bool:
-    return hasattr(_load(), "b2tts_gemm_bf16")
+    return True
 
 
 def launch_count() -> int:
@@ -333,22 +337,40 @@ def device_info():
 
 
 def gemm_supported(m: int, n: int, k: int) -> bool:
-    return has_gemm() and bool(_load().b2tts_gemm_bf16_supported(int(m), int(n), int(k)))
+    return bool(_load().b2tts_gemm_bf16_supported(int(m), int(n), int(k)))
 
 
-def gemm_bf16(x, weight, bias=None, out=None, workspace_fn=None):
-    """y[M,N] = x[M,K] @ weight[N,K]^T (+ bias[N]); bf16 in/out, fp32 accumulate."""
-    _cuda(x, BF16, "x"); _cuda(weight, BF16, "weight")
+def gemm_pack_weight(weight, mode=PACK_PLAIN):
+    """Re-tile a row-major bf16 weight [n, k] into the UMMA operand image the GEMM streams
+    (``b2tts_gemm_pack_weight``).  Returns a uint8 tensor of n*k*2 bytes."""
+    _cuda(weight, BF16, "weight")
+    n, k = weight.shape
+    if weight.stride(1) != 1:
+        weight = weight.contiguous()
+    nbytes = int(_load().b2tts_gemm_packed_bytes(n, k))
+    if nbytes == 0:
+        raise RuntimeError(f"libb200tts: gemm_pack_weight: n={n} must be a multiple of 128 and k={k} of 64")
+    packed = torch.empty(nbytes, dtype=torch.uint8, device=weight.device)
+    _check(_load().b2tts_gemm_pack_weight(weight.data_ptr(), weight.stride(0), packed.data_ptr(), n, k, int(mode),
+                                          _stream()), "gemm_pack_weight")
+    return packed
+
+
+def gemm_bf16(x, packed, n, bias=None, residual=None, epilogue=GEMM_BIAS, rounding=ROUND_EAGER, out=None,
+              splits=0, pdl=False):
+    """y = epilogue(x[M,K] @ W[N,K]^T) with W pre-packed by ``gemm_pack_weight``; bf16 in/out, fp32
+    accumulation in TMEM.  GEMM_SILU_MUL returns [M, N/2]; GEMM_RESIDUAL may write in place (out=residual)."""
+    _cuda(x, BF16, "x")
     m, k = x.shape
-    n = weight.shape[0]
     if x.stride(1) != 1:
         x = x.contiguous()
+    cols = n // 2 if epilogue == GEMM_SILU_MUL else n
     if out is None:
-        out = torch.empty(m, n, dtype=BF16, device=x.device)
-    need = int(_load().b2tts_gemm_bf16_workspace_bytes(m, n, k))
-    ws = None
-    if need:
-        ws = workspace_fn(x.device, need) if workspace_fn else torch.empty(need, dtype=torch.uint8, device=x.device)
-    _check(_load().b2tts_gemm_bf16(x.data_ptr(), x.stride(0), weight.data_ptr(), _ptr(bias), out.data_ptr(),
-                                   out.stride(0), m, n, k, _ptr(ws), need, _stream()), "gemm_bf16")
+        out = torch.empty(m, cols, dtype=BF16, device=x.device)
+    if residual is not None:
+        _cuda(residual, BF16, "residual")
+    _check(_load().b2tts_gemm_bf16(x.data_ptr(), x.stride(0), packed.data_ptr(), _ptr(bias), _ptr(residual),
+                                   residual.stride(0) if residual is not None else 0, out.data_ptr(), out.stride(0),
+                                   m, n, k, int(epilogue), int(rounding), int(splits), int(bool(pdl)), _stream()),
+           "gemm_bf16")
     return out

@@ -1,0 +1,149 @@
+"""GPU parity of the weight-streaming tcgen05 GEMM (b2tts_gemm_bf16) through the C ABI.
+
+Reference semantics: ``F.linear`` (layers/linear.py:72-73,149-153) in bf16 with fp32 accumulation; the
+fused epilogues restate ``residual + hidden`` (models/qwen3_tts_share.py:171,175) and
+``act_fn(gate) * up`` (models/qwen3_tts_share.py:131-135).  Tolerance: logits/projections within 2e-2
+relative (north_star); in practice the only difference from an fp64 contraction is the fp32 summation
+order, so the bound used here is one bf16 ulp on almost every element."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+BF16 = torch.bfloat16
+
+
+def _ref_linear(x, w, bias=None):
+    y = x.double() @ w.double().t()
+    if bias is not None:
+        y = y + bias.double()
+    return y
+
+
+def _check(got, want64, what, max_rel=2e-2):
+    want = want64.to(BF16).float()
+    err = (got.float() - want64.float()).abs().max().item()
+    scale = want64.abs().max().item() + 1e-12
+    assert err / scale <= max_rel, f"{what}: max rel err {err / scale:.3e}"
+    # bf16 rounding of an fp32 sum: at most ~1 ulp away from the rounded fp64 result
+    ulp = (got.float() - want).abs() / (want.abs().clamp_min(1e-3) * 2 ** -8)
+    frac_bad = (ulp > 1.01).float().mean().item()
+    assert frac_bad < 2e-3, f"{what}: {frac_bad:.4f} of elements differ by more than one bf16 ulp"
+
+
+SHAPES = [  # (n, k): every projection of the 1.7B talker and the code predictor
+    (4096, 2048), (2048, 2048), (2048, 6144), (3072, 2048),
+    (1024, 2048), (4096, 1024), (1024, 3072), (2048, 1024),
+]
+
+
+@pytest.mark.parametrize("n,k", SHAPES)
+@pytest.mark.parametrize("m", [1, 8, 64])
+def test_gemm_plain(native, m, n, k):
+    g = torch.Generator(device="cuda").manual_seed(m * 7 + n + k)
+    x = torch.randn(m, k, device="cuda", generator=g).to(BF16)
+    w = (torch.randn(n, k, device="cuda", generator=g) * 0.05).to(BF16)
+    packed = native.gemm_pack_weight(w)
+    y = native.gemm_bf16(x, packed, n)
+    _check(y, _ref_linear(x, w), f"gemm m={m} n={n} k={k}")
+
+
+@pytest.mark.parametrize("m", [3, 17, 100, 128, 200, 256])
+def test_gemm_ragged_m_and_bias(native, m):
+    n, k = 1024, 2048
+    g = torch.Generator(device="cuda").manual_seed(m)
+    x = torch.randn(m, k, device="cuda", generator=g).to(BF16)
+    w = (torch.randn(n, k, device="cuda", generator=g) * 0.05).to(BF16)
+    b = torch.randn(n, device="cuda", generator=g).to(BF16)
+    packed = native.gemm_pack_weight(w)
+    y = native.gemm_bf16(x, packed, n, bias=b)
+    _check(y, _ref_linear(x, w, b), f"gemm+bias m={m}")
+
+
+@pytest.mark.parametrize("splits", [1, 2, 4, 8, 16])
+def test_gemm_every_cluster_size_is_deterministic(native, splits):
+    m, n, k = 64, 1024, 2048
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(m, k, device="cuda", generator=g).to(BF16)
+    w = (torch.randn(n, k, device="cuda", generator=g) * 0.05).to(BF16)
+    packed = native.gemm_pack_weight(w)
+    y1 = native.gemm_bf16(x, packed, n, splits=splits)
+    y2 = native.gemm_bf16(x, packed, n, splits=splits)
+    assert torch.equal(y1, y2)
+    _check(y1, _ref_linear(x, w), f"gemm splits={splits}")
+
+
+def test_gemm_strided_input_and_pdl_flag(native):
+    m, n, k = 32, 2048, 1024
+    g = torch.Generator(device="cuda").manual_seed(9)
+    big = torch.randn(m, k + 64, device="cuda", generator=g).to(BF16)
+    x = big[:, 64:]                                            # row stride k+64, 16-byte aligned
+    w = (torch.randn(n, k, device="cuda", generator=g) * 0.05).to(BF16)
+    packed = native.gemm_pack_weight(w)
+    y = native.gemm_bf16(x, packed, n, pdl=True)
+    _check(y, _ref_linear(x, w), "gemm strided + pdl")
+
+
+def test_gemm_residual_epilogue_matches_reference_rounding(native):
+    """bf16(residual + bf16(x W^T)) - the decoder layer's un-fused add (qwen3_tts_share.py:171,175)."""
+    m, n, k = 64, 2048, 6144
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randn(m, k, device="cuda", generator=g).to(BF16)
+    w = (torch.randn(n, k, device="cuda", generator=g) * 0.02).to(BF16)
+    res = torch.randn(m, n, device="cuda", generator=g).to(BF16)
+    packed = native.gemm_pack_weight(w)
+    plain = native.gemm_bf16(x, packed, n)
+    want = res + plain                                          # bf16 add of the rounded projection
+    got = native.gemm_bf16(x, packed, n, residual=res, epilogue=native.GEMM_RESIDUAL)
+    assert torch.equal(got, want)
+    inplace = res.clone()
+    native.gemm_bf16(x, packed, n, residual=inplace, epilogue=native.GEMM_RESIDUAL, out=inplace)
+    assert torch.equal(inplace, want)
+
+
+@pytest.mark.parametrize("rounding", [0, 1])
+def test_gemm_silu_mul_epilogue_equals_separate_kernels(native, rounding):
+    """gate_up GEMM + SiLU*mul in one launch == GEMM, then b2tts_silu_and_mul on its bf16 output."""
+    m, inter, k = 64, 3072, 1024
+    g = torch.Generator(device="cuda").manual_seed(4)
+    x = torch.randn(m, k, device="cuda", generator=g).to(BF16)
+    w = (torch.randn(2 * inter, k, device="cuda", generator=g) * 0.05).to(BF16)     # [gate; up]
+    plain = native.gemm_bf16(x, native.gemm_pack_weight(w), 2 * inter)
+    want = native.silu_and_mul(plain[:, :inter], plain[:, inter:], rounding=rounding)
+    got = native.gemm_bf16(x, native.gemm_pack_weight(w, native.PACK_GATE_UP), 2 * inter,
+                           epilogue=native.GEMM_SILU_MUL, rounding=rounding)
+    assert got.shape == (m, inter)
+    assert torch.equal(got, want)
+
+
+def test_gemm_linearity_at_full_size(native):
+    """Size-independent property at the largest projection (gate_up of the 1.7B talker, M=256):
+    the K-split partials add up - y(x1) + y(x2) == y(x1 + x2) when every product is exact."""
+    m, n, k = 256, 12288, 2048
+    g = torch.Generator(device="cuda").manual_seed(8)
+    # small integers: every product and partial sum is exact in fp32 and in bf16 output range
+    x1 = torch.randint(-2, 3, (m, k), device="cuda", generator=g).to(BF16)
+    x2 = torch.randint(-2, 3, (m, k), device="cuda", generator=g).to(BF16)
+    w = torch.randint(-1, 2, (n, k), device="cuda", generator=g).to(BF16)
+    w[:, ::2] = 0                                              # keep |y| < 256 * ... exactly representable
+    w[:, 1::4] = 0
+    packed = native.gemm_pack_weight(w)
+    y1 = native.gemm_bf16(x1, packed, n).float()
+    y2 = native.gemm_bf16(x2, packed, n).float()
+    y12 = native.gemm_bf16(x1 + x2, packed, n).float()
+    want = (x1.float() @ w.float().t())
+    assert want.abs().max() < 256 * 8
+    exact = want.to(BF16).float() == want
+    assert torch.equal(y1[exact], want[exact])
+    both = exact & ((y1 + y2).to(BF16).float() == (y1 + y2))
+    assert torch.equal(y12[both], (y1 + y2)[both])
+
+
+def test_gemm_argument_errors(native):
+    x = torch.zeros(4, 100, device="cuda", dtype=BF16)
+    assert not native.gemm_supported(4, 128, 100)
+    assert not native.gemm_supported(300, 128, 64)
+    with pytest.raises(RuntimeError):
+        native.gemm_pack_weight(torch.zeros(100, 64, device="cuda", dtype=BF16))
+    w = native.gemm_pack_weight(torch.zeros(128, 128, device="cuda", dtype=BF16))
+    with pytest.raises(RuntimeError):
+        native.gemm_bf16(x, w, 128)

@@ -70,12 +70,59 @@ def attn_case(b, l, ragged=False, page=256, kvh=8, h=16, hd=128):
                       "alg_bytes": alg, "GBps": round(gbs, 1), "frac_measured_peak": round(gbs / peaks(), 4)}))
 
 
+def gemm_case(m, n, k, splits=0, pdl=False, epilogue=0, chain=16):
+    """`chain` GEMMs back to back over DIFFERENT weights (a stack of layers: cold weights, > L2 in
+    total), timed as one CUDA graph so that launch gaps are what a decode step sees."""
+    ncopies = max(chain, int(300e6 // (n * k * 2)) + 1)
+    ws = [(torch.randn(n, k, device=DEV, dtype=torch.float32) * 0.05).to(BF16) for _ in range(ncopies)]
+    packed = [nat.gemm_pack_weight(w, nat.PACK_GATE_UP if epilogue == 2 else nat.PACK_PLAIN) for w in ws]
+    x = torch.randn(m, k, device=DEV, dtype=BF16)
+    res = torch.randn(m, n, device=DEV, dtype=BF16) if epilogue == 1 else None
+    out = torch.empty(m, n // 2 if epilogue == 2 else n, device=DEV, dtype=BF16)
+    rows = []
+    for impl in ("ours", "cublas"):
+        def body(i0):
+            for j in range(chain):
+                i = (i0 * chain + j) % ncopies
+                if impl == "ours":
+                    nat.gemm_bf16(x, packed[i], n, residual=res, epilogue=epilogue, out=out, splits=splits, pdl=pdl)
+                else:
+                    torch.nn.functional.linear(x, ws[i])
+        body(0)
+        torch.cuda.synchronize()
+        graphs = []
+        for i0 in range(max(1, ncopies // chain)):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                body(i0)
+            graphs.append(g)
+        ms = time_ms(lambda i: graphs[i % len(graphs)].replay()) / chain
+        alg = float(n * k * 2 + m * k * 2 + m * n * 2)
+        rows.append((impl, ms, alg / ms / 1e6))
+    (_, ms_o, gb_o), (_, ms_c, gb_c) = rows
+    print(json.dumps({"kernel": "gemm_bf16", "M": m, "N": n, "K": k, "splits": splits, "pdl": pdl, "epilogue": epilogue,
+                      "us": round(ms_o * 1e3, 2), "GBps": round(gb_o, 1), "frac_measured_peak": round(gb_o / peaks(), 4),
+                      "cublas_us": round(ms_c * 1e3, 2), "cublas_GBps": round(gb_c, 1)}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("what")
     ap.add_argument("--cases", default="1:512,8:512,64:512,64:1024,256:512,512:600,8:4352,64:4096")
     ap.add_argument("--ragged", action="store_true")
+    ap.add_argument("--gemm-cases", default="64:4096:2048,64:2048:2048,64:12288:2048,64:2048:6144,64:4096:1024,"
+                                            "64:1024:2048,64:6144:1024,64:1024:3072,64:2048:1024,1:4096:2048,8:4096:2048,"
+                                            "256:4096:2048")
+    ap.add_argument("--splits", default="0")
+    ap.add_argument("--pdl", type=int, default=1)
     a = ap.parse_args()
+    if a.what == "gemm":
+        for c in a.gemm_cases.split(","):
+            m, n, k = map(int, c.split(":"))
+            for s_ in [int(v) for v in a.splits.split(",")]:
+                if s_ and (s_ > k // 64):
+                    continue
+                gemm_case(m, n, k, splits=s_, pdl=bool(a.pdl))
     if a.what == "attn":
         for c in a.cases.split(","):
             b, l = map(int, c.split(":"))
