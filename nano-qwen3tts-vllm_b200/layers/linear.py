@@ -12,16 +12,31 @@ from torch import nn
 
 from .. import _native as nat
 
-GEMM_NATIVE_MAX_M = 256
-_ws = {}
+GEMM_NATIVE_MAX_M = nat.GEMM_MAX_M
+PDL = True                      # programmatic dependent launch of the native GEMM (weight stream starts early)
+_packed: dict = {}
 
 
-def _workspace(dev, nbytes):
-    w = _ws.get(dev)
-    if w is None or w.numel() < nbytes:
-        w = torch.empty(max(nbytes, 1 << 22), dtype=torch.uint8, device=dev)
-        _ws[dev] = w
-    return w
+def packed_weight(weight: torch.Tensor, mode: int = nat.PACK_PLAIN) -> torch.Tensor:
+    """The UMMA operand image of ``weight`` [out, in] (``b2tts_gemm_pack_weight``), built once per weight
+    (again if the weight was modified in place) and cached by storage address.  Packing allocates, so
+    the first call for a weight must happen outside CUDA-graph capture (warm-up runs do that)."""
+    key = (weight.data_ptr(), tuple(weight.shape), mode)
+    try:
+        ver = weight._version
+    except RuntimeError:            # inference tensors carry no version counter
+        ver = -1
+    ent = _packed.get(key)
+    if ent is None or ent[0] != ver:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("libb200tts: weight packed for the first time under graph capture; run a warm-up first")
+        ent = (ver, nat.gemm_pack_weight(weight, mode))
+        _packed[key] = ent
+    return ent[1]
+
+
+def native_ok(m: int, n: int, k: int) -> bool:
+    return 1 <= m <= GEMM_NATIVE_MAX_M and nat.gemm_supported(m, n, k)
 
 
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = None,
@@ -30,14 +45,38 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = No
         raise RuntimeError("libb200tts: linear() needs CUDA tensors (there is no CPU path)")
     x2 = x.reshape(-1, x.shape[-1])
     m, n = x2.shape[0], weight.shape[0]
-    if nat.has_gemm() and m <= GEMM_NATIVE_MAX_M and nat.gemm_supported(m, n, x2.shape[1]):
-        y = nat.gemm_bf16(x2, weight, bias, out=out, workspace_fn=_workspace)
+    if native_ok(m, n, x2.shape[1]):
+        y = nat.gemm_bf16(x2, packed_weight(weight), n, bias=bias, out=out, pdl=PDL)
     else:
         y = torch.nn.functional.linear(x2, weight, bias)
         if out is not None:
             out.copy_(y)
             y = out
     return y.view(*x.shape[:-1], n)
+
+
+def linear_residual(x: torch.Tensor, weight: torch.Tensor, residual: torch.Tensor,
+                    out: torch.Tensor | None = None) -> torch.Tensor:
+    """bf16(residual + bf16(x W^T)) - the projection followed by the decoder layer's residual add
+    (models/qwen3_tts_share.py:171,175 of the reference) in the GEMM epilogue.  ``out`` may be ``residual``."""
+    m, n = x.shape[0], weight.shape[0]
+    if native_ok(m, n, x.shape[1]):
+        return nat.gemm_bf16(x, packed_weight(weight), n, residual=residual, epilogue=nat.GEMM_RESIDUAL, out=out, pdl=PDL)
+    y = torch.nn.functional.linear(x, weight)
+    if out is None:
+        return residual + y
+    return torch.add(residual, y, out=out)
+
+
+def linear_silu_mul(x: torch.Tensor, gate_up_weight: torch.Tensor, rounding: int = nat.ROUND_EAGER) -> torch.Tensor:
+    """silu(x Wg^T) * (x Wu^T) over the merged [gate; up] weight (qwen3_tts_share.py:131-135) with the
+    activation in the GEMM epilogue: the [M, 2I] intermediate never reaches HBM."""
+    m, n = x.shape[0], gate_up_weight.shape[0]
+    if native_ok(m, n, x.shape[1]):
+        return nat.gemm_bf16(x, packed_weight(gate_up_weight, nat.PACK_GATE_UP), n, epilogue=nat.GEMM_SILU_MUL,
+                             rounding=rounding, pdl=PDL)
+    gu = torch.nn.functional.linear(x, gate_up_weight)
+    return nat.silu_and_mul(gu[:, :n // 2], gu[:, n // 2:], rounding)
 
 
 class LinearBase(nn.Module):

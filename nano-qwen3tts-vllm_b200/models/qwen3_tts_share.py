@@ -25,7 +25,8 @@ from ..config import StackConfig
 from ..layers.activation import SiluAndMul
 from ..layers.attention import Attention
 from ..layers.layernorm import Qwen3TTSRMSNorm
-from ..layers.linear import MergedColumnParallelLinear, QKVParallelLinear, RowParallelLinear
+from ..layers.linear import (GEMM_NATIVE_MAX_M, MergedColumnParallelLinear, QKVParallelLinear, RowParallelLinear,
+                             linear_residual, linear_silu_mul)
 from ..layers.rotary_embedding import get_rope
 from ..utils.context import get_context
 
@@ -50,6 +51,11 @@ class Qwen3TTSAttention(nn.Module):
         self.attn = Attention(self.num_heads, self.head_dim, self.scaling, self.num_kv_heads)
 
     def forward(self, positions: torch.Tensor, hidden_states: torch.Tensor) -> torch.Tensor:
+        o = self.attend(positions, hidden_states)
+        return self.o_proj(o)
+
+    def attend(self, positions: torch.Tensor, hidden_states: torch.Tensor) -> torch.Tensor:
+        """Everything up to (not including) o_proj: [n, heads * head_dim]."""
         ctx = get_context()
         n = hidden_states.shape[0]
         qkv = self.qkv_proj(hidden_states)
@@ -66,7 +72,7 @@ class Qwen3TTSAttention(nn.Module):
             k_cache=self.attn.k_cache if have_cache else None, v_cache=self.attn.v_cache if have_cache else None,
             want_k_out=packed_kv or not have_cache, rounding=self.rounding)
         o = self.attn.attend(q_rot, k_rot, v)
-        return self.o_proj(o.view(n, self.q_size))
+        return o.view(n, self.q_size)
 
 
 class Qwen3TTSTalkerTextMLP(nn.Module):
@@ -106,6 +112,19 @@ class Qwen3TTSDecoderLayer(nn.Module):
         hidden_states = self.mlp(hidden_states)
         return hidden_states, residual
 
+    def forward_decode(self, positions: torch.Tensor, residual: torch.Tensor, in_place: bool) -> torch.Tensor:
+        """The same layer on the residual stream alone, for n <= GEMM_NATIVE_MAX_M rows: the two residual
+        adds ride in the o_proj / down_proj GEMM epilogues and SiLU*mul in the gate_up epilogue, so a
+        layer is 8 launches (norm, qkv, qk-norm+rope+kv-write, attention, o+res, norm, gate_up+act,
+        down+res).  Rounding points are unchanged: bf16(residual + bf16(x W^T)), then the norm.
+        ``in_place`` False keeps the caller's tensor (the first layer's input embeddings) intact."""
+        h = nat.rmsnorm(residual, self.input_layernorm.weight, self.eps, self.rounding)
+        o = self.self_attn.attend(positions, h)
+        residual = linear_residual(o, self.self_attn.o_proj.weight, residual, out=residual if in_place else None)
+        h = nat.rmsnorm(residual, self.post_attention_layernorm.weight, self.eps, self.rounding)
+        act = linear_silu_mul(h, self.mlp.gate_up_proj.weight, self.rounding)
+        return linear_residual(act, self.mlp.down_proj.weight, residual, out=residual)
+
 
 class DecoderStack(nn.Module):
     """``layers`` + final ``norm`` (Qwen3TTSTalkerModel / Qwen3TTSCodePredictorModel bodies)."""
@@ -118,6 +137,11 @@ class DecoderStack(nn.Module):
         self.norm = Qwen3TTSRMSNorm(config.hidden_size, eps=config.rms_norm_eps, rounding=rounding)
 
     def run_layers(self, input_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
+        if input_embeds.shape[0] <= GEMM_NATIVE_MAX_M:
+            residual = input_embeds
+            for i, layer in enumerate(self.layers):
+                residual = layer.forward_decode(positions, residual, in_place=i > 0)
+            return nat.rmsnorm(residual, self.norm.weight, self.config.rms_norm_eps, self.rounding)
         hidden_states, residual = input_embeds, None
         for layer in self.layers:
             hidden_states, residual = layer(positions, hidden_states, residual)
