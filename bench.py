@@ -372,11 +372,8 @@ def main():
     mc, talker, predictor = build_engines(a.model, a.streams, total_frames + a.e2e_steps + 8, device)
     sampler = ClockSampler(local) if rank == 0 else None
     loop, ms, lib_per_frame, clocks = run_device_loop(talker, predictor, mc, a.streams, a.steps, a.warmup, sampler, barrier)
-    if dist:
-        t = torch.tensor([ms], device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    frames = a.streams * a.steps * world
+    from nano_qwen3tts_vllm_b200 import replicas
+    frames, ms = replicas.aggregate(a.streams * a.steps, ms, dist, device)     # sum of units, max of time over ranks
     value = frames / (ms / 1e3)
     ms_per_step = ms / a.steps
 
@@ -403,7 +400,7 @@ def main():
                 "rtf_per_stream": round(ms_per_step / 1e3 * FRAME_HZ, 5),
                 "roofline": roofline, "step_roofline": step_roof,
                 "gpu_launches": int(lib_per_frame * a.steps),
-                "launches_per_step": {"libb200tts": int(lib_per_frame), "note": "GEMMs (cuBLASLt via torch), exponential_ noise and small copies are extra"}}
+                "launches_per_step": {"libb200tts": int(lib_per_frame), "note": "includes the tcgen05 GEMMs; exponential_ noise and small torch copies are extra"}}
     # ---- end to end through the step API with host buffers
     if not a.no_e2e:
         e2e_fps, h2d, d2h, _ = run_e2e(talker, predictor, mc, a.streams, a.e2e_steps)
