@@ -193,7 +193,7 @@ B2TTS_API int b2tts_decode_layout(int32_t* seq_lens, const int32_t* block_table,
  *   (q/k/v and gate/up as ONE GEMM each over a merged weight: models/qwen3_tts_share.py:85-87, 126-134),
  *   nn.Linear small_to_mtp_projection / lm_head[g]                 models/qwen3_tts_predictor.py:54-61,
  *   ParallelLMHead's F.linear                                      layers/embed_head.py:61
- * y[m, n] = x[m, k] @ W[n, k]^T, bf16 in/out, fp32 accumulate in TMEM, 1 <= m <= 256, n % 128 == 0,
+ * y[m, n] = x[m, k] @ W[n, k]^T, bf16 in/out, fp32 accumulate in TMEM, 1 <= m <= 128, n % 128 == 0,
  * k % 64 == 0.  W is passed PRE-PACKED: b2tts_gemm_pack_weight() re-tiles a row-major [n, k] weight
  * once at load time into [n/128][k/64] tiles of 16 KiB (the K-major SWIZZLE_128B shared-memory image
  * of a UMMA operand), b2tts_gemm_packed_bytes(n, k) bytes.  B2TTS_PACK_GATE_UP packs a merged
@@ -222,6 +222,26 @@ B2TTS_API int    b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void
                                  const void* bias, const void* residual, int64_t residual_row_stride,
                                  void* out, int64_t out_row_stride, int m, int n, int k,
                                  int epilogue, int rounding, int splits, int pdl, void* stream);
+
+
+/* ---- a4 fused into a7: input RMSNorm in the GEMM's x producers, row sums of squares out of its epilogue ----
+ * replaces `hidden = layernorm(residual)` followed by the projection that reads it
+ *                                          models/qwen3_tts_share.py:166-167,172-174, layers/layernorm.py:18-27
+ * As b2tts_gemm_bf16, plus:
+ *   norm_weight != NULL: x is the residual stream; the GEMM multiplies norm(x)[m, k] =
+ *     rounding(x[m, k] * rstd[m], norm_weight[k]) (same rounding points as b2tts_rmsnorm) with
+ *     rstd[m] = 1/sqrt(sum_j ssq_in[m, j] / k + eps), j < ssq_in_slots summed in a fixed order.
+ *   ssq_out != NULL (bias / residual epilogues): ssq_out[m, slot] = sum of squares of the bf16 values this
+ *     call stored in out[m, :] over slot's feature slice; slots per row = b2tts_gemm_ssq_slots(n, k, splits).
+ *     The next b2tts_gemm_norm_bf16 over `out` takes it as ssq_in: the decoder layer's two norm launches
+ *     disappear, and the normalised activations never reach HBM. */
+B2TTS_API int    b2tts_gemm_ssq_slots(int n, int k, int splits);
+B2TTS_API int    b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const void* w_packed,
+                                      const void* bias, const void* residual, int64_t residual_row_stride,
+                                      void* out, int64_t out_row_stride, int m, int n, int k,
+                                      int epilogue, int rounding, int splits, int pdl,
+                                      const void* norm_weight, const float* ssq_in, int ssq_in_slots, float eps,
+                                      float* ssq_out, void* stream);
 
 #ifdef __cplusplus
 }

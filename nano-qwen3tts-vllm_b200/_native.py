@@ -61,6 +61,8 @@ def _load():
         "b2tts_gemm_packed_bytes": (Z, [I, I]),
         "b2tts_gemm_pack_weight": (I, [P, L, P, I, I, I, P]),
         "b2tts_gemm_bf16": (I, [P, L, P, P, P, L, P, L, I, I, I, I, I, I, I, P]),
+        "b2tts_gemm_ssq_slots": (I, [I, I, I]),
+        "b2tts_gemm_norm_bf16": (I, [P, L, P, P, P, L, P, L, I, I, I, I, I, I, I, P, P, I, F, P, P]),
     }
     for name, (res, args) in sig.items():
         if not hasattr(lib, name):
@@ -317,7 +319,7 @@ def decode_layout(seq_lens, block_table, page_size, position_offset, advance, po
 # ------------------------------------------------------------------------------------------ a7
 GEMM_BIAS, GEMM_RESIDUAL, GEMM_SILU_MUL = 0, 1, 2
 PACK_PLAIN, PACK_GATE_UP = 0, 1
-GEMM_MAX_M = 256
+GEMM_MAX_M = 128
 
 
 def has_gemm() -> bool:
@@ -356,10 +358,16 @@ def gemm_pack_weight(weight, mode=PACK_PLAIN):
     return packed
 
 
+def gemm_ssq_slots(n: int, k: int, splits: int = 0) -> int:
+    return int(_load().b2tts_gemm_ssq_slots(int(n), int(k), int(splits)))
+
+
 def gemm_bf16(x, packed, n, bias=None, residual=None, epilogue=GEMM_BIAS, rounding=ROUND_EAGER, out=None,
-              splits=0, pdl=False):
+              splits=0, pdl=False, norm_weight=None, ssq_in=None, eps=1e-6, ssq_out=None):
     """y = epilogue(x[M,K] @ W[N,K]^T) with W pre-packed by ``gemm_pack_weight``; bf16 in/out, fp32
-    accumulation in TMEM.  GEMM_SILU_MUL returns [M, N/2]; GEMM_RESIDUAL may write in place (out=residual)."""
+    accumulation in TMEM.  GEMM_SILU_MUL returns [M, N/2]; GEMM_RESIDUAL may write in place (out=residual).
+    ``norm_weight`` + ``ssq_in`` [M, slots] fp32: x is normalised (RMSNorm) while it is staged.
+    ``ssq_out`` [M, gemm_ssq_slots(n, k, splits)] fp32 receives the row sums of squares of the output."""
     _cuda(x, BF16, "x")
     m, k = x.shape
     if x.stride(1) != 1:
@@ -369,8 +377,26 @@ def gemm_bf16(x, packed, n, bias=None, residual=None, epilogue=GEMM_BIAS, roundi
         out = torch.empty(m, cols, dtype=BF16, device=x.device)
     if residual is not None:
         _cuda(residual, BF16, "residual")
-    _check(_load().b2tts_gemm_bf16(x.data_ptr(), x.stride(0), packed.data_ptr(), _ptr(bias), _ptr(residual),
-                                   residual.stride(0) if residual is not None else 0, out.data_ptr(), out.stride(0),
-                                   m, n, k, int(epilogue), int(rounding), int(splits), int(bool(pdl)), _stream()),
-           "gemm_bf16")
+    res_stride = residual.stride(0) if residual is not None else 0
+    if norm_weight is None and ssq_out is None:
+        _check(_load().b2tts_gemm_bf16(x.data_ptr(), x.stride(0), packed.data_ptr(), _ptr(bias), _ptr(residual),
+                                       res_stride, out.data_ptr(), out.stride(0),
+                                       m, n, k, int(epilogue), int(rounding), int(splits), int(bool(pdl)), _stream()),
+               "gemm_bf16")
+        return out
+    slots_in = 0
+    if norm_weight is not None:
+        _cuda(norm_weight, BF16, "norm_weight"); _cuda(ssq_in, torch.float32, "ssq_in")
+        if ssq_in.dim() != 2 or ssq_in.shape[0] < m or not ssq_in.is_contiguous():
+            raise ValueError("ssq_in must be a contiguous [>=M, slots] fp32 tensor")
+        slots_in = ssq_in.shape[1]
+    if ssq_out is not None:
+        _cuda(ssq_out, torch.float32, "ssq_out")
+        need = gemm_ssq_slots(n, k, splits)
+        if ssq_out.dim() != 2 or ssq_out.shape[0] < m or ssq_out.shape[1] != need or not ssq_out.is_contiguous():
+            raise ValueError(f"ssq_out must be a contiguous [>=M, {need}] fp32 tensor")
+    _check(_load().b2tts_gemm_norm_bf16(x.data_ptr(), x.stride(0), packed.data_ptr(), _ptr(bias), _ptr(residual),
+                                        res_stride, out.data_ptr(), out.stride(0), m, n, k, int(epilogue),
+                                        int(rounding), int(splits), int(bool(pdl)), _ptr(norm_weight), _ptr(ssq_in),
+                                        slots_in, float(eps), _ptr(ssq_out), _stream()), "gemm_norm_bf16")
     return out

@@ -61,6 +61,13 @@ __device__ __forceinline__ void stg_na_v4(void* p, uint4 v) {        // streamin
                :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every kernel of this library may be launched with programmatic stream serialization: it must
+// execute pdl_wait() before it reads anything a previous kernel wrote or writes anything a previous
+// kernel may still read; pdl_launch() lets the next kernel's CTAs start their prologue early.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------- warp / block reductions
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -26,16 +26,20 @@
 //     (qwen3_tts_share.py:171,175) or SiLU(gate)*up (qwen3_tts_share.py:131-135);
 //   * programmatic dependent launch: the W stream starts before the previous kernel has finished
 //     (weights do not depend on it); only the x producers / epilogue execute griddepcontrol.wait.
+#include <cuda.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b2 {
 
 constexpr int G_BN = 128;                       // output features per CTA = UMMA M
 constexpr int G_BK = 64;                        // K per stage = one 128-byte swizzle row of bf16
-constexpr int G_STAGES = 4;
+constexpr int G_STAGES = 4;                    // ring depth the split heuristic assumes
+constexpr int G_MAX_STAGES = 12;
 constexpr int G_THREADS = 192;                  // warp 0: W producer, warp 1: MMA issuer + TMEM owner, warps 2-5: x producers + epilogue
 constexpr int G_WTILE_BYTES = G_BN * G_BK * 2;  // 16 KiB
-constexpr int G_MAX_M = 256;
+constexpr int G_MAX_M = 128;
 
 struct GemmParams {
   const __nv_bfloat16* x;
@@ -53,6 +57,16 @@ struct GemmParams {
   int epilogue;                 // B2TTS_GEMM_*
   int rounding;                 // B2TTS_ROUND_* of the SiLU*mul epilogue
   int tmem_cols;                // power of two >= 32, >= mpad
+  int stages;                   // ring depth (2..4)
+  // fused input RMSNorm: x is the RESIDUAL stream; the x producers stage norm(x) = f(x * rstd[m], w[k])
+  const __nv_bfloat16* norm_w;  // [K] or null
+  const float* ssq_in;          // [M, ssq_in_slots] partial sums of squares of the x rows (fixed-order sum)
+  int ssq_in_slots;
+  float eps;
+  // per-row partial sum of squares of the OUTPUT rows (bias / residual epilogues): [M, n / (128 / splits)]
+  float* ssq_out;
+  unsigned long long* trace;    // debug: 8 globaltimer stamps per CTA (null = off)
+  int ssq_lanes;                // lanes per row when summing ssq_in (power of two, divides ssq_in_slots)
 };
 
 // ---------------------------------------------------------------- tcgen05 / cluster PTX
@@ -104,6 +118,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
+// 16 columns without the wait: several can be in flight, then one tmem_ld_wait()
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t local_addr, uint32_t cta_rank) {
   uint32_t r;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta_rank));
@@ -112,26 +135,78 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t local_addr, uint32_t cta_r
 __device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" :: "r"(addr), "f"(v) : "memory");
 }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// bulk async copy own shared memory -> a peer CTA's shared memory, completing on the peer's mbarrier
+__device__ __forceinline__ void bulk_s2c(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(bar_cluster) : "memory");
+}
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define G_TRACE(slot) do { if (p.trace) p.trace[(blockIdx.y * gridDim.x + blockIdx.x) * 8 + (slot)] = gtimer(); } while (0)
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      :: "r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+
 __device__ __forceinline__ float gsilu_f(float g) { return g / (1.0f + expf(-g)); }   // as elementwise.cu
+
+__device__ __forceinline__ void st_cluster_v4(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void bar_sync_producers() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// fused-norm transform of 8 staged x values: EAGER = bf16(bf16(x*rstd)*w) (layernorm.py:22-27 op by op),
+// FUSED = one rounding (what inductor emits); identical to rmsnorm_kernel's norm_out.
+__device__ __forceinline__ uint4 norm8(uint4 x, uint4 w, float rs, bool eager) {
+  float xf[8], wf[8];
+  xf[0] = bf16lo(x.x); xf[1] = bf16hi(x.x); xf[2] = bf16lo(x.y); xf[3] = bf16hi(x.y);
+  xf[4] = bf16lo(x.z); xf[5] = bf16hi(x.z); xf[6] = bf16lo(x.w); xf[7] = bf16hi(x.w);
+  wf[0] = bf16lo(w.x); wf[1] = bf16hi(w.x); wf[2] = bf16lo(w.y); wf[3] = bf16hi(w.y);
+  wf[4] = bf16lo(w.z); wf[5] = bf16hi(w.z); wf[6] = bf16lo(w.w); wf[7] = bf16hi(w.w);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float t = xf[i] * rs;
+    xf[i] = (eager ? rbf(t) : t) * wf[i];
+  }
+  uint4 o;
+  o.x = pack_bf16(xf[0], xf[1]); o.y = pack_bf16(xf[2], xf[3]);
+  o.z = pack_bf16(xf[4], xf[5]); o.w = pack_bf16(xf[6], xf[7]);
+  return o;
+}
 
 // One GEMM CTA: 128 features x Mpad batch columns over its K range.  NCH = 16-byte x chunks each
 // producer thread stages per k-block (Mpad * 8 / 128).
 template <int NCH>
 __global__ void __launch_bounds__(G_THREADS, 1)
-gemm_stream_kernel(const GemmParams p) {
+gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_x) {
   extern __shared__ uint8_t smem_dyn[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
   const int mpad = p.mpad;
+  const int NS = p.stages;
   const int stage_bytes = G_WTILE_BYTES + mpad * 128;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + G_STAGES * stage_bytes);
-  uint64_t* empty_bar = full_bar + G_STAGES;
-  uint64_t* accum_bar = empty_bar + G_STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+  uint8_t* ring_end = smem + NS * stage_bytes;
+  // receive buffer of the split-K exchange (S > 1): recv[src_rank][feature within my slice][mpad + 4] fp32
+  float* recv = reinterpret_cast<float*>(ring_end);
+  uint8_t* tail = ring_end + (p.splits > 1 ? (mpad + 4) * 512 : 0);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty_bar = full_bar + G_MAX_STAGES;
+  uint64_t* raw_bar = empty_bar + G_MAX_STAGES;    // x tile landed (TMA), before the optional in-place norm
+  uint64_t* accum_bar = raw_bar + G_MAX_STAGES;
+  uint64_t* recv_bar = accum_bar + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(recv_bar + 1);
+  float* rstd_s = reinterpret_cast<float*>(tmem_slot + 2);        // [mpad]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -142,33 +217,54 @@ gemm_stream_kernel(const GemmParams p) {
   const int kb_end = (int)(((int64_t)(rank + 1) * p.kblocks) / S);
   const int nkb = kb_end - kb_begin;
 
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (threadIdx.x == 0) G_TRACE(0);
+  pdl_launch();
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < G_STAGES; ++s) {
+    for (int s = 0; s < NS; ++s) {
       mbar_init(full_bar + s, 1 + 4);           // W producer (expect_tx arrive) + 4 x-producer warps
       mbar_init(empty_bar + s, 1);              // tcgen05.commit
+      mbar_init(raw_bar + s, 1);
     }
     mbar_init(accum_bar, 1);
+    mbar_init(recv_bar, 1);
     mbar_fence_init();
+    if (S > 1) mbar_expect_tx(recv_bar, (uint32_t)((mpad + 4) * 512));   // S slices of (128/S) rows
   }
   if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (S > 1) cluster_arrive();                  // my receive barrier is initialised (waited on before the exchange)
+  if (threadIdx.x == 0) G_TRACE(1);
 
   if (warp == 0) {
-    // =========================== W producer: one 16 KiB bulk copy per k-block, no dependency on
-    // the previous kernel, so it runs ahead of griddepcontrol.wait.
+    // =========================== producer thread.  W: one 16 KiB bulk copy per k-block; it does not
+    // depend on the previous kernel, so the first ring-full is requested BEFORE griddepcontrol.wait.
+    // x: one 2-D tensor-map copy per k-block (SWIZZLE_128B: lands as the UMMA B tile, rows >= M
+    // zero-filled), requested after the wait.  Both go through the TMA unit, so neither the HBM nor
+    // the L2 round trip is ever paid per block by a waiting thread.
     if (lane == 0) {
       const uint8_t* src = p.wp + ((int64_t)tile * p.kblocks + kb_begin) * G_WTILE_BYTES;
-      for (int i = 0; i < nkb; ++i) {
-        const int stage = i % G_STAGES;
-        const uint32_t ph = (i / G_STAGES) & 1;
-        mbar_wait(empty_bar + stage, ph ^ 1);
+      const uint32_t xbytes = (uint32_t)mpad * 128u;
+      const int first = min(nkb, NS);
+      for (int i = 0; i < first; ++i) {
+        mbar_expect_tx(full_bar + i, G_WTILE_BYTES);
+        bulk_g2s(smem + i * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + i);
+      }
+      pdl_wait();
+      for (int i = 0; i < first; ++i) {
+        mbar_expect_tx(raw_bar + i, xbytes);
+        tma_load_2d(smem + i * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, 0, raw_bar + i);
+      }
+      for (int i = first; i < nkb; ++i) {
+        const int stage = i % NS;
+        mbar_wait(empty_bar + stage, ((i / NS) & 1) ^ 1);
         mbar_expect_tx(full_bar + stage, G_WTILE_BYTES);
         bulk_g2s(smem + stage * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + stage);
+        mbar_expect_tx(raw_bar + stage, xbytes);
+        tma_load_2d(smem + stage * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, 0, raw_bar + stage);
       }
     }
     __syncwarp();
@@ -177,8 +273,8 @@ gemm_stream_kernel(const GemmParams p) {
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_bf16(mpad);
       for (int i = 0; i < nkb; ++i) {
-        const int stage = i % G_STAGES;
-        const uint32_t ph = (i / G_STAGES) & 1;
+        const int stage = i % NS;
+        const uint32_t ph = (i / NS) & 1;
         mbar_wait(full_bar + stage, ph);
         tc_fence_after();
         const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
@@ -193,90 +289,146 @@ gemm_stream_kernel(const GemmParams p) {
     }
     __syncwarp();
   } else {
-    // =========================== x producers (128 threads): global (L2) -> swizzled smem
-    asm volatile("griddepcontrol.wait;" ::: "memory");
+    // =========================== x tiles land by TMA; with the fused norm these 4 warps transform the
+    // landed tile in place (shared-memory latency only), then release it to the MMA issuer.
+    pdl_wait();
+    if (threadIdx.x == 64) G_TRACE(2);
     const int tp = threadIdx.x - 64;
-    uint4 cur[NCH], nxt[NCH];
-    auto load = [&](uint4* dst, int kb) {
-      const __nv_bfloat16* base = p.x + (int64_t)(kb_begin + kb) * G_BK;
-#pragma unroll
-      for (int j = 0; j < NCH; ++j) {
-        const int idx = tp + 128 * j;
-        const int r = idx >> 3, c = idx & 7;
-        dst[j] = (r < p.m) ? ldg_v4(base + (int64_t)r * p.x_stride + c * 8) : make_uint4(0, 0, 0, 0);
+    const bool normed = p.norm_w != nullptr;
+    const bool eager = p.rounding == B2TTS_ROUND_EAGER;
+    if (normed) {
+      // rstd[m] from the partial sums of squares the producing kernel left: G lanes per row, each a
+      // contiguous chunk summed in order, then a fixed shuffle tree (deterministic).
+      const int G = p.ssq_lanes, rows_per_pass = 128 / G;
+      const int gl = tp % G, chunk = p.ssq_in_slots / G;
+      for (int r0 = 0; r0 < mpad; r0 += rows_per_pass) {
+        const int r = r0 + tp / G;
+        float sum = 0.f;
+        if (r < p.m) {
+          const float* src = p.ssq_in + (int64_t)r * p.ssq_in_slots + gl * chunk;
+          if ((chunk & 3) == 0) {
+            for (int i = 0; i < chunk; i += 4) {
+              const float4 v = *reinterpret_cast<const float4*>(src + i);
+              sum += v.x; sum += v.y; sum += v.z; sum += v.w;
+            }
+          } else {
+            for (int i = 0; i < chunk; ++i) sum += src[i];
+          }
+        }
+        for (int o = 1; o < G; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if (r < mpad && gl == 0) {
+          const float var = sum / (float)p.k + p.eps;
+          rstd_s[r] = eager ? 1.0f / sqrtf(var) : rsqrtf(var);
+        }
       }
-    };
-    if (nkb > 0) load(cur, 0);
+      bar_sync_producers();
+    }
     for (int i = 0; i < nkb; ++i) {
-      const int stage = i % G_STAGES;
-      const uint32_t ph = (i / G_STAGES) & 1;
-      if (i + 1 < nkb) load(nxt, i + 1);
-      mbar_wait(empty_bar + stage, ph ^ 1);
-      uint8_t* xs = smem + stage * stage_bytes + G_WTILE_BYTES;
+      const int stage = i % NS;
+      const uint32_t ph = (i / NS) & 1;
+      mbar_wait(raw_bar + stage, ph);
+      if (normed) {
+        uint8_t* xs = smem + stage * stage_bytes + G_WTILE_BYTES;
+        const uint4 wv = ldg_v4(p.norm_w + (int64_t)(kb_begin + i) * G_BK + (tp & 7) * 8);
 #pragma unroll
-      for (int j = 0; j < NCH; ++j) {
-        const int idx = tp + 128 * j;
-        const int r = idx >> 3, c = idx & 7;
-        if (r < mpad) *reinterpret_cast<uint4*>(xs + r * 128 + ((c ^ (r & 7)) << 4)) = cur[j];
+        for (int j = 0; j < NCH; ++j) {
+          const int idx = tp + 128 * j;
+          const int r = idx >> 3, c = idx & 7;
+          if (r < p.m) {
+            uint4* cell = reinterpret_cast<uint4*>(xs + r * 128 + ((c ^ (r & 7)) << 4));
+            *cell = norm8(*cell, wv, rstd_s[r], eager);
+          }
+        }
+        fence_proxy_async();
       }
-      fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(full_bar + stage);
-#pragma unroll
-      for (int j = 0; j < NCH; ++j) cur[j] = nxt[j];
+      if (threadIdx.x == 64 && i == 0) G_TRACE(3);
     }
   }
 
   // =========================== all threads: accumulator complete => this CTA's ring is free
   mbar_wait(accum_bar, 0);
   tc_fence_after();
-  if (warp < 2) asm volatile("griddepcontrol.wait;" ::: "memory");   // the epilogue below reads res / writes out
-  if (S > 1) cluster_sync_all();                // every CTA of the cluster is past its MMAs: rings are reusable
+  if (threadIdx.x == 0) G_TRACE(4);
+  if (warp < 2) pdl_wait();                     // the epilogue below reads res / writes out
+  if (S > 1) cluster_wait();                    // (long complete) every peer has initialised its receive barrier
 
-  // reduction buffer red[src_rank][m][feature within owner slice] (fp32) aliases the ring
+  // Split-K exchange.  Every CTA spills its 128 x mpad fp32 partial to a staging area that aliases
+  // its own (now idle) ring, rows = features, padded by 4 floats (conflict-free 16-byte stores, and
+  // the reduce reads it conflict-free with lanes along m).  Feature rows of one owner are contiguous,
+  // so ONE bulk async copy per peer (shared::cta -> shared::cluster through the TMA unit) moves the
+  // slice into the owner's receive buffer recv[src][row][mpad+4] and completes on the OWNER's
+  // mbarrier: no cluster barrier on the critical path, no per-thread remote stores.
   const int rows_own = G_BN / S;
-  float* red = reinterpret_cast<float*>(smem);
+  const int rstride = mpad + 4;
+  float* stg = reinterpret_cast<float*>(smem);
+  const float* red = (S > 1) ? recv : stg;
   if (warp >= 2) {
     const int q = warp & 3;                     // TMEM lane quarter this warp may read
     const int f = q * 32 + lane;                // feature row of the tile held by this thread
-    const int owner = f / rows_own, fo = f - owner * rows_own;
-    const uint32_t local = smem_u32(red + ((int64_t)rank * mpad) * rows_own + fo);
-    const uint32_t dst = (S > 1) ? mapa_u32(local, (uint32_t)owner) : local;
-    for (int c0 = 0; c0 < mpad; c0 += 16) {
-      float v[16];
+    float* row = stg + (int64_t)f * rstride;
+    for (int c0 = 0; c0 < mpad; c0 += 64) {
+      uint32_t v[64];
+      const int nq = min(4, (mpad - c0) >> 4);  // 16-column quarters in this pass
       if (nkb > 0) {
-        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq)
+          if (qq < nq) tmem_ld16_nowait(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c0 + 16 * qq), v + 16 * qq);
+        tmem_ld_wait();
       } else {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) v[j] = 0.f;
+        for (int j = 0; j < 64; ++j) v[j] = 0u;
       }
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const uint32_t a = dst + (uint32_t)((c0 + j) * rows_own * 4);
-        if (S > 1) st_cluster_f32(a, v[j]);
-        else asm volatile("st.shared.f32 [%0], %1;" :: "r"(a), "f"(v[j]) : "memory");
+      for (int qq = 0; qq < 4; ++qq)
+        if (qq < nq) {
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) {
+            const int jj = 16 * qq + j;
+            *reinterpret_cast<uint4*>(row + c0 + jj) = make_uint4(v[jj], v[jj + 1], v[jj + 2], v[jj + 3]);
+          }
+        }
+    }
+    if (S > 1) {
+      fence_proxy_async();                      // generic-proxy stores -> visible to the bulk copies
+      bar_sync_producers();
+      if (threadIdx.x == 64) {
+        const uint32_t chunk = (uint32_t)(rows_own * rstride * 4);
+        const uint32_t recv_local = smem_u32(recv) + (uint32_t)rank * chunk;
+        const uint32_t bar_local = smem_u32(recv_bar);
+        for (int o = 0; o < S; ++o) {
+          const int peer = (rank + o) % S;      // spread the traffic
+          bulk_s2c(mapa_u32(recv_local, (uint32_t)peer), smem_u32(stg) + (uint32_t)peer * chunk, chunk,
+                   mapa_u32(bar_local, (uint32_t)peer));
+        }
       }
     }
   }
   tc_fence_before();
-  if (S > 1) cluster_sync_all(); else __syncthreads();
+  if (S > 1) {
+    mbar_wait(recv_bar, 0);                     // all S slices (own included) have landed
+    cluster_arrive();                           // my receive buffer is complete; peers may retire their staging
+  } else {
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) G_TRACE(6);
 
   // =========================== fixed-order sum of the S partials + fused epilogue.
-  // One item = (batch row m, 8 consecutive features of this CTA's slice).
+  // One item = (batch row m, 8 consecutive features of this CTA's slice); returns the sum of squares
+  // of the 8 bf16 values it stored.
   {
     const int groups = rows_own >> 3;
-    const int items = p.m * groups;
     const int n0 = tile * G_BN + rank * rows_own;
-    for (int it = threadIdx.x; it < items; it += G_THREADS) {
-      const int m = it / groups, g8 = it - m * groups;
+    auto item = [&](int m, int g8) -> float {
       float acc[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+      const int rstride = mpad + 4;
       for (int s = 0; s < S; ++s) {
-        const float4* src = reinterpret_cast<const float4*>(red + ((int64_t)s * mpad + m) * rows_own + g8 * 8);
-        const float4 a = src[0], b = src[1];
-        acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
-        acc[4] += b.x; acc[5] += b.y; acc[6] += b.z; acc[7] += b.w;
+        const float* src = red + ((int64_t)s * rows_own + g8 * 8) * rstride + m;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += src[j * rstride];
       }
       const int n = n0 + g8 * 8;
       if (p.epilogue == B2TTS_GEMM_SILU_MUL) {
@@ -290,27 +442,51 @@ gemm_stream_kernel(const GemmParams p) {
         uint2 w;
         w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
         stg_v2(p.out + (int64_t)m * p.out_stride + (n >> 1), w);
-      } else {
-        if (p.epilogue == B2TTS_GEMM_BIAS && p.bias) {
-          const uint4 bw = ldg_v4(p.bias + n);
-          acc[0] += bf16lo(bw.x); acc[1] += bf16hi(bw.x); acc[2] += bf16lo(bw.y); acc[3] += bf16hi(bw.y);
-          acc[4] += bf16lo(bw.z); acc[5] += bf16hi(bw.z); acc[6] += bf16lo(bw.w); acc[7] += bf16hi(bw.w);
-        } else if (p.epilogue == B2TTS_GEMM_RESIDUAL) {
-          // bf16(residual + bf16(x W^T)): the projection output is rounded before the add
-          const uint4 rw = ldg_v4(p.res + (int64_t)m * p.res_stride + n);
-          acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
-          acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
-          acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
-          acc[6] = rbf(acc[6]) + bf16lo(rw.w); acc[7] = rbf(acc[7]) + bf16hi(rw.w);
-        }
-        uint4 w;
-        w.x = pack_bf16(acc[0], acc[1]); w.y = pack_bf16(acc[2], acc[3]);
-        w.z = pack_bf16(acc[4], acc[5]); w.w = pack_bf16(acc[6], acc[7]);
-        stg_v4(p.out + (int64_t)m * p.out_stride + n, w);
+        return 0.f;
+      }
+      if (p.epilogue == B2TTS_GEMM_BIAS && p.bias) {
+        const uint4 bw = ldg_v4(p.bias + n);
+        acc[0] += bf16lo(bw.x); acc[1] += bf16hi(bw.x); acc[2] += bf16lo(bw.y); acc[3] += bf16hi(bw.y);
+        acc[4] += bf16lo(bw.z); acc[5] += bf16hi(bw.z); acc[6] += bf16lo(bw.w); acc[7] += bf16hi(bw.w);
+      } else if (p.epilogue == B2TTS_GEMM_RESIDUAL) {
+        // bf16(residual + bf16(x W^T)): the projection output is rounded before the add
+        const uint4 rw = ldg_v4(p.res + (int64_t)m * p.res_stride + n);
+        acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
+        acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
+        acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
+        acc[6] = rbf(acc[6]) + bf16lo(rw.w); acc[7] = rbf(acc[7]) + bf16hi(rw.w);
+      }
+      uint4 w;
+      w.x = pack_bf16(acc[0], acc[1]); w.y = pack_bf16(acc[2], acc[3]);
+      w.z = pack_bf16(acc[4], acc[5]); w.w = pack_bf16(acc[6], acc[7]);
+      stg_v4(p.out + (int64_t)m * p.out_stride + n, w);
+      float q = 0.f;
+      q = fmaf(bf16lo(w.x), bf16lo(w.x), q); q = fmaf(bf16hi(w.x), bf16hi(w.x), q);
+      q = fmaf(bf16lo(w.y), bf16lo(w.y), q); q = fmaf(bf16hi(w.y), bf16hi(w.y), q);
+      q = fmaf(bf16lo(w.z), bf16lo(w.z), q); q = fmaf(bf16hi(w.z), bf16hi(w.z), q);
+      q = fmaf(bf16lo(w.w), bf16lo(w.w), q); q = fmaf(bf16hi(w.w), bf16hi(w.w), q);
+      return q;
+    };
+    if (p.ssq_out) {
+      // one thread per batch row walks this CTA's feature groups in order: a deterministic partial
+      // sum of squares of the stored row slice, slot = (tile, rank)
+      const int slots = (p.n / G_BN) * S;
+      for (int m = threadIdx.x; m < p.m; m += G_THREADS) {
+        float q = 0.f;
+        for (int g8 = 0; g8 < groups; ++g8) q += item(m, g8);
+        p.ssq_out[(int64_t)m * slots + tile * S + rank] = q;
+      }
+    } else {
+      const int items = p.m * groups;
+      for (int it = threadIdx.x; it < items; it += G_THREADS) {
+        const int g8 = it / p.m;                   // lanes along m: conflict-free reads of red
+        item(it - g8 * p.m, g8);
       }
     }
   }
+  if (S > 1) cluster_wait();                    // peers' copies out of my staging area have completed
   __syncthreads();
+  if (threadIdx.x == 0) G_TRACE(7);
   if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
 }
 
@@ -341,17 +517,35 @@ gemm_pack_kernel(const __nv_bfloat16* __restrict__ w, int64_t w_stride, uint8_t*
 }
 
 static int choose_splits(int n_tiles, int kblocks) {
+  // fill the SMs, then keep splitting while a CTA still has more k-blocks than the ring holds and
+  // two CTAs per SM can be resident
   int s = 1;
-  while (s < 16 && n_tiles * s < 120 && s * 2 <= kblocks) s *= 2;
+  while (s < 8 && s * 2 <= kblocks && (n_tiles * s < 120 || (kblocks / s > G_STAGES && n_tiles * s * 2 <= 2 * 148))) s *= 2;
   return s;
 }
 
-static size_t gemm_smem_bytes(int mpad) {
-  return (size_t)G_STAGES * (G_WTILE_BYTES + mpad * 128) + 1024 + 128;
+static size_t gemm_smem_bytes(int mpad, int stages, int splits) {
+  return (size_t)stages * (G_WTILE_BYTES + mpad * 128) + (splits > 1 ? (size_t)(mpad + 4) * 512 : 0) + 256 + (size_t)mpad * 4 +
+         1024;
+}
+
+// ring depth: the deepest ring that still lets two CTAs share an SM (the next GEMM's weight prefetch
+// then overlaps this one's epilogue under programmatic dependent launch), else the deepest that fits.
+static int choose_stages(int mpad, int splits) {
+  const size_t two_per_sm = 113 * 1024, one_per_sm = 227 * 1024;
+  if (const char* e = getenv("B2TTS_GEMM_STAGES")) {            // experiments only
+    const int st = atoi(e);
+    if (st >= 2 && st <= G_MAX_STAGES && gemm_smem_bytes(mpad, st, splits) <= one_per_sm) return st;
+  }
+  for (int st : {4, 3})
+    if (gemm_smem_bytes(mpad, st, splits) <= two_per_sm) return st;
+  for (int st : {4, 3, 2})
+    if (gemm_smem_bytes(mpad, st, splits) <= one_per_sm) return st;
+  return 0;
 }
 
 template <int NCH>
-static int launch_gemm(const GemmParams& p, cudaStream_t st, int pdl) {
+static int launch_gemm(const GemmParams& p, const CUtensorMap& tmap, cudaStream_t st, int pdl) {
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_stream_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -363,7 +557,7 @@ static int launch_gemm(const GemmParams& p, cudaStream_t st, int pdl) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(p.splits, p.n / G_BN, 1);
   cfg.blockDim = dim3(G_THREADS, 1, 1);
-  cfg.dynamicSmemBytes = gemm_smem_bytes(p.mpad);
+  cfg.dynamicSmemBytes = gemm_smem_bytes(p.mpad, p.stages, p.splits);
   cfg.stream = st;
   cudaLaunchAttribute attrs[2];
   int na = 0;
@@ -381,7 +575,7 @@ static int launch_gemm(const GemmParams& p, cudaStream_t st, int pdl) {
   }
   cfg.attrs = attrs;
   cfg.numAttrs = na;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_stream_kernel<NCH>, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_stream_kernel<NCH>, p, tmap);
   count_launch();
   if (e != cudaSuccess) return cuda_fail(e, "gemm_bf16");
   return B2TTS_OK;
@@ -416,12 +610,46 @@ extern "C" int b2tts_gemm_pack_weight(const void* weight, int64_t weight_row_str
   return B2TTS_OK;
 }
 
-extern "C" int b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void* w_packed,
-                               const void* bias, const void* residual, int64_t residual_row_stride,
-                               void* out, int64_t out_row_stride, int m, int n, int k,
-                               int epilogue, int rounding, int splits, int pdl, void* stream) {
-  using namespace b2;
-  const char* what = "gemm_bf16";
+namespace b2 {
+// x[M, K] (bf16, row stride in elements) as a 2-D tensor map: box = 64 k x mpad rows, SWIZZLE_128B, rows
+// beyond M zero-filled.  The driver entry point is resolved through the runtime (no libcuda link).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int make_x_tensor_map(CUtensorMap* tm, const void* x, int64_t row_stride, int m, int k, int mpad, const char* what) {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !sym) {
+      set_error("%s: cuTensorMapEncodeTiled unavailable", what);
+      return B2TTS_ECUDA;
+    }
+    fn = reinterpret_cast<EncodeTiledFn>(sym);
+  }
+  const cuuint64_t dims[2] = {(cuuint64_t)k, (cuuint64_t)m};
+  const cuuint64_t strides[1] = {(cuuint64_t)row_stride * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)G_BK, (cuuint32_t)mpad};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(x), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("%s: cuTensorMapEncodeTiled failed (%d) for x [%d, %d] stride %lld", what, (int)r, m, k, (long long)row_stride);
+    return B2TTS_ECUDA;
+  }
+  return B2TTS_OK;
+}
+
+static unsigned long long* g_trace_base = nullptr;   // debug only (b2tts_debug_gemm_trace)
+static size_t g_trace_slots = 0, g_trace_next = 0;
+static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, const void* w_packed,
+                     const void* bias, const void* residual, int64_t residual_row_stride,
+                     void* out, int64_t out_row_stride, int m, int n, int k,
+                     int epilogue, int rounding, int splits, int pdl,
+                     const void* norm_weight, const float* ssq_in, int ssq_in_slots, float eps, float* ssq_out,
+                     void* stream) {
   B2_REQUIRE(m >= 0 && n > 0 && k > 0, B2TTS_EINVAL, "%s: m=%d n=%d k=%d", what, m, n, k);
   if (m == 0) return B2TTS_OK;
   B2_REQUIRE(b2tts_gemm_bf16_supported(m, n, k), B2TTS_EUNSUPPORTED,
@@ -434,6 +662,9 @@ extern "C" int b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void* 
                  (epilogue == B2TTS_GEMM_SILU_MUL || out_row_stride % 8 == 0) &&
                  (!bias || aligned16(bias)) && (!residual || (aligned16(residual) && residual_row_stride % 8 == 0)),
              B2TTS_EALIGN, "%s: pointers / strides must be 16-byte aligned", what);
+  B2_REQUIRE(!norm_weight || (ssq_in && ssq_in_slots > 0 && aligned16(norm_weight) && aligned16(ssq_in)), B2TTS_EINVAL,
+             "%s: fused norm needs ssq_in with >= 1 slot per row (16-byte aligned)", what);
+  B2_REQUIRE(!ssq_out || epilogue != B2TTS_GEMM_SILU_MUL, B2TTS_EINVAL, "%s: ssq_out with the SiLU*mul epilogue", what);
   GemmParams p{};
   p.x = static_cast<const __nv_bfloat16*>(x);
   p.x_stride = x_row_stride;
@@ -452,13 +683,70 @@ extern "C" int b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void* 
   B2_REQUIRE((s == 1 || s == 2 || s == 4 || s == 8 || s == 16) && s <= p.kblocks, B2TTS_EINVAL,
              "%s: splits %d must be 1,2,4,8,16 and <= k/64", what, s);
   p.splits = s;
+  p.stages = choose_stages(p.mpad, s);
+  B2_REQUIRE(p.stages >= 2, B2TTS_EUNSUPPORTED, "%s: no shared-memory plan for m=%d", what, m);
   p.tmem_cols = 32;
   while (p.tmem_cols < p.mpad) p.tmem_cols <<= 1;
+  p.norm_w = static_cast<const __nv_bfloat16*>(norm_weight);
+  p.ssq_in = ssq_in;
+  p.ssq_in_slots = ssq_in_slots;
+  p.eps = eps;
+  p.ssq_out = ssq_out;
+  p.ssq_lanes = 1;
+  p.trace = nullptr;
+  if (g_trace_base && g_trace_next < g_trace_slots) p.trace = g_trace_base + (g_trace_next++) * 4096 * 8;
+  if (norm_weight) {
+    int g = 128 / p.mpad;
+    if (g > 8) g = 8;
+    if (g < 1) g = 1;
+    while (g > 1 && (ssq_in_slots % g)) g >>= 1;
+    // float4 loads need 16-byte aligned chunks
+    while (g > 1 && ((ssq_in_slots / g) % 4)) g >>= 1;
+    p.ssq_lanes = g;
+    B2_REQUIRE(ssq_in_slots % 4 == 0 || g == 1, B2TTS_EALIGN, "%s: ssq_in_slots %d", what, ssq_in_slots);
+  }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nch = p.mpad / 16;                  // 16-byte chunks per producer thread per k-block
-  if (nch <= 1) return launch_gemm<1>(p, st, pdl);
-  if (nch <= 2) return launch_gemm<2>(p, st, pdl);
-  if (nch <= 4) return launch_gemm<4>(p, st, pdl);
-  if (nch <= 8) return launch_gemm<8>(p, st, pdl);
-  return launch_gemm<16>(p, st, pdl);
+  CUtensorMap tmap;
+  int rc = make_x_tensor_map(&tmap, x, x_row_stride, m, k, p.mpad, what);
+  if (rc) return rc;
+  if (nch <= 1) return launch_gemm<1>(p, tmap, st, pdl);
+  if (nch <= 2) return launch_gemm<2>(p, tmap, st, pdl);
+  if (nch <= 4) return launch_gemm<4>(p, tmap, st, pdl);
+  return launch_gemm<8>(p, tmap, st, pdl);
+}
+}  // namespace b2
+
+extern "C" int b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void* w_packed,
+                               const void* bias, const void* residual, int64_t residual_row_stride,
+                               void* out, int64_t out_row_stride, int m, int n, int k,
+                               int epilogue, int rounding, int splits, int pdl, void* stream) {
+  return b2::gemm_impl("gemm_bf16", x, x_row_stride, w_packed, bias, residual, residual_row_stride, out, out_row_stride,
+                       m, n, k, epilogue, rounding, splits, pdl, nullptr, nullptr, 0, 0.f, nullptr, stream);
+}
+
+extern "C" int b2tts_gemm_ssq_slots(int n, int k, int splits) {
+  if (n <= 0 || k <= 0 || n % b2::G_BN || k % b2::G_BK) return 0;
+  const int s = splits > 0 ? splits : b2::choose_splits(n / b2::G_BN, k / b2::G_BK);
+  return (n / b2::G_BN) * s;
+}
+
+extern "C" int b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const void* w_packed,
+                                    const void* bias, const void* residual, int64_t residual_row_stride,
+                                    void* out, int64_t out_row_stride, int m, int n, int k,
+                                    int epilogue, int rounding, int splits, int pdl,
+                                    const void* norm_weight, const float* ssq_in, int ssq_in_slots, float eps,
+                                    float* ssq_out, void* stream) {
+  return b2::gemm_impl("gemm_norm_bf16", x, x_row_stride, w_packed, bias, residual, residual_row_stride, out,
+                       out_row_stride, m, n, k, epilogue, rounding, splits, pdl, norm_weight, ssq_in, ssq_in_slots, eps,
+                       ssq_out, stream);
+}
+
+// Debug aid (tools/gemm_trace.py): every following GEMM launch records 8 globaltimer stamps per CTA into
+// buffer + launch_index * 4096 * 8 (uint64), for `launches` launches.  NULL switches tracing off.
+extern "C" B2TTS_API int b2tts_debug_gemm_trace(void* buffer, int launches) {
+  b2::g_trace_base = static_cast<unsigned long long*>(buffer);
+  b2::g_trace_slots = buffer ? (size_t)launches : 0;
+  b2::g_trace_next = 0;
+  return B2TTS_OK;
 }
