@@ -232,16 +232,38 @@ B2TTS_API int    b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void
  *     rounding(x[m, k] * rstd[m], norm_weight[k]) (same rounding points as b2tts_rmsnorm) with
  *     rstd[m] = 1/sqrt(sum_j ssq_in[m, j] / k + eps), j < ssq_in_slots summed in a fixed order.
  *   ssq_out != NULL (bias / residual epilogues): ssq_out[m, slot] = sum of squares of the bf16 values this
- *     call stored in out[m, :] over slot's feature slice; slots per row = b2tts_gemm_ssq_slots(n, k, splits).
+ *     call stored in out[m, :] over slot's feature slice; slots per row = b2tts_gemm_ssq_slots(m, n, k, splits).
  *     The next b2tts_gemm_norm_bf16 over `out` takes it as ssq_in: the decoder layer's two norm launches
  *     disappear, and the normalised activations never reach HBM. */
-B2TTS_API int    b2tts_gemm_ssq_slots(int n, int k, int splits);
+B2TTS_API int    b2tts_gemm_ssq_slots(int m, int n, int k, int splits);
 B2TTS_API int    b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const void* w_packed,
                                       const void* bias, const void* residual, int64_t residual_row_stride,
                                       void* out, int64_t out_row_stride, int m, int n, int k,
                                       int epilogue, int rounding, int splits, int pdl,
                                       const void* norm_weight, const float* ssq_in, int ssq_in_slots, float eps,
                                       float* ssq_out, void* stream);
+
+/* ---- a5 + a4 + a1 + a2 in one launch: the decode step of Qwen3TTSAttention.forward ------------------------
+ * replaces q_norm, k_norm, rotary_emb, store_kvcache and flash_attn_with_kvcache as called per decode token
+ *                                       models/qwen3_tts_share.py:96-109, layers/attention.py:33-54, 92-95
+ * q/k/v are the rows of the QKV projection (one new token per sequence).  The kernel normalises + rotates q
+ * and k (arguments as b2tts_qknorm_rope_kvwrite), writes K (normed + rotated) and V (raw) of the new token
+ * to cache[slot_mapping[i]], attends over context_lens[i] cached tokens INCLUDING the new one
+ * (arguments as b2tts_paged_attn_decode) and folds the split-KV partials itself (the last CTA of a
+ * sequence to finish does it, in split order).  K cache bytes and attention outputs equal those of the
+ * separate calls.  workspace: b2tts_fused_decode_attn_workspace_bytes(...) bytes, ZERO-FILLED once by the
+ * caller before the first launch (the kernel leaves its tickets zero).  pdl as b2tts_gemm_bf16. */
+B2TTS_API size_t b2tts_fused_decode_attn_workspace_bytes(int batch, int num_heads, int head_dim, int max_ctx);
+B2TTS_API int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, const void* k, int64_t k_row_stride,
+                            const void* v, int64_t v_row_stride,
+                            const void* q_weight, const void* k_weight, float eps,
+                            const int64_t* positions, int64_t pos_row_stride,
+                            const float* inv_freq, const int32_t* modality, float attention_scaling,
+                            const int32_t* slot_mapping, void* k_cache, void* v_cache,
+                            const int32_t* block_table, int bt_stride, const int32_t* context_lens,
+                            void* out, void* workspace, size_t workspace_bytes,
+                            int batch, int num_heads, int num_kv_heads, int head_dim, int page_size,
+                            float scale, int max_ctx, int rounding, int pdl, void* stream);
 
 #ifdef __cplusplus
 }

@@ -61,7 +61,10 @@ def _load():
         "b2tts_gemm_packed_bytes": (Z, [I, I]),
         "b2tts_gemm_pack_weight": (I, [P, L, P, I, I, I, P]),
         "b2tts_gemm_bf16": (I, [P, L, P, P, P, L, P, L, I, I, I, I, I, I, I, P]),
-        "b2tts_gemm_ssq_slots": (I, [I, I, I]),
+        "b2tts_gemm_ssq_slots": (I, [I, I, I, I]),
+        "b2tts_fused_decode_attn_workspace_bytes": (Z, [I, I, I, I]),
+        "b2tts_fused_decode_attn": (I, [P, L, P, L, P, L, P, P, F, P, L, P, P, F, P, P, P, P, I, P, P, P, Z,
+                                        I, I, I, I, I, F, I, I, I, P]),
         "b2tts_gemm_norm_bf16": (I, [P, L, P, P, P, L, P, L, I, I, I, I, I, I, I, P, P, I, F, P, P]),
     }
     for name, (res, args) in sig.items():
@@ -144,6 +147,38 @@ def paged_attn_decode(q, k_cache, v_cache, block_table, context_lens, scale, max
                                            block_table.data_ptr(), block_table.stride(0), context_lens.data_ptr(),
                                            out.data_ptr(), _ptr(workspace), wbytes, b, h, kvh, hd, page,
                                            float(scale), int(max_ctx), _stream()), "paged_attn_decode")
+    return out
+
+
+def fused_decode_attn_workspace(batch, num_heads, head_dim, max_ctx, device) -> torch.Tensor:
+    """Zero-filled scratch for ``fused_decode_attn`` (split partials + per-row tickets; the kernel leaves the
+    tickets zero, so one allocation serves every later launch of up to ``batch`` rows)."""
+    n = max(int(_load().b2tts_fused_decode_attn_workspace_bytes(b, num_heads, head_dim, max_ctx))
+            for b in range(1, batch + 1))
+    return torch.zeros(n + 16, dtype=torch.uint8, device=device)
+
+
+def fused_decode_attn(q, k, v, q_weight, k_weight, eps, positions, inv_freq, slot_mapping, k_cache, v_cache,
+                      block_table, context_lens, scale, max_ctx, workspace, *, modality=None, attention_scaling=1.0,
+                      rounding=ROUND_EAGER, out=None, pdl=True):
+    """The whole decode step of the attention block in one launch: q/k head norm + RoPE, KV write of the new
+    token, paged GQA attention over ``context_lens`` tokens (the new one included), split-KV combine.
+    q [B, heads, 128], k/v [B, kv_heads, 128] are views of the QKV projection; returns [B, heads, 128]."""
+    _cuda(q, BF16, "q"); _cuda(k, BF16, "k"); _cuda(v, BF16, "v")
+    _cuda(positions, I64, "positions"); _cuda(inv_freq, F32, "inv_freq"); _cuda(slot_mapping, I32, "slot_mapping")
+    _cuda(block_table, I32, "block_table"); _cuda(context_lens, I32, "context_lens")
+    b, h, hd = q.shape
+    page, kvh = k_cache.shape[1], k_cache.shape[2]
+    if out is None:
+        out = torch.empty(b, h, hd, dtype=BF16, device=q.device)
+    pos_stride = positions.stride(0) if positions.dim() == 2 else 0
+    _check(_load().b2tts_fused_decode_attn(
+        q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0),
+        _ptr(q_weight), _ptr(k_weight), float(eps), positions.data_ptr(), pos_stride, inv_freq.data_ptr(),
+        _ptr(modality), float(attention_scaling), slot_mapping.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+        block_table.data_ptr(), block_table.stride(0), context_lens.data_ptr(), out.data_ptr(),
+        workspace.data_ptr(), workspace.numel() * workspace.element_size(), b, h, kvh, hd, page, float(scale),
+        int(max_ctx), int(rounding), int(bool(pdl)), _stream()), "fused_decode_attn")
     return out
 
 
@@ -358,8 +393,8 @@ def gemm_pack_weight(weight, mode=PACK_PLAIN):
     return packed
 
 
-def gemm_ssq_slots(n: int, k: int, splits: int = 0) -> int:
-    return int(_load().b2tts_gemm_ssq_slots(int(n), int(k), int(splits)))
+def gemm_ssq_slots(m: int, n: int, k: int, splits: int = 0) -> int:
+    return int(_load().b2tts_gemm_ssq_slots(int(m), int(n), int(k), int(splits)))
 
 
 def gemm_bf16(x, packed, n, bias=None, residual=None, epilogue=GEMM_BIAS, rounding=ROUND_EAGER, out=None,
@@ -392,7 +427,7 @@ def gemm_bf16(x, packed, n, bias=None, residual=None, epilogue=GEMM_BIAS, roundi
         slots_in = ssq_in.shape[1]
     if ssq_out is not None:
         _cuda(ssq_out, torch.float32, "ssq_out")
-        need = gemm_ssq_slots(n, k, splits)
+        need = gemm_ssq_slots(m, n, k, splits)
         if ssq_out.dim() != 2 or ssq_out.shape[0] < m or ssq_out.shape[1] != need or not ssq_out.is_contiguous():
             raise ValueError(f"ssq_out must be a contiguous [>=M, {need}] fp32 tensor")
     _check(_load().b2tts_gemm_norm_bf16(x.data_ptr(), x.stride(0), packed.data_ptr(), _ptr(bias), _ptr(residual),

@@ -1,0 +1,508 @@
+// attention_fused.cu - the decode step of Qwen3TTSAttention.forward (models/qwen3_tts_share.py:96-109)
+// as ONE kernel: per-head q/k RMSNorm + RoPE (layers/rotary_embedding.py:11-212), the paged KV write of
+// the new token (store_kvcache, layers/attention.py:10-54), the block_table paged GQA attention
+// (flash_attn_with_kvcache, attention.py:92-95) and the split-KV combine.  The separate
+// qknorm_rope_kvwrite / paged_attn / attn_combine launches of the decode path collapse into this one.
+//
+// Same HBM design as attention.cu: one CTA per (sequence, KV split) covers all kv heads; a producer
+// warp streams 8-token K and V tiles (all heads of a token are contiguous in the page) with 1-D bulk
+// async copies into a 3-stage mbarrier ring; consumer warp w owns kv head w and its GROUP q heads.
+// Fusion:
+//   * prologue: every consumer warp normalises + rotates its q heads straight out of the QKV GEMM
+//     output (registers only).  The split that owns the sequence's last tile also normalises +
+//     rotates k head w, writes it and the raw v head to cache[slot], and keeps both in registers:
+//     when the last tile lands in shared memory the warp overwrites the new token's row (its own
+//     head's 256 bytes) with the register copy, so it never depends on reading its own global write;
+//   * rounding points and even the fp32 summation order of the head norm are those of
+//     qknorm_rope_kvwrite_kernel (norm_rope.cu), so K cache bytes are identical to the unfused path;
+//   * combine: split partials go to the workspace; the LAST CTA of a sequence to finish (atomic
+//     ticket) folds them in split order - deterministic - and resets the ticket for the next launch.
+#include "common.cuh"
+
+namespace b2 {
+
+constexpr int FA_HD = 128;
+constexpr int FA_TILE = 8;
+constexpr int FA_NSTAGE = 3;
+
+struct FusedAttnParams {
+  const __nv_bfloat16 *q, *k, *v;          // rows of the QKV projection
+  int64_t q_stride, k_stride, v_stride;
+  const __nv_bfloat16 *q_w, *k_w;          // head-norm weights [128]
+  float eps;
+  const int64_t* positions;                // [rows] or [3][rows]
+  int64_t pos_row_stride;
+  const float* inv_freq;                   // [64]
+  const int32_t* modality;                 // [128] or null
+  float attention_scaling;
+  const int32_t* slot_mapping;             // [rows]
+  __nv_bfloat16 *k_cache, *v_cache;        // [pages, page, kvh, 128]
+  const int32_t* block_table;
+  int bt_stride, page_size;
+  const int32_t* context_lens;
+  __nv_bfloat16* out;                      // [rows, heads*128]
+  float* part_acc;                         // [rows, nsplit, heads, 128]
+  float* part_ml;                          // [rows, nsplit, heads, 2]
+  int* tickets;                            // [rows], zero between launches
+  int nsplit, num_heads, num_kv_heads;
+  float scale_log2;
+};
+
+__device__ __forceinline__ float fa_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ void fa_unpack8(const uint4& r, float* f) {
+  f[0] = bf16lo(r.x); f[1] = bf16hi(r.x); f[2] = bf16lo(r.y); f[3] = bf16hi(r.y);
+  f[4] = bf16lo(r.z); f[5] = bf16hi(r.z); f[6] = bf16lo(r.w); f[7] = bf16hi(r.w);
+}
+__device__ __forceinline__ uint4 fa_pack8(const float* f) {
+  uint4 r;
+  r.x = pack_bf16(f[0], f[1]); r.y = pack_bf16(f[2], f[3]); r.z = pack_bf16(f[4], f[5]); r.w = pack_bf16(f[6], f[7]);
+  return r;
+}
+
+// Head norm + RoPE of one 128-wide head held as x[0..7] = dims 8j.., x[8..15] = dims 64+8j.. by the 8
+// lanes j of a token group.  Bit-identical to qknorm_rope_kvwrite_kernel: that kernel's lane l owns dims
+// {2l, 2l+1, 64+2l, 64+2l+1} and reduces with an xor tree 16,8,4,2,1; here lane j owns its lanes
+// 4j..4j+3, so the tree becomes xor 4,2,1 across lanes on four partials, then (p0+p2)+(p1+p3).
+template <bool EAGER>
+__device__ __forceinline__ void head_norm_rope(float* x, const __nv_bfloat16* w, float eps, int j,
+                                               const float* c1, const float* s1, const float* c2, const float* s2) {
+  if (w) {
+    float pp[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float ss = x[2 * i] * x[2 * i];
+      ss = fmaf(x[2 * i + 1], x[2 * i + 1], ss);
+      ss = fmaf(x[8 + 2 * i], x[8 + 2 * i], ss);
+      ss = fmaf(x[8 + 2 * i + 1], x[8 + 2 * i + 1], ss);
+      ss += __shfl_xor_sync(0xffffffffu, ss, 4);
+      ss += __shfl_xor_sync(0xffffffffu, ss, 2);
+      ss += __shfl_xor_sync(0xffffffffu, ss, 1);
+      pp[i] = ss;
+    }
+    const float sum = (pp[0] + pp[2]) + (pp[1] + pp[3]);
+    const float var = sum / (float)FA_HD + eps;
+    const float rstd = EAGER ? 1.0f / sqrtf(var) : rsqrtf(var);
+    float wf[16];
+    fa_unpack8(ldg_v4(w + 8 * j), wf);
+    fa_unpack8(ldg_v4(w + 64 + 8 * j), wf + 8);
+#pragma unroll
+    for (int d = 0; d < 16; ++d) x[d] = rbf(EAGER ? rbf(x[d] * rstd) * wf[d] : (x[d] * rstd) * wf[d]);
+  }
+#pragma unroll
+  for (int d = 0; d < 8; ++d) {
+    const float a = x[d], b = x[8 + d];
+    x[d] = rbf(rbf(a * c1[d]) + rbf(-b * s1[d]));          // rotate_half: first half pairs with -x2
+    x[8 + d] = rbf(rbf(b * c2[d]) + rbf(a * s2[d]));
+  }
+}
+
+template <int GROUP, bool EAGER>
+__global__ void __launch_bounds__(288, 2)
+fused_decode_attn_kernel(const FusedAttnParams p) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  const int kvh = p.num_kv_heads;
+  const int kv_dim = kvh * FA_HD;
+  const int stage_elems = FA_TILE * kv_dim;
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+  __nv_bfloat16* Vs = Ks + FA_NSTAGE * stage_elems;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(Vs + FA_NSTAGE * stage_elems);
+  uint64_t* empty_bar = full_bar + FA_NSTAGE;
+  int* last_flag = reinterpret_cast<int*>(empty_bar + FA_NSTAGE);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x;
+  const int split = blockIdx.y;
+
+  pdl_launch();
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < FA_NSTAGE; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(empty_bar + s, kvh);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  pdl_wait();                                   // q/k/v rows, slots and lengths come from earlier kernels
+
+  int L = __ldg(p.context_lens + row);
+  if (L < 0) L = 0;
+  const int n_tiles = (L + FA_TILE - 1) / FA_TILE;
+  const int t_begin = (int)(((int64_t)split * n_tiles) / p.nsplit);
+  const int t_end = (int)(((int64_t)(split + 1) * n_tiles) / p.nsplit);
+  const int my_tiles = t_end - t_begin;
+  const bool writer = (split == p.nsplit - 1);  // owns the last tile, i.e. the token appended this step
+
+  if (warp == kvh) {
+    // =========================== producer warp
+    if (lane == 0) {
+      for (int i = 0; i < my_tiles; ++i) {
+        const int stage = i % FA_NSTAGE;
+        const uint32_t ph = (i / FA_NSTAGE) & 1;
+        mbar_wait(empty_bar + stage, ph ^ 1);
+        const int tok0 = (t_begin + i) * FA_TILE;
+        const int ntok = min(FA_TILE, L - tok0);
+        int page = __ldg(p.block_table + (int64_t)row * p.bt_stride + tok0 / p.page_size);
+        if (page < 0) page = 0;                  // never faults on a stale (-1) table entry
+        const int64_t slot = (int64_t)page * p.page_size + tok0 % p.page_size;
+        const uint32_t bytes = (uint32_t)(ntok * kv_dim * 2);
+        mbar_expect_tx(full_bar + stage, 2u * bytes);
+        bulk_g2s(Ks + stage * stage_elems, p.k_cache + slot * kv_dim, bytes, full_bar + stage);
+        bulk_g2s(Vs + stage * stage_elems, p.v_cache + slot * kv_dim, bytes, full_bar + stage);
+      }
+    }
+    return;
+  }
+
+  // =========================== consumer warp `warp` owns kv head `warp`
+  const int g = lane >> 3;        // token slot within a 4-token step
+  const int j = lane & 7;         // which 16 head-dims: [8j,8j+8) and [64+8j,64+8j+8)
+  const int head0 = warp * GROUP;
+
+  if (L == 0) {                   // CUDA-graph padding row (talker_mode_runner.py:97-100): zeros, no ticket
+    if (split == 0 && g == 0) {
+#pragma unroll
+      for (int h = 0; h < GROUP; ++h) {
+        __nv_bfloat16* o = p.out + ((int64_t)row * p.num_heads + head0 + h) * FA_HD;
+        stg_v4(o + 8 * j, make_uint4(0, 0, 0, 0));
+        stg_v4(o + 64 + 8 * j, make_uint4(0, 0, 0, 0));
+      }
+    }
+    return;
+  }
+
+  // ---- cos/sin of this lane's 16 columns (fp32 angle -> bf16, as rotary_embedding.py:138-139)
+  float c1[8], s1[8], c2[8], s2[8];
+#pragma unroll
+  for (int d = 0; d < 8; ++d) {
+    const int fi = 8 * j + d;
+    const float f = __ldg(p.inv_freq + fi);
+    const int m1 = p.modality ? __ldg(p.modality + fi) : 0;
+    const float a1 = (float)__ldg(p.positions + (int64_t)m1 * p.pos_row_stride + row) * f;
+    c1[d] = rbf(cosf(a1) * p.attention_scaling);
+    s1[d] = rbf(sinf(a1) * p.attention_scaling);
+    const int m2 = p.modality ? __ldg(p.modality + FA_HD / 2 + fi) : 0;
+    if (m2 != m1) {
+      const float a2 = (float)__ldg(p.positions + (int64_t)m2 * p.pos_row_stride + row) * f;
+      c2[d] = rbf(cosf(a2) * p.attention_scaling);
+      s2[d] = rbf(sinf(a2) * p.attention_scaling);
+    } else {
+      c2[d] = c1[d]; s2[d] = s1[d];
+    }
+  }
+
+  // ---- q heads: norm + rope in registers, pre-scaled for exp2
+  float qv[GROUP][16];
+#pragma unroll
+  for (int h = 0; h < GROUP; ++h) {
+    const __nv_bfloat16* qp = p.q + (int64_t)row * p.q_stride + (head0 + h) * FA_HD;
+    fa_unpack8(ldg_v4(qp + 8 * j), qv[h]);
+    fa_unpack8(ldg_v4(qp + 64 + 8 * j), qv[h] + 8);
+    head_norm_rope<EAGER>(qv[h], p.q_w, p.eps, j, c1, s1, c2, s2);
+#pragma unroll
+    for (int d = 0; d < 16; ++d) qv[h][d] *= p.scale_log2;
+  }
+
+  // ---- the appended token: k head (norm + rope) and raw v head -> cache[slot] and registers
+  uint4 kn0 = make_uint4(0, 0, 0, 0), kn1 = kn0, vn0 = kn0, vn1 = kn0;
+  if (writer) {
+    float kf[16];
+    const __nv_bfloat16* kp = p.k + (int64_t)row * p.k_stride + warp * FA_HD;
+    fa_unpack8(ldg_v4(kp + 8 * j), kf);
+    fa_unpack8(ldg_v4(kp + 64 + 8 * j), kf + 8);
+    head_norm_rope<EAGER>(kf, p.k_w, p.eps, j, c1, s1, c2, s2);
+    kn0 = fa_pack8(kf); kn1 = fa_pack8(kf + 8);
+    const __nv_bfloat16* vp = p.v + (int64_t)row * p.v_stride + warp * FA_HD;
+    vn0 = ldg_v4(vp + 8 * j); vn1 = ldg_v4(vp + 64 + 8 * j);
+    const int slot = __ldg(p.slot_mapping + row);
+    if (slot >= 0 && g == 0) {
+      __nv_bfloat16* kd = p.k_cache + (int64_t)slot * kv_dim + warp * FA_HD;
+      __nv_bfloat16* vd = p.v_cache + (int64_t)slot * kv_dim + warp * FA_HD;
+      stg_v4(kd + 8 * j, kn0); stg_v4(kd + 64 + 8 * j, kn1);
+      stg_v4(vd + 8 * j, vn0); stg_v4(vd + 64 + 8 * j, vn1);
+    }
+  }
+
+  float m[GROUP], l[GROUP], acc[GROUP][16];
+#pragma unroll
+  for (int h = 0; h < GROUP; ++h) {
+    m[h] = -INFINITY; l[h] = 0.f;
+#pragma unroll
+    for (int d = 0; d < 16; ++d) acc[h][d] = 0.f;
+  }
+
+  for (int i = 0; i < my_tiles; ++i) {
+    const int stage = i % FA_NSTAGE;
+    const uint32_t ph = (i / FA_NSTAGE) & 1;
+    const int tok0 = (t_begin + i) * FA_TILE;
+    const int ntok = min(FA_TILE, L - tok0);
+    mbar_wait(full_bar + stage, ph);
+    __nv_bfloat16* kt = Ks + stage * stage_elems + warp * FA_HD;
+    __nv_bfloat16* vt = Vs + stage * stage_elems + warp * FA_HD;
+    if (writer && i == my_tiles - 1) {
+      // the bulk copy may have read the new token's row before or after the global store above:
+      // replace this head's slice of that row with the register copy
+      if (g == 0) {
+        __nv_bfloat16* kr = kt + (L - 1 - tok0) * kv_dim;
+        __nv_bfloat16* vr = vt + (L - 1 - tok0) * kv_dim;
+        *reinterpret_cast<uint4*>(kr + 8 * j) = kn0; *reinterpret_cast<uint4*>(kr + 64 + 8 * j) = kn1;
+        *reinterpret_cast<uint4*>(vr + 8 * j) = vn0; *reinterpret_cast<uint4*>(vr + 64 + 8 * j) = vn1;
+      }
+      __syncwarp();
+    }
+
+    float s[FA_TILE / 4][GROUP];
+    int tokc[FA_TILE / 4];
+#pragma unroll
+    for (int it = 0; it < FA_TILE / 4; ++it) {
+      const int tok = it * 4 + g;
+      const bool valid = tok < ntok;
+      tokc[it] = valid ? tok : 0;
+      const __nv_bfloat16* kr = kt + tokc[it] * kv_dim;
+      float kf[16];
+      fa_unpack8(*reinterpret_cast<const uint4*>(kr + 8 * j), kf);
+      fa_unpack8(*reinterpret_cast<const uint4*>(kr + 64 + 8 * j), kf + 8);
+#pragma unroll
+      for (int h = 0; h < GROUP; ++h) {
+        float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+        for (int d = 0; d < 16; d += 2) {
+          d0 = fmaf(qv[h][d], kf[d], d0);
+          d1 = fmaf(qv[h][d + 1], kf[d + 1], d1);
+        }
+        float dot = d0 + d1;
+        dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+        s[it][h] = valid ? dot : -INFINITY;
+      }
+    }
+    float alpha[GROUP];
+#pragma unroll
+    for (int h = 0; h < GROUP; ++h) {
+      float mt = s[0][h];
+#pragma unroll
+      for (int it = 1; it < FA_TILE / 4; ++it) mt = fmaxf(mt, s[it][h]);
+      mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, 8));
+      mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, 16));
+      const float mn = fmaxf(m[h], mt);
+      alpha[h] = fa_exp2(m[h] - mn);
+      m[h] = mn;
+      float ps = 0.f;
+#pragma unroll
+      for (int it = 0; it < FA_TILE / 4; ++it) {
+        s[it][h] = fa_exp2(s[it][h] - mn);
+        ps += s[it][h];
+      }
+      l[h] = fmaf(l[h], alpha[h], ps);
+#pragma unroll
+      for (int d = 0; d < 16; ++d) acc[h][d] *= alpha[h];
+    }
+#pragma unroll
+    for (int it = 0; it < FA_TILE / 4; ++it) {
+      const __nv_bfloat16* vr = vt + tokc[it] * kv_dim;
+      float vf[16];
+      fa_unpack8(*reinterpret_cast<const uint4*>(vr + 8 * j), vf);
+      fa_unpack8(*reinterpret_cast<const uint4*>(vr + 64 + 8 * j), vf + 8);
+#pragma unroll
+      for (int h = 0; h < GROUP; ++h)
+#pragma unroll
+        for (int d = 0; d < 16; ++d) acc[h][d] = fmaf(s[it][h], vf[d], acc[h][d]);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty_bar + stage);
+  }
+
+  // ---- fold the 4 token slots of the warp
+#pragma unroll
+  for (int h = 0; h < GROUP; ++h) {
+    l[h] += __shfl_xor_sync(0xffffffffu, l[h], 8);
+    l[h] += __shfl_xor_sync(0xffffffffu, l[h], 16);
+#pragma unroll
+    for (int d = 0; d < 16; ++d) {
+      acc[h][d] += __shfl_xor_sync(0xffffffffu, acc[h][d], 8);
+      acc[h][d] += __shfl_xor_sync(0xffffffffu, acc[h][d], 16);
+    }
+  }
+
+  if (p.nsplit == 1) {
+    if (g == 0) {
+#pragma unroll
+      for (int h = 0; h < GROUP; ++h) {
+        const float inv = 1.f / l[h];
+        float o[16];
+#pragma unroll
+        for (int d = 0; d < 16; ++d) o[d] = acc[h][d] * inv;
+        __nv_bfloat16* op = p.out + ((int64_t)row * p.num_heads + head0 + h) * FA_HD;
+        stg_v4(op + 8 * j, fa_pack8(o));
+        stg_v4(op + 64 + 8 * j, fa_pack8(o + 8));
+      }
+    }
+    return;
+  }
+
+  // ---- split-KV: partials out, then the last CTA of this sequence folds all of them
+  if (g == 0) {
+#pragma unroll
+    for (int h = 0; h < GROUP; ++h) {
+      const int64_t idx = ((int64_t)row * p.nsplit + split) * p.num_heads + head0 + h;
+      float* pa = p.part_acc + idx * FA_HD;
+      *reinterpret_cast<float4*>(pa + 8 * j) = make_float4(acc[h][0], acc[h][1], acc[h][2], acc[h][3]);
+      *reinterpret_cast<float4*>(pa + 8 * j + 4) = make_float4(acc[h][4], acc[h][5], acc[h][6], acc[h][7]);
+      *reinterpret_cast<float4*>(pa + 64 + 8 * j) = make_float4(acc[h][8], acc[h][9], acc[h][10], acc[h][11]);
+      *reinterpret_cast<float4*>(pa + 64 + 8 * j + 4) = make_float4(acc[h][12], acc[h][13], acc[h][14], acc[h][15]);
+      if (j == 0) {
+        p.part_ml[idx * 2] = my_tiles > 0 ? m[h] : -INFINITY;
+        p.part_ml[idx * 2 + 1] = my_tiles > 0 ? l[h] : 0.f;
+      }
+    }
+  }
+  __threadfence();
+  asm volatile("bar.sync 1, %0;" :: "r"(kvh * 32) : "memory");      // the consumer warps only
+  if (threadIdx.x == 0) {
+    const int t = atomicAdd(p.tickets + row, 1);
+    *last_flag = (t == p.nsplit - 1);
+    if (t == p.nsplit - 1) p.tickets[row] = 0;                     // ready for the next launch
+  }
+  asm volatile("bar.sync 1, %0;" :: "r"(kvh * 32) : "memory");
+  if (!*last_flag) return;
+  __threadfence();
+  // warp w folds heads head0 .. head0+GROUP-1; lane owns 4 consecutive dims
+#pragma unroll
+  for (int h = 0; h < GROUP; ++h) {
+    const int head = head0 + h;
+    const int64_t base = ((int64_t)row * p.nsplit) * p.num_heads + head;
+    float M = -INFINITY;
+    for (int s = 0; s < p.nsplit; ++s) M = fmaxf(M, __ldcg(p.part_ml + (base + (int64_t)s * p.num_heads) * 2));
+    float4 num = make_float4(0.f, 0.f, 0.f, 0.f);
+    float den = 0.f;
+    for (int s = 0; s < p.nsplit; ++s) {
+      const int64_t idx = base + (int64_t)s * p.num_heads;
+      const float ls = __ldcg(p.part_ml + idx * 2 + 1);
+      if (ls > 0.f) {
+        const float w = fa_exp2(__ldcg(p.part_ml + idx * 2) - M);
+        const float4 a = __ldcg(reinterpret_cast<const float4*>(p.part_acc + idx * FA_HD) + lane);
+        num.x = fmaf(w, a.x, num.x); num.y = fmaf(w, a.y, num.y);
+        num.z = fmaf(w, a.z, num.z); num.w = fmaf(w, a.w, num.w);
+        den = fmaf(w, ls, den);
+      }
+    }
+    const float inv = den > 0.f ? 1.f / den : 0.f;
+    uint2 o;
+    o.x = pack_bf16(num.x * inv, num.y * inv);
+    o.y = pack_bf16(num.z * inv, num.w * inv);
+    stg_v2(p.out + ((int64_t)row * p.num_heads + head) * FA_HD + 4 * lane, o);
+  }
+}
+
+static size_t fa_smem_bytes(int kv_heads) {
+  return (size_t)2 * FA_NSTAGE * FA_TILE * kv_heads * FA_HD * 2 + 2 * FA_NSTAGE * sizeof(uint64_t) + 16;
+}
+
+// split-KV factor: one wave of 2 CTAs per SM, at least 2 tiles per split
+static int fa_choose_nsplit(int rows, int max_ctx) {
+  const int max_tiles = (max_ctx + FA_TILE - 1) / FA_TILE;
+  int n = (2 * sm_count()) / (rows > 0 ? rows : 1);
+  const int cap = (max_tiles + 1) / 2;
+  if (n > cap) n = cap;
+  if (n < 1) n = 1;
+  if (n > 32) n = 32;
+  return n;
+}
+
+}  // namespace b2
+
+extern "C" size_t b2tts_fused_decode_attn_workspace_bytes(int batch, int num_heads, int head_dim, int max_ctx) {
+  if (batch <= 0 || num_heads <= 0 || head_dim <= 0 || max_ctx <= 0) return 0;
+  const int nsplit = b2::fa_choose_nsplit(batch, max_ctx);
+  // partials + (m, l) + one ticket per row (the tickets must be zero before the first launch)
+  return (size_t)batch * nsplit * num_heads * (head_dim + 2) * sizeof(float) + (size_t)batch * sizeof(int) + 16;
+}
+
+extern "C" int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, const void* k, int64_t k_row_stride,
+                                       const void* v, int64_t v_row_stride,
+                                       const void* q_weight, const void* k_weight, float eps,
+                                       const int64_t* positions, int64_t pos_row_stride,
+                                       const float* inv_freq, const int32_t* modality, float attention_scaling,
+                                       const int32_t* slot_mapping, void* k_cache, void* v_cache,
+                                       const int32_t* block_table, int bt_stride, const int32_t* context_lens,
+                                       void* out, void* workspace, size_t workspace_bytes,
+                                       int batch, int num_heads, int num_kv_heads, int head_dim, int page_size,
+                                       float scale, int max_ctx, int rounding, int pdl, void* stream) {
+  using namespace b2;
+  const char* what = "fused_decode_attn";
+  B2_REQUIRE(batch >= 0 && max_ctx > 0 && page_size > 0 && bt_stride > 0, B2TTS_EINVAL,
+             "%s: batch=%d max_ctx=%d page_size=%d bt_stride=%d", what, batch, max_ctx, page_size, bt_stride);
+  if (batch == 0) return B2TTS_OK;
+  B2_REQUIRE(q && k && v && positions && inv_freq && slot_mapping && k_cache && v_cache && block_table && context_lens &&
+                 out && workspace, B2TTS_EINVAL, "%s: null pointer", what);
+  B2_REQUIRE(head_dim == FA_HD, B2TTS_EUNSUPPORTED, "%s: head_dim %d unsupported (128)", what, head_dim);
+  B2_REQUIRE(num_kv_heads >= 1 && num_kv_heads <= 8 && num_heads % num_kv_heads == 0, B2TTS_EUNSUPPORTED,
+             "%s: heads %d / kv heads %d unsupported", what, num_heads, num_kv_heads);
+  B2_REQUIRE(page_size % FA_TILE == 0, B2TTS_EUNSUPPORTED, "%s: page_size %d must be a multiple of %d", what, page_size,
+             FA_TILE);
+  B2_REQUIRE(rounding == B2TTS_ROUND_EAGER || rounding == B2TTS_ROUND_FUSED, B2TTS_EINVAL, "%s: rounding %d", what, rounding);
+  B2_REQUIRE(aligned16(q) && aligned16(k) && aligned16(v) && aligned16(k_cache) && aligned16(v_cache) && aligned16(out) &&
+                 aligned16(workspace) && q_row_stride % 8 == 0 && k_row_stride % 8 == 0 && v_row_stride % 8 == 0 &&
+                 (!q_weight || aligned16(q_weight)) && (!k_weight || aligned16(k_weight)),
+             B2TTS_EALIGN, "%s: pointers / strides must be 16-byte aligned", what);
+  FusedAttnParams p{};
+  p.q = static_cast<const __nv_bfloat16*>(q);
+  p.k = static_cast<const __nv_bfloat16*>(k);
+  p.v = static_cast<const __nv_bfloat16*>(v);
+  p.q_stride = q_row_stride; p.k_stride = k_row_stride; p.v_stride = v_row_stride;
+  p.q_w = static_cast<const __nv_bfloat16*>(q_weight);
+  p.k_w = static_cast<const __nv_bfloat16*>(k_weight);
+  p.eps = eps;
+  p.positions = positions;
+  p.pos_row_stride = pos_row_stride;
+  p.inv_freq = inv_freq;
+  p.modality = modality;
+  p.attention_scaling = attention_scaling;
+  p.slot_mapping = slot_mapping;
+  p.k_cache = static_cast<__nv_bfloat16*>(k_cache);
+  p.v_cache = static_cast<__nv_bfloat16*>(v_cache);
+  p.block_table = block_table;
+  p.bt_stride = bt_stride;
+  p.page_size = page_size;
+  p.context_lens = context_lens;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.nsplit = fa_choose_nsplit(batch, max_ctx);
+  p.num_heads = num_heads;
+  p.num_kv_heads = num_kv_heads;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  const size_t acc_elems = (size_t)batch * p.nsplit * num_heads * head_dim;
+  const size_t need = b2tts_fused_decode_attn_workspace_bytes(batch, num_heads, head_dim, max_ctx);
+  B2_REQUIRE(workspace_bytes >= need, B2TTS_EWORKSPACE, "%s: workspace %zu B < %zu B needed", what, workspace_bytes, need);
+  p.part_acc = static_cast<float*>(workspace);
+  p.part_ml = p.part_acc + acc_elems;
+  p.tickets = reinterpret_cast<int*>(p.part_ml + (size_t)batch * p.nsplit * num_heads * 2);
+
+  const int group = num_heads / num_kv_heads;
+  const bool eager = rounding == B2TTS_ROUND_EAGER;
+  void (*kern)(const FusedAttnParams) = nullptr;
+  if (group == 1) kern = eager ? fused_decode_attn_kernel<1, true> : fused_decode_attn_kernel<1, false>;
+  else if (group == 2) kern = eager ? fused_decode_attn_kernel<2, true> : fused_decode_attn_kernel<2, false>;
+  else if (group == 4) kern = eager ? fused_decode_attn_kernel<4, true> : fused_decode_attn_kernel<4, false>;
+  B2_REQUIRE(kern, B2TTS_EUNSUPPORTED, "%s: GQA group %d unsupported (1, 2, 4)", what, group);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return cuda_fail(e, what);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(batch, p.nsplit, 1);
+  cfg.blockDim = dim3(32 * (num_kv_heads + 1), 1, 1);
+  cfg.dynamicSmemBytes = fa_smem_bytes(num_kv_heads);
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  e = cudaLaunchKernelEx(&cfg, kern, p);
+  count_launch();
+  if (e != cudaSuccess) return cuda_fail(e, what);
+  return B2TTS_OK;
+}

@@ -393,6 +393,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     if (S > 1) {
       fence_proxy_async();                      // generic-proxy stores -> visible to the bulk copies
       bar_sync_producers();
+      if (threadIdx.x == 64) G_TRACE(5);
       if (threadIdx.x == 64) {
         const uint32_t chunk = (uint32_t)(rows_own * rstride * 4);
         const uint32_t recv_local = smem_u32(recv) + (uint32_t)rank * chunk;
@@ -516,14 +517,6 @@ gemm_pack_kernel(const __nv_bfloat16* __restrict__ w, int64_t w_stride, uint8_t*
   }
 }
 
-static int choose_splits(int n_tiles, int kblocks) {
-  // fill the SMs, then keep splitting while a CTA still has more k-blocks than the ring holds and
-  // two CTAs per SM can be resident
-  int s = 1;
-  while (s < 8 && s * 2 <= kblocks && (n_tiles * s < 120 || (kblocks / s > G_STAGES && n_tiles * s * 2 <= 2 * 148))) s *= 2;
-  return s;
-}
-
 static size_t gemm_smem_bytes(int mpad, int stages, int splits) {
   return (size_t)stages * (G_WTILE_BYTES + mpad * 128) + (splits > 1 ? (size_t)(mpad + 4) * 512 : 0) + 256 + (size_t)mpad * 4 +
          1024;
@@ -542,6 +535,20 @@ static int choose_stages(int mpad, int splits) {
   for (int st : {4, 3, 2})
     if (gemm_smem_bytes(mpad, st, splits) <= one_per_sm) return st;
   return 0;
+}
+
+static int choose_splits(int n_tiles, int kblocks, int mpad) {
+  // the largest K-split (cluster size <= 8: 16-CTA clusters schedule badly) whose CTAs are all
+  // resident at once given the shared-memory footprint, with at least two k-blocks per CTA
+  int best = 1;
+  for (int s = 2; s <= 8; s *= 2) {
+    if (s * 2 > kblocks) break;
+    const int st = choose_stages(mpad, s);
+    if (st < 2) break;
+    const int per_sm = gemm_smem_bytes(mpad, st, s) <= 113 * 1024 ? 2 : 1;
+    if (n_tiles * s <= sm_count() * per_sm) best = s;
+  }
+  return best;
 }
 
 template <int NCH>
@@ -679,7 +686,7 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
   p.kblocks = k / G_BK;
   p.epilogue = epilogue;
   p.rounding = rounding;
-  int s = splits > 0 ? splits : choose_splits(n / G_BN, p.kblocks);
+  int s = splits > 0 ? splits : choose_splits(n / G_BN, p.kblocks, p.mpad);
   B2_REQUIRE((s == 1 || s == 2 || s == 4 || s == 8 || s == 16) && s <= p.kblocks, B2TTS_EINVAL,
              "%s: splits %d must be 1,2,4,8,16 and <= k/64", what, s);
   p.splits = s;
@@ -725,9 +732,9 @@ extern "C" int b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void* 
                        m, n, k, epilogue, rounding, splits, pdl, nullptr, nullptr, 0, 0.f, nullptr, stream);
 }
 
-extern "C" int b2tts_gemm_ssq_slots(int n, int k, int splits) {
+extern "C" int b2tts_gemm_ssq_slots(int m, int n, int k, int splits) {
   if (n <= 0 || k <= 0 || n % b2::G_BN || k % b2::G_BK) return 0;
-  const int s = splits > 0 ? splits : b2::choose_splits(n / b2::G_BN, k / b2::G_BK);
+  const int s = splits > 0 ? splits : b2::choose_splits(n / b2::G_BN, k / b2::G_BK, (m + 15) & ~15);
   return (n / b2::G_BN) * s;
 }
 

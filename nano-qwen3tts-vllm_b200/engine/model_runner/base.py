@@ -161,12 +161,15 @@ class ModelRunner:
             ws_bytes = max(ws_bytes, nat.paged_attn_decode_workspace_bytes(
                 bs, c.num_attention_heads, c.head_dim, self.max_blocks * self.block_size))
         self.attn_workspace = torch.empty(max(ws_bytes, 16), dtype=torch.uint8, device=self.device)
+        self.fused_attn_workspace = nat.fused_decode_attn_workspace(
+            self.max_bs, c.num_attention_heads, c.head_dim, self.max_blocks * self.block_size, self.device)
         layer_id = 0
         for module in self.model.modules():
             if hasattr(module, "k_cache") and hasattr(module, "v_cache"):
                 module.k_cache = self.kv_cache[0, layer_id]
                 module.v_cache = self.kv_cache[1, layer_id]
                 module.workspace = self.attn_workspace
+                module.fused_workspace = self.fused_attn_workspace
                 layer_id += 1
 
     # ------------------------------------------------------------------ batch layout

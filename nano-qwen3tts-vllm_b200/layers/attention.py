@@ -26,6 +26,7 @@ class Attention(nn.Module):
         self.num_heads, self.head_dim, self.scale, self.num_kv_heads = num_heads, head_dim, scale, num_kv_heads
         self.k_cache = self.v_cache = torch.tensor([])
         self.workspace = None                     # split-KV scratch, bound by the runner
+        self.fused_workspace = None               # zero-filled scratch of the fused decode kernel, bound by the runner
 
     def attend(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tensor | None = None):
         """Attention only (the KV rows of this step are already in the cache)."""

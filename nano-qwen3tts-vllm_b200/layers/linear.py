@@ -39,42 +39,77 @@ def native_ok(m: int, n: int, k: int) -> bool:
     return 1 <= m <= GEMM_NATIVE_MAX_M and nat.gemm_supported(m, n, k)
 
 
+class RowNorm:
+    """An RMSNorm that has not been applied yet: the consuming GEMM normalises its input rows while it
+    stages them (``b2tts_gemm_norm_bf16``).  ``ssq`` [M, slots] fp32 holds partial sums of squares of the
+    rows, left by the GEMM epilogue that produced them."""
+    __slots__ = ("weight", "ssq", "eps", "rounding")
+
+    def __init__(self, weight, ssq, eps, rounding):
+        self.weight, self.ssq, self.eps, self.rounding = weight, ssq, eps, rounding
+
+
+def _norm_kw(norm):
+    return {} if norm is None else dict(norm_weight=norm.weight, ssq_in=norm.ssq, eps=norm.eps, rounding=norm.rounding)
+
+
+def _ssq_buffer(m, n, k, device):
+    return torch.empty(m, nat.gemm_ssq_slots(m, n, k), dtype=torch.float32, device=device)
+
+
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = None,
-           out: torch.Tensor | None = None) -> torch.Tensor:
+           out: torch.Tensor | None = None, norm: RowNorm | None = None, want_ssq: bool = False):
+    """y = x W^T (+ b).  ``norm``: x is un-normalised and the GEMM applies the RMSNorm on the fly (native
+    path only).  ``want_ssq``: also return the [M, slots] partial row sums of squares of y."""
     if not x.is_cuda:
         raise RuntimeError("libb200tts: linear() needs CUDA tensors (there is no CPU path)")
     x2 = x.reshape(-1, x.shape[-1])
     m, n = x2.shape[0], weight.shape[0]
     if native_ok(m, n, x2.shape[1]):
-        y = nat.gemm_bf16(x2, packed_weight(weight), n, bias=bias, out=out, pdl=PDL)
-    else:
-        y = torch.nn.functional.linear(x2, weight, bias)
-        if out is not None:
-            out.copy_(y)
-            y = out
+        ssq = _ssq_buffer(m, n, x2.shape[1], x.device) if want_ssq else None
+        y = nat.gemm_bf16(x2, packed_weight(weight), n, bias=bias, out=out, pdl=PDL, ssq_out=ssq, **_norm_kw(norm))
+        y = y.view(*x.shape[:-1], n)
+        return (y, ssq) if want_ssq else y
+    if norm is not None or want_ssq:
+        raise RuntimeError(f"libb200tts: fused-norm GEMM unsupported for m={m} n={n} k={x2.shape[1]}")
+    y = torch.nn.functional.linear(x2, weight, bias)
+    if out is not None:
+        out.copy_(y)
+        y = out
     return y.view(*x.shape[:-1], n)
 
 
 def linear_residual(x: torch.Tensor, weight: torch.Tensor, residual: torch.Tensor,
-                    out: torch.Tensor | None = None) -> torch.Tensor:
+                    out: torch.Tensor | None = None, want_ssq: bool = False):
     """bf16(residual + bf16(x W^T)) - the projection followed by the decoder layer's residual add
-    (models/qwen3_tts_share.py:171,175 of the reference) in the GEMM epilogue.  ``out`` may be ``residual``."""
+    (models/qwen3_tts_share.py:171,175 of the reference) in the GEMM epilogue.  ``out`` may be ``residual``.
+    ``want_ssq`` also returns the partial row sums of squares of the result (for the next fused norm)."""
     m, n = x.shape[0], weight.shape[0]
     if native_ok(m, n, x.shape[1]):
-        return nat.gemm_bf16(x, packed_weight(weight), n, residual=residual, epilogue=nat.GEMM_RESIDUAL, out=out, pdl=PDL)
+        ssq = _ssq_buffer(m, n, x.shape[1], x.device) if want_ssq else None
+        y = nat.gemm_bf16(x, packed_weight(weight), n, residual=residual, epilogue=nat.GEMM_RESIDUAL, out=out, pdl=PDL,
+                          ssq_out=ssq)
+        return (y, ssq) if want_ssq else y
+    if want_ssq:
+        raise RuntimeError(f"libb200tts: ssq epilogue unsupported for m={m} n={n} k={x.shape[1]}")
     y = torch.nn.functional.linear(x, weight)
     if out is None:
         return residual + y
     return torch.add(residual, y, out=out)
 
 
-def linear_silu_mul(x: torch.Tensor, gate_up_weight: torch.Tensor, rounding: int = nat.ROUND_EAGER) -> torch.Tensor:
+def linear_silu_mul(x: torch.Tensor, gate_up_weight: torch.Tensor, rounding: int = nat.ROUND_EAGER,
+                    norm: RowNorm | None = None) -> torch.Tensor:
     """silu(x Wg^T) * (x Wu^T) over the merged [gate; up] weight (qwen3_tts_share.py:131-135) with the
     activation in the GEMM epilogue: the [M, 2I] intermediate never reaches HBM."""
     m, n = x.shape[0], gate_up_weight.shape[0]
     if native_ok(m, n, x.shape[1]):
+        kw = _norm_kw(norm)
+        kw.setdefault("rounding", rounding)
         return nat.gemm_bf16(x, packed_weight(gate_up_weight, nat.PACK_GATE_UP), n, epilogue=nat.GEMM_SILU_MUL,
-                             rounding=rounding, pdl=PDL)
+                             pdl=PDL, **kw)
+    if norm is not None:
+        raise RuntimeError(f"libb200tts: fused-norm GEMM unsupported for m={m} n={n} k={x.shape[1]}")
     gu = torch.nn.functional.linear(x, gate_up_weight)
     return nat.silu_and_mul(gu[:, :n // 2], gu[:, n // 2:], rounding)
 

@@ -12,7 +12,7 @@ from torch import nn
 
 from .. import _native as nat
 from ..config import StackConfig
-from ..layers.linear import ReplicatedLinear, linear
+from ..layers.linear import ReplicatedLinear, linear, native_ok
 from .qwen3_tts_share import DecoderStack, load_reference_weights
 
 
@@ -24,8 +24,8 @@ class Qwen3TTSCodePredictorModel(DecoderStack):
         self.codec_embedding = nn.Parameter(torch.empty(n, config.vocab_size, talker_config.hidden_size),
                                             requires_grad=False)
 
-    def forward(self, input_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
-        return self.run_layers(input_embeds, positions)
+    def forward(self, input_embeds: torch.Tensor, positions: torch.Tensor, input_ssq=None) -> torch.Tensor:
+        return self.run_layers(input_embeds, positions, input_ssq)
 
 
 class Qwen3TTSCodePredictorForCausalLM(nn.Module):
@@ -71,9 +71,15 @@ class Qwen3TTSCodePredictorForCausalLM(nn.Module):
         return nat.gather_rows(self.model.codec_embedding, input_ids.view(-1), (steps - 1).to(torch.int32))
 
     def forward(self, inputs_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
-        if self.small_to_mtp_projection is not None:
-            inputs_embeds = self.small_to_mtp_projection(inputs_embeds)
-        return self.model(inputs_embeds, positions)
+        proj, ssq = self.small_to_mtp_projection, None
+        if proj is not None:
+            x2 = inputs_embeds.reshape(-1, inputs_embeds.shape[-1])
+            if native_ok(x2.shape[0], proj.weight.shape[0], x2.shape[1]):
+                # the projection's epilogue leaves the row sums of squares the first layer's norm needs
+                inputs_embeds, ssq = linear(x2, proj.weight, proj.bias, want_ssq=True)
+            else:
+                inputs_embeds = proj(inputs_embeds)
+        return self.model(inputs_embeds, positions, ssq)
 
     def compute_logits(self, hidden_states: torch.Tensor, generation_steps: list[int]) -> torch.Tensor:
         """hidden_states [num_seqs * len, H] -> logits of the LAST position of every sequence through

@@ -26,9 +26,12 @@ from ..layers.activation import SiluAndMul
 from ..layers.attention import Attention
 from ..layers.layernorm import Qwen3TTSRMSNorm
 from ..layers.linear import (GEMM_NATIVE_MAX_M, MergedColumnParallelLinear, QKVParallelLinear, RowParallelLinear,
-                             linear_residual, linear_silu_mul)
+                             RowNorm, linear, linear_residual, linear_silu_mul)
 from ..layers.rotary_embedding import get_rope
 from ..utils.context import get_context
+
+
+FUSED_DECODE_ATTENTION = True     # False: separate qknorm_rope_kvwrite + paged_attn_decode launches
 
 
 class Qwen3TTSAttention(nn.Module):
@@ -54,17 +57,27 @@ class Qwen3TTSAttention(nn.Module):
         o = self.attend(positions, hidden_states)
         return self.o_proj(o)
 
-    def attend(self, positions: torch.Tensor, hidden_states: torch.Tensor) -> torch.Tensor:
-        """Everything up to (not including) o_proj: [n, heads * head_dim]."""
+    def attend(self, positions: torch.Tensor, hidden_states: torch.Tensor, norm: RowNorm | None = None) -> torch.Tensor:
+        """Everything up to (not including) o_proj: [n, heads * head_dim].  With ``norm`` the input is the
+        un-normalised residual stream and the QKV GEMM applies the input RMSNorm while staging it."""
         ctx = get_context()
         n = hidden_states.shape[0]
-        qkv = self.qkv_proj(hidden_states)
+        qkv = linear(hidden_states, self.qkv_proj.weight, norm=norm)
         q = qkv[:, :self.q_size].view(n, self.num_heads, self.head_dim)
         k = qkv[:, self.q_size:self.q_size + self.kv_size].view(n, self.num_kv_heads, self.head_dim)
         v = qkv[:, self.q_size + self.kv_size:].view(n, self.num_kv_heads, self.head_dim)
         have_cache = self.attn.k_cache.numel() > 0
         packed_kv = ctx.is_prefill and ctx.block_tables is None           # prefill attends to the projections
         rope = self.rotary_emb
+        if have_cache and not ctx.is_prefill and self.attn.fused_workspace is not None and FUSED_DECODE_ATTENTION:
+            # decode: q/k-norm + RoPE + KV write + paged attention + split-KV combine in one launch
+            max_ctx = ctx.max_context_len or ctx.block_tables.shape[1] * self.attn.k_cache.shape[1]
+            o = nat.fused_decode_attn(
+                q, k, v, self.q_norm.weight, self.k_norm.weight, self.eps, positions, rope.inv_freq, ctx.slot_mapping,
+                self.attn.k_cache, self.attn.v_cache, ctx.block_tables, ctx.context_lens, self.scaling, max_ctx,
+                self.attn.fused_workspace, modality=rope.modality if positions.dim() > 1 else None,
+                attention_scaling=rope.attention_scaling, rounding=self.rounding)
+            return o.view(n, self.q_size)
         q_rot, k_rot = nat.qknorm_rope_kvwrite(
             q, k, v, self.q_norm.weight, self.k_norm.weight, self.eps, positions, rope.inv_freq,
             modality=rope.modality if positions.dim() > 1 else None, attention_scaling=rope.attention_scaling,
@@ -112,18 +125,26 @@ class Qwen3TTSDecoderLayer(nn.Module):
         hidden_states = self.mlp(hidden_states)
         return hidden_states, residual
 
-    def forward_decode(self, positions: torch.Tensor, residual: torch.Tensor, in_place: bool) -> torch.Tensor:
-        """The same layer on the residual stream alone, for n <= GEMM_NATIVE_MAX_M rows: the two residual
-        adds ride in the o_proj / down_proj GEMM epilogues and SiLU*mul in the gate_up epilogue, so a
-        layer is 8 launches (norm, qkv, qk-norm+rope+kv-write, attention, o+res, norm, gate_up+act,
-        down+res).  Rounding points are unchanged: bf16(residual + bf16(x W^T)), then the norm.
-        ``in_place`` False keeps the caller's tensor (the first layer's input embeddings) intact."""
-        h = nat.rmsnorm(residual, self.input_layernorm.weight, self.eps, self.rounding)
-        o = self.self_attn.attend(positions, h)
-        residual = linear_residual(o, self.self_attn.o_proj.weight, residual, out=residual if in_place else None)
-        h = nat.rmsnorm(residual, self.post_attention_layernorm.weight, self.eps, self.rounding)
-        act = linear_silu_mul(h, self.mlp.gate_up_proj.weight, self.rounding)
-        return linear_residual(act, self.mlp.down_proj.weight, residual, out=residual)
+    def forward_decode(self, positions: torch.Tensor, residual: torch.Tensor, ssq: torch.Tensor | None, in_place: bool):
+        """The same layer on the residual stream alone, for n <= GEMM_NATIVE_MAX_M rows, 5 launches:
+        QKV GEMM (input RMSNorm applied while x is staged), q/k-norm + RoPE + KV write, attention,
+        o_proj GEMM (+ residual add, row sums of squares out), gate_up GEMM (post-attention RMSNorm in,
+        SiLU*mul out), down GEMM (+ residual add, row sums of squares out).  ``ssq`` = partial row sums of
+        squares of ``residual`` from the GEMM that produced it (None: a separate RMSNorm launch).
+        Rounding points are unchanged: bf16(residual + bf16(x W^T)), then the norm of the rounded sum.
+        ``in_place`` False keeps the caller's tensor (the first layer's input embeddings) intact.
+        Returns (residual, ssq)."""
+        if ssq is None:
+            h = nat.rmsnorm(residual, self.input_layernorm.weight, self.eps, self.rounding)
+            o = self.self_attn.attend(positions, h)
+        else:
+            o = self.self_attn.attend(positions, residual,
+                                      RowNorm(self.input_layernorm.weight, ssq, self.eps, self.rounding))
+        residual, ssq = linear_residual(o, self.self_attn.o_proj.weight, residual, out=residual if in_place else None,
+                                        want_ssq=True)
+        act = linear_silu_mul(residual, self.mlp.gate_up_proj.weight, self.rounding,
+                              norm=RowNorm(self.post_attention_layernorm.weight, ssq, self.eps, self.rounding))
+        return linear_residual(act, self.mlp.down_proj.weight, residual, out=residual, want_ssq=True)
 
 
 class DecoderStack(nn.Module):
@@ -136,11 +157,12 @@ class DecoderStack(nn.Module):
         self.layers = nn.ModuleList([Qwen3TTSDecoderLayer(config, rounding) for _ in range(config.num_hidden_layers)])
         self.norm = Qwen3TTSRMSNorm(config.hidden_size, eps=config.rms_norm_eps, rounding=rounding)
 
-    def run_layers(self, input_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
+    def run_layers(self, input_embeds: torch.Tensor, positions: torch.Tensor,
+                   input_ssq: torch.Tensor | None = None) -> torch.Tensor:
         if input_embeds.shape[0] <= GEMM_NATIVE_MAX_M:
-            residual = input_embeds
+            residual, ssq = input_embeds, input_ssq
             for i, layer in enumerate(self.layers):
-                residual = layer.forward_decode(positions, residual, in_place=i > 0)
+                residual, ssq = layer.forward_decode(positions, residual, ssq, in_place=i > 0)
             return nat.rmsnorm(residual, self.norm.weight, self.config.rms_norm_eps, self.rounding)
         hidden_states, residual = input_embeds, None
         for layer in self.layers:

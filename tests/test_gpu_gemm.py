@@ -164,7 +164,7 @@ def test_gemm_ssq_out_then_fused_norm_in(native, m, rounding):
     w_qkv = (torch.randn(4096, h, device="cuda", generator=g) * 0.03).to(BF16)
     nw = (1 + 0.1 * torch.randn(h, device="cuda", generator=g)).to(BF16)
     pd, pq = native.gemm_pack_weight(w_down), native.gemm_pack_weight(w_qkv)
-    slots = native.gemm_ssq_slots(h, inter)
+    slots = native.gemm_ssq_slots(m, h, inter)
     ssq = torch.full((m, slots), float("nan"), device="cuda")
     new_res = native.gemm_bf16(act, pd, h, residual=res, epilogue=native.GEMM_RESIDUAL, ssq_out=ssq)
     want_res = native.gemm_bf16(act, pd, h, residual=res, epilogue=native.GEMM_RESIDUAL)
@@ -204,7 +204,7 @@ def test_gemm_bias_epilogue_ssq_out(native):
     x = torch.randn(m, k, device="cuda", generator=g).to(BF16)
     w = (torch.randn(n, k, device="cuda", generator=g) * 0.05).to(BF16)
     b = torch.randn(n, device="cuda", generator=g).to(BF16)
-    ssq = torch.zeros(m, native.gemm_ssq_slots(n, k), device="cuda")
+    ssq = torch.zeros(m, native.gemm_ssq_slots(m, n, k), device="cuda")
     y = native.gemm_bf16(x, native.gemm_pack_weight(w), n, bias=b, ssq_out=ssq)
     assert torch.equal(y, native.gemm_bf16(x, native.gemm_pack_weight(w), n, bias=b))
     torch.testing.assert_close(ssq.sum(1), y.float().pow(2).sum(1), rtol=1e-5, atol=1e-5)

@@ -31,10 +31,10 @@ trace.zero_()
 g.replay(); torch.cuda.synchronize()
 t = trace.view(chain, 4096, 8).cpu()
 ncta = int((t[0, :, 0] != 0).sum())
-names = ["entry", "setup done", "x: dep resolved", "x: first block staged", "accum complete", "cluster wait 1", "exchange done", "end"]
+names = ["entry", "setup done", "x: dep resolved", "x: first block staged", "accum complete", "staged", "exchange done", "end"]
 base = int(t[0, :ncta, 0].min())
 print(f"M={m} N={n} K={k} splits={splits} CTAs={ncta}; times in us relative to first CTA entry of launch 0")
 for i in range(chain):
     tt = (t[i, :ncta].double() - base) / 1e3
-    row = "  ".join(f"{names[j][:14]:>14s} {tt[:, j].min():6.2f}/{tt[:, j].median():6.2f}/{tt[:, j].max():6.2f}" for j in (0, 2, 3, 4, 6, 7))
+    row = "  ".join(f"{names[j][:14]:>14s} {tt[:, j].min():6.2f}/{tt[:, j].median():6.2f}/{tt[:, j].max():6.2f}" for j in (2, 3, 4, 5, 6, 7))
     print(f"launch {i}: {row}")
