@@ -8,15 +8,16 @@
 // warp streams 8-token K and V tiles (all heads of a token are contiguous in the page) with 1-D bulk
 // async copies into a 3-stage mbarrier ring; consumer warp w owns kv head w and its GROUP q heads.
 // Fusion:
-//   * prologue: every consumer warp normalises + rotates its q heads straight out of the QKV GEMM
-//     output (registers only).  The split that owns the sequence's last tile also normalises +
-//     rotates k head w, writes it and the raw v head to cache[slot], and keeps both in registers:
-//     when the last tile lands in shared memory the warp overwrites the new token's row (its own
-//     head's 256 bytes) with the register copy, so it never depends on reading its own global write;
-//   * rounding points and even the fp32 summation order of the head norm are those of
-//     qknorm_rope_kvwrite_kernel (norm_rope.cu), so K cache bytes are identical to the unfused path;
+//   * prologue: the consumer warps run the arithmetic of qknorm_rope_kvwrite_kernel (norm_rope.cu; same
+//     lane mapping, rounding points and summation order, so K cache bytes are identical to the unfused
+//     path) on the one new token: q heads go to shared memory; the split that owns the sequence's last
+//     tile also normalises + rotates k, writes it and the raw v to cache[slot] and keeps a copy in
+//     shared memory: when the last tile lands, each warp overwrites its head's slice of the new token's
+//     row with that copy, so it never depends on reading its own global write;
 //   * combine: split partials go to the workspace; the LAST CTA of a sequence to finish (atomic
 //     ticket) folds them in split order - deterministic - and resets the ticket for the next launch.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b2 {
@@ -63,43 +64,6 @@ __device__ __forceinline__ uint4 fa_pack8(const float* f) {
   return r;
 }
 
-// Head norm + RoPE of one 128-wide head held as x[0..7] = dims 8j.., x[8..15] = dims 64+8j.. by the 8
-// lanes j of a token group.  Bit-identical to qknorm_rope_kvwrite_kernel: that kernel's lane l owns dims
-// {2l, 2l+1, 64+2l, 64+2l+1} and reduces with an xor tree 16,8,4,2,1; here lane j owns its lanes
-// 4j..4j+3, so the tree becomes xor 4,2,1 across lanes on four partials, then (p0+p2)+(p1+p3).
-template <bool EAGER>
-__device__ __forceinline__ void head_norm_rope(float* x, const __nv_bfloat16* w, float eps, int j,
-                                               const float* c1, const float* s1, const float* c2, const float* s2) {
-  if (w) {
-    float pp[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      float ss = x[2 * i] * x[2 * i];
-      ss = fmaf(x[2 * i + 1], x[2 * i + 1], ss);
-      ss = fmaf(x[8 + 2 * i], x[8 + 2 * i], ss);
-      ss = fmaf(x[8 + 2 * i + 1], x[8 + 2 * i + 1], ss);
-      ss += __shfl_xor_sync(0xffffffffu, ss, 4);
-      ss += __shfl_xor_sync(0xffffffffu, ss, 2);
-      ss += __shfl_xor_sync(0xffffffffu, ss, 1);
-      pp[i] = ss;
-    }
-    const float sum = (pp[0] + pp[2]) + (pp[1] + pp[3]);
-    const float var = sum / (float)FA_HD + eps;
-    const float rstd = EAGER ? 1.0f / sqrtf(var) : rsqrtf(var);
-    float wf[16];
-    fa_unpack8(ldg_v4(w + 8 * j), wf);
-    fa_unpack8(ldg_v4(w + 64 + 8 * j), wf + 8);
-#pragma unroll
-    for (int d = 0; d < 16; ++d) x[d] = rbf(EAGER ? rbf(x[d] * rstd) * wf[d] : (x[d] * rstd) * wf[d]);
-  }
-#pragma unroll
-  for (int d = 0; d < 8; ++d) {
-    const float a = x[d], b = x[8 + d];
-    x[d] = rbf(rbf(a * c1[d]) + rbf(-b * s1[d]));          // rotate_half: first half pairs with -x2
-    x[8 + d] = rbf(rbf(b * c2[d]) + rbf(a * s2[d]));
-  }
-}
-
 template <int GROUP, bool EAGER>
 __global__ void __launch_bounds__(288, 2)
 fused_decode_attn_kernel(const FusedAttnParams p) {
@@ -112,6 +76,9 @@ fused_decode_attn_kernel(const FusedAttnParams p) {
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(Vs + FA_NSTAGE * stage_elems);
   uint64_t* empty_bar = full_bar + FA_NSTAGE;
   int* last_flag = reinterpret_cast<int*>(empty_bar + FA_NSTAGE);
+  __nv_bfloat16* q_s = reinterpret_cast<__nv_bfloat16*>(last_flag + 4);     // [heads][128] normed + rotated q
+  __nv_bfloat16* kn_s = q_s + p.num_heads * FA_HD;                          // [kvh][128] the new token's K
+  __nv_bfloat16* vn_s = kn_s + kv_dim;                                      // [kvh][128] the new token's V
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -158,7 +125,7 @@ fused_decode_attn_kernel(const FusedAttnParams p) {
     return;
   }
 
-  // =========================== consumer warp `warp` owns kv head `warp`
+  // =========================== consumer warps
   const int g = lane >> 3;        // token slot within a 4-token step
   const int j = lane & 7;         // which 16 head-dims: [8j,8j+8) and [64+8j,64+8j+8)
   const int head0 = warp * GROUP;
@@ -175,56 +142,90 @@ fused_decode_attn_kernel(const FusedAttnParams p) {
     return;
   }
 
-  // ---- cos/sin of this lane's 16 columns (fp32 angle -> bf16, as rotary_embedding.py:138-139)
-  float c1[8], s1[8], c2[8], s2[8];
+  // ---- prologue: the body of qknorm_rope_kvwrite_kernel (norm_rope.cu) for this one token, same lane
+  // mapping and arithmetic (lane l holds dims {2l, 2l+1, 64+2l, 64+2l+1}; a warp walks heads warp,
+  // warp+kvh, ...): q heads -> shared memory, and on the writer split k (normed + rotated) and v (raw)
+  // -> cache[slot] and shared memory.
+  {
+    float c1[2], s1[2], c2[2], s2[2];
 #pragma unroll
-  for (int d = 0; d < 8; ++d) {
-    const int fi = 8 * j + d;
-    const float f = __ldg(p.inv_freq + fi);
-    const int m1 = p.modality ? __ldg(p.modality + fi) : 0;
-    const float a1 = (float)__ldg(p.positions + (int64_t)m1 * p.pos_row_stride + row) * f;
-    c1[d] = rbf(cosf(a1) * p.attention_scaling);
-    s1[d] = rbf(sinf(a1) * p.attention_scaling);
-    const int m2 = p.modality ? __ldg(p.modality + FA_HD / 2 + fi) : 0;
-    if (m2 != m1) {
-      const float a2 = (float)__ldg(p.positions + (int64_t)m2 * p.pos_row_stride + row) * f;
-      c2[d] = rbf(cosf(a2) * p.attention_scaling);
-      s2[d] = rbf(sinf(a2) * p.attention_scaling);
-    } else {
-      c2[d] = c1[d]; s2[d] = s1[d];
+    for (int e = 0; e < 2; ++e) {
+      const int fi = 2 * lane + e;
+      const float f = __ldg(p.inv_freq + fi);
+      const int m1 = p.modality ? __ldg(p.modality + fi) : 0;
+      const float a1 = (float)__ldg(p.positions + (int64_t)m1 * p.pos_row_stride + row) * f;
+      c1[e] = rbf(cosf(a1) * p.attention_scaling);
+      s1[e] = rbf(sinf(a1) * p.attention_scaling);
+      const int m2 = p.modality ? __ldg(p.modality + FA_HD / 2 + fi) : 0;
+      if (m2 != m1) {
+        const float a2 = (float)__ldg(p.positions + (int64_t)m2 * p.pos_row_stride + row) * f;
+        c2[e] = rbf(cosf(a2) * p.attention_scaling);
+        s2[e] = rbf(sinf(a2) * p.attention_scaling);
+      } else {
+        c2[e] = c1[e]; s2[e] = s1[e];
+      }
+    }
+    const int slot = writer ? __ldg(p.slot_mapping + row) : -1;
+    const int total = p.num_heads + (writer ? kvh : 0);
+    for (int hh = warp; hh < total; hh += kvh) {
+      const bool is_k = hh >= p.num_heads;
+      const int h = is_k ? hh - p.num_heads : hh;
+      const __nv_bfloat16* src = is_k ? p.k + (int64_t)row * p.k_stride + h * FA_HD : p.q + (int64_t)row * p.q_stride + h * FA_HD;
+      const __nv_bfloat16* w = is_k ? p.k_w : p.q_w;
+      const uint32_t r1 = *reinterpret_cast<const uint32_t*>(src + 2 * lane);
+      const uint32_t r2 = *reinterpret_cast<const uint32_t*>(src + 64 + 2 * lane);
+      float x1[2] = {bf16lo(r1), bf16hi(r1)};
+      float x2[2] = {bf16lo(r2), bf16hi(r2)};
+      if (w) {
+        float ss = x1[0] * x1[0];
+        ss = fmaf(x1[1], x1[1], ss); ss = fmaf(x2[0], x2[0], ss); ss = fmaf(x2[1], x2[1], ss);
+        const float var = warp_sum(ss) / (float)FA_HD + p.eps;
+        const float rstd = EAGER ? 1.0f / sqrtf(var) : rsqrtf(var);
+        const uint32_t w1 = *reinterpret_cast<const uint32_t*>(w + 2 * lane);
+        const uint32_t w2 = *reinterpret_cast<const uint32_t*>(w + 64 + 2 * lane);
+        const float wf[4] = {bf16lo(w1), bf16hi(w1), bf16lo(w2), bf16hi(w2)};
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          x1[e] = rbf(EAGER ? rbf(x1[e] * rstd) * wf[e] : (x1[e] * rstd) * wf[e]);
+          x2[e] = rbf(EAGER ? rbf(x2[e] * rstd) * wf[2 + e] : (x2[e] * rstd) * wf[2 + e]);
+        }
+      }
+      float o1[2], o2[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        o1[e] = rbf(x1[e] * c1[e]) + rbf(-x2[e] * s1[e]);   // rotate_half: first half pairs with -x2
+        o2[e] = rbf(x2[e] * c2[e]) + rbf(x1[e] * s2[e]);
+      }
+      const uint32_t y1 = pack_bf16(o1[0], o1[1]), y2 = pack_bf16(o2[0], o2[1]);
+      __nv_bfloat16* dst = is_k ? kn_s + h * FA_HD : q_s + h * FA_HD;
+      *reinterpret_cast<uint32_t*>(dst + 2 * lane) = y1;
+      *reinterpret_cast<uint32_t*>(dst + 64 + 2 * lane) = y2;
+      if (is_k && slot >= 0) {
+        __nv_bfloat16* cd = p.k_cache + (int64_t)slot * kv_dim + h * FA_HD;
+        *reinterpret_cast<uint32_t*>(cd + 2 * lane) = y1;
+        *reinterpret_cast<uint32_t*>(cd + 64 + 2 * lane) = y2;
+      }
+    }
+    if (writer) {                                          // V goes to the cache untouched
+      const __nv_bfloat16* vs = p.v + (int64_t)row * p.v_stride;
+      for (int i = threadIdx.x; i < (kv_dim >> 3); i += kvh * 32) {
+        const uint4 vv = ldg_v4(vs + 8 * i);
+        *reinterpret_cast<uint4*>(vn_s + 8 * i) = vv;
+        if (slot >= 0) stg_v4(p.v_cache + (int64_t)slot * kv_dim + 8 * i, vv);
+      }
     }
   }
+  asm volatile("bar.sync 1, %0;" :: "r"(kvh * 32) : "memory");      // the consumer warps only
 
-  // ---- q heads: norm + rope in registers, pre-scaled for exp2
+  // ---- this warp's q heads from shared memory, pre-scaled for exp2
   float qv[GROUP][16];
 #pragma unroll
   for (int h = 0; h < GROUP; ++h) {
-    const __nv_bfloat16* qp = p.q + (int64_t)row * p.q_stride + (head0 + h) * FA_HD;
-    fa_unpack8(ldg_v4(qp + 8 * j), qv[h]);
-    fa_unpack8(ldg_v4(qp + 64 + 8 * j), qv[h] + 8);
-    head_norm_rope<EAGER>(qv[h], p.q_w, p.eps, j, c1, s1, c2, s2);
+    const __nv_bfloat16* qp = q_s + (head0 + h) * FA_HD;
+    fa_unpack8(*reinterpret_cast<const uint4*>(qp + 8 * j), qv[h]);
+    fa_unpack8(*reinterpret_cast<const uint4*>(qp + 64 + 8 * j), qv[h] + 8);
 #pragma unroll
     for (int d = 0; d < 16; ++d) qv[h][d] *= p.scale_log2;
-  }
-
-  // ---- the appended token: k head (norm + rope) and raw v head -> cache[slot] and registers
-  uint4 kn0 = make_uint4(0, 0, 0, 0), kn1 = kn0, vn0 = kn0, vn1 = kn0;
-  if (writer) {
-    float kf[16];
-    const __nv_bfloat16* kp = p.k + (int64_t)row * p.k_stride + warp * FA_HD;
-    fa_unpack8(ldg_v4(kp + 8 * j), kf);
-    fa_unpack8(ldg_v4(kp + 64 + 8 * j), kf + 8);
-    head_norm_rope<EAGER>(kf, p.k_w, p.eps, j, c1, s1, c2, s2);
-    kn0 = fa_pack8(kf); kn1 = fa_pack8(kf + 8);
-    const __nv_bfloat16* vp = p.v + (int64_t)row * p.v_stride + warp * FA_HD;
-    vn0 = ldg_v4(vp + 8 * j); vn1 = ldg_v4(vp + 64 + 8 * j);
-    const int slot = __ldg(p.slot_mapping + row);
-    if (slot >= 0 && g == 0) {
-      __nv_bfloat16* kd = p.k_cache + (int64_t)slot * kv_dim + warp * FA_HD;
-      __nv_bfloat16* vd = p.v_cache + (int64_t)slot * kv_dim + warp * FA_HD;
-      stg_v4(kd + 8 * j, kn0); stg_v4(kd + 64 + 8 * j, kn1);
-      stg_v4(vd + 8 * j, vn0); stg_v4(vd + 64 + 8 * j, vn1);
-    }
   }
 
   float m[GROUP], l[GROUP], acc[GROUP][16];
@@ -249,8 +250,12 @@ fused_decode_attn_kernel(const FusedAttnParams p) {
       if (g == 0) {
         __nv_bfloat16* kr = kt + (L - 1 - tok0) * kv_dim;
         __nv_bfloat16* vr = vt + (L - 1 - tok0) * kv_dim;
-        *reinterpret_cast<uint4*>(kr + 8 * j) = kn0; *reinterpret_cast<uint4*>(kr + 64 + 8 * j) = kn1;
-        *reinterpret_cast<uint4*>(vr + 8 * j) = vn0; *reinterpret_cast<uint4*>(vr + 64 + 8 * j) = vn1;
+        const __nv_bfloat16* kn = kn_s + warp * FA_HD;
+        const __nv_bfloat16* vn = vn_s + warp * FA_HD;
+        *reinterpret_cast<uint4*>(kr + 8 * j) = *reinterpret_cast<const uint4*>(kn + 8 * j);
+        *reinterpret_cast<uint4*>(kr + 64 + 8 * j) = *reinterpret_cast<const uint4*>(kn + 64 + 8 * j);
+        *reinterpret_cast<uint4*>(vr + 8 * j) = *reinterpret_cast<const uint4*>(vn + 8 * j);
+        *reinterpret_cast<uint4*>(vr + 64 + 8 * j) = *reinterpret_cast<const uint4*>(vn + 64 + 8 * j);
       }
       __syncwarp();
     }
@@ -399,15 +404,20 @@ fused_decode_attn_kernel(const FusedAttnParams p) {
   }
 }
 
-static size_t fa_smem_bytes(int kv_heads) {
-  return (size_t)2 * FA_NSTAGE * FA_TILE * kv_heads * FA_HD * 2 + 2 * FA_NSTAGE * sizeof(uint64_t) + 16;
+static size_t fa_smem_bytes(int kv_heads, int num_heads) {
+  return (size_t)2 * FA_NSTAGE * FA_TILE * kv_heads * FA_HD * 2 + 2 * FA_NSTAGE * sizeof(uint64_t) + 16 +
+         (size_t)(num_heads + 2 * kv_heads) * FA_HD * 2;
 }
 
-// split-KV factor: one wave of 2 CTAs per SM, at least 2 tiles per split
+// split-KV factor: one wave of 2 CTAs per SM, at least 8 tiles (64 tokens) of table capacity per split
 static int fa_choose_nsplit(int rows, int max_ctx) {
+  if (const char* e = getenv("B2TTS_FA_NSPLIT")) {             // experiments only
+    const int v = atoi(e);
+    if (v >= 1 && v <= 32) return v;
+  }
   const int max_tiles = (max_ctx + FA_TILE - 1) / FA_TILE;
   int n = (2 * sm_count()) / (rows > 0 ? rows : 1);
-  const int cap = (max_tiles + 1) / 2;
+  const int cap = max_tiles / 8;
   if (n > cap) n = cap;
   if (n < 1) n = 1;
   if (n > 32) n = 32;
@@ -494,7 +504,7 @@ extern "C" int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, cons
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(batch, p.nsplit, 1);
   cfg.blockDim = dim3(32 * (num_kv_heads + 1), 1, 1);
-  cfg.dynamicSmemBytes = fa_smem_bytes(num_kv_heads);
+  cfg.dynamicSmemBytes = fa_smem_bytes(num_kv_heads, num_heads);
   cfg.stream = static_cast<cudaStream_t>(stream);
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

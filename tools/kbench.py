@@ -105,6 +105,48 @@ def gemm_case(m, n, k, splits=0, pdl=False, epilogue=0, chain=16):
                       "cublas_us": round(ms_c * 1e3, 2), "cublas_GBps": round(gb_c, 1)}), flush=True)
 
 
+def fattn_case(b, l, layers=28, page=256, kvh=8, h=16, hd=128):
+    """Fused decode attention vs the three separate launches, `layers` launches per graph over different
+    caches (cold KV), uniform context l."""
+    pages_per = (l + page - 1) // page
+    npages = b * pages_per
+    caches = [(torch.randn(npages, page, kvh, hd, device=DEV, dtype=BF16),
+               torch.randn(npages, page, kvh, hd, device=DEV, dtype=BF16)) for _ in range(layers)]
+    bt = torch.randperm(npages, generator=torch.Generator().manual_seed(13)).to(torch.int32).view(b, pages_per).to(DEV)
+    lens = torch.full((b,), l, dtype=torch.int32, device=DEV)
+    slots = (bt[:, (l - 1) // page] * page + (l - 1) % page).to(torch.int32).contiguous()
+    qkv = torch.randn(b, (h + 2 * kvh) * hd, device=DEV, dtype=BF16)
+    q, k, v = qkv[:, :h * hd].view(b, h, hd), qkv[:, h * hd:(h + kvh) * hd].view(b, kvh, hd), qkv[:, (h + kvh) * hd:].view(b, kvh, hd)
+    w = torch.ones(hd, device=DEV, dtype=BF16)
+    inv_freq = (1.0 / (1e6 ** (torch.arange(0, hd, 2, device=DEV).float() / hd))).contiguous()
+    pos = (lens.long() - 1).contiguous()
+    max_ctx = pages_per * page
+    ws = nat.fused_decode_attn_workspace(b, h, hd, max_ctx, DEV)
+    ws2 = torch.empty(max(16, nat.paged_attn_decode_workspace_bytes(b, h, hd, max_ctx)), dtype=torch.uint8, device=DEV)
+    out = torch.empty(b, h, hd, device=DEV, dtype=BF16)
+
+    def fused():
+        for kc, vc in caches:
+            nat.fused_decode_attn(q, k, v, w, w, 1e-6, pos, inv_freq, slots, kc, vc, bt, lens, hd ** -0.5, max_ctx, ws, out=out)
+
+    def separate():
+        for kc, vc in caches:
+            qr, _ = nat.qknorm_rope_kvwrite(q, k, v, w, w, 1e-6, pos, inv_freq, slot_mapping=slots, k_cache=kc, v_cache=vc,
+                                            want_k_out=False)
+            nat.paged_attn_decode(qr, kc, vc, bt, lens, hd ** -0.5, max_ctx, out=out, workspace=ws2)
+    res = {}
+    for name, fn in (("fused", fused), ("separate", separate)):
+        fn(); torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        res[name] = time_ms(lambda i: g.replay()) / layers * 1e3
+    alg = float(b * (4096 * l + 8192))
+    print(json.dumps({"kernel": "fused_decode_attn", "B": b, "L": l, "fused_us": round(res["fused"], 2),
+                      "separate_us": round(res["separate"], 2), "fused_GBps": round(alg / res["fused"] / 1e3, 1),
+                      "nsplit_env": os.environ.get("B2TTS_FA_NSPLIT")}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("what")
@@ -123,6 +165,10 @@ def main():
                 if s_ and (s_ > k // 64):
                     continue
                 gemm_case(m, n, k, splits=s_, pdl=bool(a.pdl))
+    if a.what == "fattn":
+        for c in a.cases.split(","):
+            b, l = map(int, c.split(":"))
+            fattn_case(b, l, layers=5 if l <= 32 else 28)
     if a.what == "attn":
         for c in a.cases.split(","):
             b, l = map(int, c.split(":"))
