@@ -243,6 +243,32 @@ B2TTS_API int    b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const
                                       const void* norm_weight, const float* ssq_in, int ssq_in_slots, float eps,
                                       float* ssq_out, void* stream);
 
+/* ---- a7 x 4 in one launch: the persistent GEMM chain of the decoder layer ------------------------------------
+ * replaces the four dependent projections between two attention calls
+ *     o_proj (+ residual add) -> gate_up_proj (post_attention_layernorm in, SiLU*mul out) -> down_proj (+ residual add)
+ *     -> the next layer's qkv_proj (input_layernorm in)                      models/qwen3_tts_share.py:163-176
+ * with ONE persistent kernel (one CTA per SM) whose weight stream never stops at a GEMM boundary: a producer
+ * thread keeps a deep shared-memory ring of packed weight tiles full across the whole chain while the CTAs
+ * reduce split-K partials through L2 and cross a grid barrier between GEMMs.  Every op is a b2tts_gemm_norm_bf16
+ * (same packed weights, epilogues, fused input norm and rounding points); op i+1 may read what op i wrote
+ * (x, residual, ssq_in).  ssq_out of an op has b2tts_gemm_chain_ssq_slots(n) = n/16 slots per row.
+ * 1 <= nops <= 4, 1 <= m <= 128.  workspace: b2tts_gemm_chain_workspace_bytes(...) bytes, ZERO-FILLED once by the
+ * caller (the kernel leaves its barrier counters zero); one workspace must not be used by two launches that
+ * can run concurrently.  The grid needs every SM of the device: do not run two chains concurrently. */
+typedef struct b2tts_gemm_op {
+  const void* x;            int64_t x_row_stride;         /* [m, k] bf16 */
+  const void* w_packed;                                   /* b2tts_gemm_pack_weight image of W[n, k] */
+  const void* residual;     int64_t residual_row_stride;  /* B2TTS_GEMM_RESIDUAL */
+  void* out;                int64_t out_row_stride;       /* [m, n] (or [m, n/2] for SiLU*mul); may alias residual */
+  const void* norm_weight;  const float* ssq_in;          /* fused input RMSNorm (or NULL) */
+  float* ssq_out;                                         /* [m, n/16] partial row sums of squares (or NULL) */
+  int n, k, epilogue, ssq_in_slots;
+} b2tts_gemm_op;
+B2TTS_API int    b2tts_gemm_chain_ssq_slots(int n);
+B2TTS_API size_t b2tts_gemm_chain_workspace_bytes(int m, const int* n, const int* k, int nops);
+B2TTS_API int    b2tts_gemm_chain(const b2tts_gemm_op* ops, int nops, int m, float eps, int rounding,
+                                  void* workspace, size_t workspace_bytes, int pdl, void* stream);
+
 /* ---- a5 + a4 + a1 + a2 in one launch: the decode step of Qwen3TTSAttention.forward ------------------------
  * replaces q_norm, k_norm, rotary_emb, store_kvcache and flash_attn_with_kvcache as called per decode token
  *                                       models/qwen3_tts_share.py:96-109, layers/attention.py:33-54, 92-95

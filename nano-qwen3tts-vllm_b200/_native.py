@@ -66,6 +66,9 @@ def _load():
         "b2tts_fused_decode_attn": (I, [P, L, P, L, P, L, P, P, F, P, L, P, P, F, P, P, P, P, I, P, P, P, Z,
                                         I, I, I, I, I, F, I, I, I, P]),
         "b2tts_gemm_norm_bf16": (I, [P, L, P, P, P, L, P, L, I, I, I, I, I, I, I, P, P, I, F, P, P]),
+        "b2tts_gemm_chain_ssq_slots": (I, [I]),
+        "b2tts_gemm_chain_workspace_bytes": (Z, [I, P, P, I]),
+        "b2tts_gemm_chain": (I, [P, I, I, F, I, P, Z, I, P]),
     }
     for name, (res, args) in sig.items():
         if not hasattr(lib, name):
@@ -435,3 +438,70 @@ def gemm_bf16(x, packed, n, bias=None, residual=None, epilogue=GEMM_BIAS, roundi
                                         int(rounding), int(splits), int(bool(pdl)), _ptr(norm_weight), _ptr(ssq_in),
                                         slots_in, float(eps), _ptr(ssq_out), _stream()), "gemm_norm_bf16")
     return out
+
+
+# ------------------------------------------------------------------------------------------ a7 x 4: GEMM chain
+class GemmOp(ctypes.Structure):
+    """``b2tts_gemm_op`` (include/b200tts.h)."""
+    _fields_ = [("x", c_void_p), ("x_row_stride", c_int64), ("w_packed", c_void_p),
+                ("residual", c_void_p), ("residual_row_stride", c_int64),
+                ("out", c_void_p), ("out_row_stride", c_int64),
+                ("norm_weight", c_void_p), ("ssq_in", c_void_p), ("ssq_out", c_void_p),
+                ("n", c_int), ("k", c_int), ("epilogue", c_int), ("ssq_in_slots", c_int)]
+
+
+GEMM_CHAIN_MAX_OPS = 4
+
+
+def gemm_chain_ssq_slots(n: int) -> int:
+    return int(_load().b2tts_gemm_chain_ssq_slots(int(n)))
+
+
+def gemm_chain_workspace(m: int, shapes, device) -> torch.Tensor:
+    """Zero-filled workspace for chains of up to ``m`` rows whose ops have any of the (n, k) ``shapes``."""
+    need = 0
+    for i in range(0, len(shapes), GEMM_CHAIN_MAX_OPS):
+        sub = shapes[i:i + GEMM_CHAIN_MAX_OPS]
+        ns = (c_int * len(sub))(*[int(v[0]) for v in sub])
+        ks = (c_int * len(sub))(*[int(v[1]) for v in sub])
+        got = int(_load().b2tts_gemm_chain_workspace_bytes(int(m), ns, ks, len(sub)))
+        if got == 0:
+            raise RuntimeError(f"libb200tts gemm_chain_workspace: unsupported m={m} shapes={sub}")
+        need = max(need, got)
+    return torch.zeros(need + 16, dtype=torch.uint8, device=device)
+
+
+def gemm_chain(ops: list[dict], m: int, workspace: torch.Tensor, eps: float = 1e-6, rounding: int = ROUND_EAGER,
+               pdl: bool = True):
+    """Up to 4 dependent GEMMs in one persistent launch (``b2tts_gemm_chain``).  Each op is a dict with
+    ``x`` [m, k] bf16, ``packed`` (``gemm_pack_weight`` image), ``n``, ``out``, and optionally ``residual``,
+    ``epilogue``, ``norm_weight`` + ``ssq_in`` [m, slots] fp32, ``ssq_out`` [m, n/16] fp32."""
+    arr = (GemmOp * len(ops))()
+    keep = []
+    for i, o in enumerate(ops):
+        x = o["x"]
+        _cuda(x, BF16, "x")
+        if x.stride(1) != 1:
+            x = x.contiguous()
+            keep.append(x)
+        out = o["out"]
+        _cuda(out, BF16, "out")
+        res = o.get("residual")
+        ssq_in, ssq_out = o.get("ssq_in"), o.get("ssq_out")
+        n, k = int(o["n"]), int(x.shape[1])
+        if ssq_out is not None and (ssq_out.dtype != F32 or not ssq_out.is_contiguous() or ssq_out.shape[1] != n // 16):
+            raise ValueError(f"gemm_chain op {i}: ssq_out must be a contiguous [>=m, {n // 16}] fp32 tensor")
+        if ssq_in is not None and (ssq_in.dtype != F32 or not ssq_in.is_contiguous()):
+            raise ValueError(f"gemm_chain op {i}: ssq_in must be a contiguous [>=m, slots] fp32 tensor")
+        a = arr[i]
+        a.x, a.x_row_stride = x.data_ptr(), x.stride(0)
+        a.w_packed = o["packed"].data_ptr()
+        a.residual, a.residual_row_stride = _ptr(res), (res.stride(0) if res is not None else 0)
+        a.out, a.out_row_stride = out.data_ptr(), out.stride(0)
+        a.norm_weight = _ptr(o.get("norm_weight"))
+        a.ssq_in, a.ssq_out = _ptr(ssq_in), _ptr(ssq_out)
+        a.n, a.k, a.epilogue = n, k, int(o.get("epilogue", GEMM_BIAS))
+        a.ssq_in_slots = int(ssq_in.shape[1]) if ssq_in is not None else 0
+    _check(_load().b2tts_gemm_chain(ctypes.byref(arr), len(ops), int(m), float(eps), int(rounding),
+                                    workspace.data_ptr(), workspace.numel() * workspace.element_size(),
+                                    int(bool(pdl)), _stream()), "gemm_chain")

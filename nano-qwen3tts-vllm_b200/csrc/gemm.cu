@@ -749,6 +749,502 @@ extern "C" int b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const v
                        ssq_out, stream);
 }
 
+// =====================================================================================================
+// Persistent GEMM CHAIN: up to 4 dependent projections of the decoder layer in ONE launch
+// (o_proj + residual -> gate_up (+ post-attention RMSNorm in, SiLU*mul out) -> down_proj + residual ->
+// the NEXT layer's qkv_proj (+ input RMSNorm in); models/qwen3_tts_share.py:163-176 of the reference).
+//
+// Why: at decode batch sizes every projection is a few microseconds of weight streaming wrapped in
+// ~5 us of dependent latencies (kernel boundary, x fetch, accumulator drain, split-K exchange,
+// epilogue), during which HBM idles: a per-GEMM launch reaches < 30 % of the HBM roofline however
+// well its inner loop streams.  Weights do not depend on activations, so here ONE persistent CTA per SM
+// runs a static schedule over all GEMMs of the chain and its producer thread keeps a deep ring of
+// weight tiles (10 x 16 KiB per SM, 23 MB chip-wide) full ACROSS GEMM boundaries: while the CTAs
+// exchange split-K partials and cross the grid barrier of GEMM i, HBM is already streaming GEMM i+1.
+//
+//   warp 0   W producer: 16 KiB bulk copies of packed weight tiles, runs ahead through the whole chain
+//   warp 1   MMA issuer: tcgen05.mma into one of two TMEM accumulators (the drain of item j overlaps
+//            the MMAs of item j+1)
+//   warp 2   x producer: 2-D tensor-map copies of the activation tile (SWIZZLE_128B = UMMA B operand);
+//            starts GEMM i once grid barrier B(i-1) says its input rows are complete
+//   warps 3-6  fused input RMSNorm on the landed x tile; accumulator drain (tcgen05.ld) to the fp32
+//            split-K scratch in L2; after grid barrier A(i) the REDUCE phase: every (row, 16 features)
+//            unit of the output is summed over the splits in a fixed order (deterministic), gets the
+//            fused epilogue (residual add / SiLU*mul / plain) and its sum of squares, then barrier B(i).
+// Work item = (128-feature tile, K split); items are dealt round-robin to the CTAs; the split count
+// per GEMM balances k-blocks per CTA.  Grid barriers are monotonic counters in the workspace, reset by
+// the last CTA to leave, so a CUDA graph can replay the launch without a memset.
+// Rounding points are those of gemm_stream_kernel (bf16(residual + bf16(acc)), norm of the rounded sum).
+namespace b2 {
+constexpr int C_MAX_OPS = 4;
+constexpr int C_THREADS = 224;
+constexpr int C_EPI0 = 96;                       // first epilogue thread
+constexpr int C_UNIT = 16;                       // features per reduce unit = one ssq slot
+constexpr int C_SYNC_WORDS = 16;                 // 2 * C_MAX_OPS barrier counters + exit counter, padded
+
+struct ChainOp {
+  const uint8_t* wp;
+  const __nv_bfloat16* norm_w;
+  const float* ssq_in;
+  const __nv_bfloat16* res;
+  __nv_bfloat16* out;
+  float* ssq_out;
+  int64_t res_stride, out_stride;
+  int n, kblocks, n_tiles, splits, epilogue, ssq_in_slots, ssq_lanes, k;
+};
+
+struct ChainParams {
+  ChainOp op[C_MAX_OPS];
+  int nops, m, mpad, tmem_cols, nw, nx, rounding;
+  float eps;
+  float* partial;                                // [splits][n][mpad] fp32, reused by every op
+  unsigned* sync;                                // C_SYNC_WORDS counters, zero between launches
+  unsigned long long* trace;                     // debug: 8 globaltimer stamps per (CTA, op) (null = off)
+};
+#define C_TRACE(op_i, slot) do { if (p.trace && te == 0) p.trace[((int64_t)cta * C_MAX_OPS + (op_i)) * 8 + (slot)] = gtimer(); } while (0)
+
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void grid_wait(const unsigned* ctr, unsigned target) {
+  while (ld_acquire_gpu(ctr) < target) { }
+}
+__device__ __forceinline__ void grid_arrive(unsigned* ctr) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(ctr) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
+
+__global__ void __launch_bounds__(C_THREADS, 1)
+gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
+                  const __grid_constant__ CUtensorMap tm2, const __grid_constant__ CUtensorMap tm3) {
+  extern __shared__ uint8_t smem_dyn[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
+  const int mpad = p.mpad, NW = p.nw, NX = p.nx;
+  const int xstage = mpad * 128;
+  uint8_t* wring = smem;
+  uint8_t* xring = wring + NW * G_WTILE_BYTES;
+  uint64_t* wfull = reinterpret_cast<uint64_t*>(xring + NX * xstage);
+  uint64_t* wempty = wfull + G_MAX_STAGES;
+  uint64_t* xraw = wempty + G_MAX_STAGES;
+  uint64_t* xfull = xraw + G_MAX_STAGES;
+  uint64_t* xempty = xfull + G_MAX_STAGES;
+  uint64_t* accfull = xempty + G_MAX_STAGES;
+  uint64_t* accempty = accfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accempty + 2);
+  float* rstd_s = reinterpret_cast<float*>(tmem_slot + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int G = gridDim.x;
+  const int cta = blockIdx.x;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NW; ++s) { mbar_init(wfull + s, 1); mbar_init(wempty + s, 1); }
+    for (int s = 0; s < NX; ++s) { mbar_init(xraw + s, 1); mbar_init(xfull + s, 4); mbar_init(xempty + s, 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(accfull + b, 1); mbar_init(accempty + b, 4); }
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // =========================== W producer: never waits for activations
+    if (lane == 0) {
+      uint32_t j = 0;
+      for (int i = 0; i < p.nops; ++i) {
+        const ChainOp& op = p.op[i];
+        const int S = op.splits, items = op.n_tiles * S;
+        for (int t = cta; t < items; t += G) {
+          const int tile = t / S, s = t - tile * S;
+          const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
+          const uint8_t* src = op.wp + ((int64_t)tile * op.kblocks + kb0) * G_WTILE_BYTES;
+          for (int kb = kb0; kb < kb1; ++kb, ++j, src += G_WTILE_BYTES) {
+            const uint32_t slot = j % NW;
+            mbar_wait(wempty + slot, ((j / NW) & 1) ^ 1);
+            mbar_expect_tx(wfull + slot, G_WTILE_BYTES);
+            bulk_g2s(wring + slot * G_WTILE_BYTES, src, G_WTILE_BYTES, wfull + slot);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // =========================== MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(mpad);
+      uint32_t j = 0, it = 0;
+      for (int i = 0; i < p.nops; ++i) {
+        const ChainOp& op = p.op[i];
+        const int S = op.splits, items = op.n_tiles * S;
+        for (int t = cta; t < items; t += G, ++it) {
+          const int tile = t / S, s = t - tile * S;
+          const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
+          const uint32_t b = it & 1;
+          mbar_wait(accempty + b, ((it >> 1) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_addr = tmem_base + b * (uint32_t)mpad;
+          for (int kb = kb0; kb < kb1; ++kb, ++j) {
+            const uint32_t sw = j % NW, sx = j % NX;
+            mbar_wait(wfull + sw, (j / NW) & 1);
+            mbar_wait(xfull + sx, (j / NX) & 1);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(wring + sw * G_WTILE_BYTES);
+            const uint32_t b_addr = smem_u32(xring + sx * xstage);
+#pragma unroll
+            for (int k = 0; k < G_BK / 16; ++k)
+              umma_bf16(d_addr, umma_desc_sw128(a_addr + k * 32), umma_desc_sw128(b_addr + k * 32), idesc,
+                        (uint32_t)((kb > kb0) || (k > 0)));
+            umma_commit(wempty + sw);
+            umma_commit(xempty + sx);
+          }
+          umma_commit(accfull + b);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2) {
+    // =========================== x producer
+    if (lane == 0) {
+      uint32_t j = 0;
+      const uint32_t xbytes = (uint32_t)xstage;
+      for (int i = 0; i < p.nops; ++i) {
+        const ChainOp& op = p.op[i];
+        if (i == 0) {
+          pdl_wait();
+        } else {
+          grid_wait(p.sync + 2 * (i - 1) + 1, (unsigned)G);
+          fence_proxy_async_all();
+        }
+        const CUtensorMap* tm = i == 0 ? &tm0 : i == 1 ? &tm1 : i == 2 ? &tm2 : &tm3;
+        const int S = op.splits, items = op.n_tiles * S;
+        for (int t = cta; t < items; t += G) {
+          const int tile = t / S, s = t - tile * S;
+          const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
+          for (int kb = kb0; kb < kb1; ++kb, ++j) {
+            const uint32_t slot = j % NX;
+            mbar_wait(xempty + slot, ((j / NX) & 1) ^ 1);
+            mbar_expect_tx(xraw + slot, xbytes);
+            tma_load_2d(xring + slot * xstage, tm, kb * G_BK, 0, xraw + slot);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // =========================== epilogue warps: x norm hop, accumulator drain, reduce phase
+    const int te = threadIdx.x - C_EPI0;
+    const int q = warp & 3;                     // TMEM lane quarter this warp may read
+    const bool eager = p.rounding == B2TTS_ROUND_EAGER;
+    uint32_t j = 0, it = 0;
+    C_TRACE(0, 0);
+    pdl_wait();
+    for (int i = 0; i < p.nops; ++i) {
+      const ChainOp& op = p.op[i];
+      if (i > 0) {
+        if (te == 0) grid_wait(p.sync + 2 * (i - 1) + 1, (unsigned)G);
+        epi_bar();
+      }
+      C_TRACE(i, 1);
+      const bool normed = op.norm_w != nullptr;
+      if (normed) {
+        const int GL = op.ssq_lanes, rows_per_pass = 128 / GL;
+        const int gl = te % GL, chunk = op.ssq_in_slots / GL;
+        for (int r0 = 0; r0 < mpad; r0 += rows_per_pass) {
+          const int r = r0 + te / GL;
+          float sum = 0.f;
+          if (r < p.m) {
+            const float* src = op.ssq_in + (int64_t)r * op.ssq_in_slots + gl * chunk;
+            if ((chunk & 3) == 0) {
+              for (int c = 0; c < chunk; c += 4) {
+                const float4 v = __ldcg(reinterpret_cast<const float4*>(src + c));
+                sum += v.x; sum += v.y; sum += v.z; sum += v.w;
+              }
+            } else {
+              for (int c = 0; c < chunk; ++c) sum += __ldcg(src + c);
+            }
+          }
+          for (int o = 1; o < GL; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+          if (r < mpad && gl == 0) {
+            const float var = sum / (float)op.k + p.eps;
+            rstd_s[r] = eager ? 1.0f / sqrtf(var) : rsqrtf(var);
+          }
+        }
+        epi_bar();
+      }
+      C_TRACE(i, 2);
+      const int S = op.splits, items = op.n_tiles * S;
+      for (int t = cta; t < items; t += G, ++it) {
+        const int tile = t / S, s = t - tile * S;
+        const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
+        for (int kb = kb0; kb < kb1; ++kb, ++j) {
+          const uint32_t sx = j % NX;
+          mbar_wait(xraw + sx, (j / NX) & 1);
+          if (kb == kb0 && t == cta) C_TRACE(i, 3);
+          if (normed) {
+            uint8_t* xs = xring + sx * xstage;
+            const uint4 wv = ldg_v4(op.norm_w + (int64_t)kb * G_BK + (te & 7) * 8);
+            for (int idx = te; idx < mpad * 8; idx += 128) {
+              const int r = idx >> 3, c = idx & 7;
+              if (r < p.m) {
+                uint4* cell = reinterpret_cast<uint4*>(xs + r * 128 + ((c ^ (r & 7)) << 4));
+                *cell = norm8(*cell, wv, rstd_s[r], eager);
+              }
+            }
+            fence_proxy_async();
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(xfull + sx);
+        }
+        // drain the accumulator of this item to the split-K scratch: thread = feature row, mpad columns
+        const uint32_t b = it & 1;
+        mbar_wait(accfull + b, (it >> 1) & 1);
+        tc_fence_after();
+        float* row = p.partial + ((int64_t)s * op.n + (int64_t)tile * G_BN + q * 32 + lane) * mpad;
+        for (int c0 = 0; c0 < mpad; c0 += 64) {
+          uint32_t v[64];
+          const int nq = min(4, (mpad - c0) >> 4);
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq)
+            if (qq < nq) tmem_ld16_nowait(tmem_base + ((uint32_t)(q * 32) << 16) + b * (uint32_t)mpad + (uint32_t)(c0 + 16 * qq), v + 16 * qq);
+          tmem_ld_wait();
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq)
+            if (qq < nq) {
+#pragma unroll
+              for (int jj = 0; jj < 16; jj += 4)
+                __stcg(reinterpret_cast<uint4*>(row + c0 + 16 * qq + jj),
+                       make_uint4(v[16 * qq + jj], v[16 * qq + jj + 1], v[16 * qq + jj + 2], v[16 * qq + jj + 3]));
+            }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(accempty + b);
+      }
+      // ---- grid barrier A(i): every partial of op i is in L2
+      C_TRACE(i, 4);
+      __threadfence();
+      epi_bar();
+      if (te == 0) {
+        grid_arrive(p.sync + 2 * i);
+        grid_wait(p.sync + 2 * i, (unsigned)G);
+      }
+      epi_bar();
+      C_TRACE(i, 5);
+      if (i == p.nops - 1) pdl_launch();
+      // ---- reduce phase: unit = (row m, 16 features); lanes run along m (coalesced scratch reads)
+      {
+        const int M = p.m, N = op.n;
+        const int units = M * (N / C_UNIT);
+        const int slots = N / C_UNIT;
+        for (int u = cta * 128 + te; u < units; u += G * 128) {
+          const int ch = u / M, m = u - ch * M;
+          float qsum = 0.f;
+#pragma unroll
+          for (int g8 = 0; g8 < C_UNIT / 8; ++g8) {
+            const int n = ch * C_UNIT + g8 * 8;
+            float acc[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+            for (int sp = 0; sp < S; ++sp) {
+              const float* src = p.partial + ((int64_t)sp * N + n) * mpad + m;
+#pragma unroll
+              for (int e = 0; e < 8; ++e) acc[e] += __ldcg(src + e * mpad);
+            }
+            if (op.epilogue == B2TTS_GEMM_SILU_MUL) {
+              float o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float gt = rbf(acc[e]), up = rbf(acc[4 + e]);
+                o[e] = eager ? rbf(gsilu_f(gt)) * up : gsilu_f(gt) * up;
+              }
+              uint2 w;
+              w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
+              stg_v2(op.out + (int64_t)m * op.out_stride + (n >> 1), w);
+              continue;
+            }
+            if (op.epilogue == B2TTS_GEMM_RESIDUAL) {
+              const uint4 rw = __ldcg(reinterpret_cast<const uint4*>(op.res + (int64_t)m * op.res_stride + n));
+              acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
+              acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
+              acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
+              acc[6] = rbf(acc[6]) + bf16lo(rw.w); acc[7] = rbf(acc[7]) + bf16hi(rw.w);
+            }
+            uint4 w;
+            w.x = pack_bf16(acc[0], acc[1]); w.y = pack_bf16(acc[2], acc[3]);
+            w.z = pack_bf16(acc[4], acc[5]); w.w = pack_bf16(acc[6], acc[7]);
+            stg_v4(op.out + (int64_t)m * op.out_stride + n, w);
+            qsum = fmaf(bf16lo(w.x), bf16lo(w.x), qsum); qsum = fmaf(bf16hi(w.x), bf16hi(w.x), qsum);
+            qsum = fmaf(bf16lo(w.y), bf16lo(w.y), qsum); qsum = fmaf(bf16hi(w.y), bf16hi(w.y), qsum);
+            qsum = fmaf(bf16lo(w.z), bf16lo(w.z), qsum); qsum = fmaf(bf16hi(w.z), bf16hi(w.z), qsum);
+            qsum = fmaf(bf16lo(w.w), bf16lo(w.w), qsum); qsum = fmaf(bf16hi(w.w), bf16hi(w.w), qsum);
+          }
+          if (op.ssq_out) op.ssq_out[(int64_t)m * slots + ch] = qsum;
+        }
+      }
+      // ---- barrier B(i): the rows op i+1 reads are complete (arrive only; the readers wait)
+      C_TRACE(i, 6);
+      if (i + 1 < p.nops) {
+        __threadfence();
+        epi_bar();
+        if (te == 0) grid_arrive(p.sync + 2 * i + 1);
+      }
+    }
+  }
+  pdl_launch();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+  // the last CTA to leave resets the barrier counters: every role of every CTA is past every wait
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned old = atomicAdd(p.sync + 2 * C_MAX_OPS, 1u);
+    if (old == (unsigned)G - 1) {
+      for (int k = 0; k < 2 * C_MAX_OPS + 1; ++k) p.sync[k] = 0u;
+      __threadfence();
+    }
+  }
+}
+
+static size_t chain_smem_bytes(int mpad, int nw, int nx) {
+  return (size_t)nw * G_WTILE_BYTES + (size_t)nx * mpad * 128 + (5 * G_MAX_STAGES + 4) * 8 + 16 + (size_t)mpad * 4 + 1024;
+}
+
+// K split of one chain op: minimise k-blocks on the busiest CTA (+ a term for the reduce cost of many splits)
+static int chain_choose_splits(int n_tiles, int kblocks, int ctas) {
+  if (const char* e = getenv("B2TTS_CHAIN_SPLITS")) {            // experiments only
+    const int v = atoi(e);
+    if (v >= 1 && v <= 16 && v <= kblocks) return v;
+  }
+  int best = 1;
+  float best_cost = 1e30f;
+  for (int s = 1; s <= 16 && s <= kblocks; ++s) {
+    const int rounds = (n_tiles * s + ctas - 1) / ctas;
+    const float cost = (float)(rounds * ((kblocks + s - 1) / s)) + 0.25f * (float)s;
+    if (cost < best_cost - 1e-6f) { best_cost = cost; best = s; }
+  }
+  return best;
+}
+}  // namespace b2
+
+extern "C" B2TTS_API int b2tts_gemm_chain_ssq_slots(int n) { return n > 0 && n % b2::C_UNIT == 0 ? n / b2::C_UNIT : 0; }
+
+extern "C" B2TTS_API size_t b2tts_gemm_chain_workspace_bytes(int m, const int* n, const int* k, int nops) {
+  using namespace b2;
+  if (m < 1 || m > G_MAX_M || nops < 1 || nops > C_MAX_OPS || !n || !k) return 0;
+  const int mpad = (m + 15) & ~15;
+  size_t part = 0;
+  for (int i = 0; i < nops; ++i) {
+    if (n[i] <= 0 || k[i] <= 0 || n[i] % G_BN || k[i] % G_BK) return 0;
+    const int s = 16 < k[i] / G_BK ? 16 : k[i] / G_BK;           // upper bound of any split choice
+    const size_t b = (size_t)s * n[i] * mpad * 4;
+    if (b > part) part = b;
+  }
+  return C_SYNC_WORDS * 4 + 192 + part;
+}
+
+extern "C" B2TTS_API int b2tts_gemm_chain(const b2tts_gemm_op* ops, int nops, int m, float eps, int rounding,
+                                          void* workspace, size_t workspace_bytes, int pdl, void* stream) {
+  using namespace b2;
+  const char* what = "gemm_chain";
+  B2_REQUIRE(ops && nops >= 1 && nops <= C_MAX_OPS, B2TTS_EINVAL, "%s: 1..%d ops", what, C_MAX_OPS);
+  B2_REQUIRE(m >= 0 && m <= G_MAX_M, B2TTS_EUNSUPPORTED, "%s: m=%d (0..%d)", what, m, G_MAX_M);
+  if (m == 0) return B2TTS_OK;
+  B2_REQUIRE(workspace && aligned16(workspace), B2TTS_EINVAL, "%s: workspace", what);
+  ChainParams p{};
+  p.nops = nops; p.m = m; p.mpad = (m + 15) & ~15; p.rounding = rounding; p.eps = eps;
+  p.tmem_cols = 32;
+  while (p.tmem_cols < 2 * p.mpad) p.tmem_cols <<= 1;
+  p.nx = p.mpad <= 64 ? 4 : 3;
+  p.nw = 10;
+  while (p.nw > 4 && chain_smem_bytes(p.mpad, p.nw, p.nx) > 227 * 1024) --p.nw;
+  if (const char* e = getenv("B2TTS_CHAIN_NW")) {                // experiments only
+    const int v = atoi(e);
+    if (v >= 2 && v <= G_MAX_STAGES && chain_smem_bytes(p.mpad, v, p.nx) <= 227 * 1024) p.nw = v;
+  }
+  const int ctas = sm_count();
+  CUtensorMap tmaps[C_MAX_OPS];
+  size_t part = 0;
+  for (int i = 0; i < nops; ++i) {
+    const b2tts_gemm_op& o = ops[i];
+    B2_REQUIRE(o.x && o.w_packed && o.out, B2TTS_EINVAL, "%s: op %d null pointer", what, i);
+    B2_REQUIRE(o.n > 0 && o.k > 0 && o.n % G_BN == 0 && o.k % G_BK == 0, B2TTS_EUNSUPPORTED,
+               "%s: op %d n=%d (multiple of %d), k=%d (multiple of %d)", what, i, o.n, G_BN, o.k, G_BK);
+    B2_REQUIRE(o.epilogue == B2TTS_GEMM_BIAS || o.epilogue == B2TTS_GEMM_RESIDUAL || o.epilogue == B2TTS_GEMM_SILU_MUL,
+               B2TTS_EINVAL, "%s: op %d epilogue %d", what, i, o.epilogue);
+    B2_REQUIRE(o.epilogue != B2TTS_GEMM_RESIDUAL || o.residual, B2TTS_EINVAL, "%s: op %d residual epilogue without residual", what, i);
+    B2_REQUIRE(aligned16(o.x) && aligned16(o.w_packed) && aligned16(o.out) && o.x_row_stride % 8 == 0 &&
+                   o.out_row_stride % 4 == 0 && (o.epilogue == B2TTS_GEMM_SILU_MUL || o.out_row_stride % 8 == 0) &&
+                   (!o.residual || (aligned16(o.residual) && o.residual_row_stride % 8 == 0)),
+               B2TTS_EALIGN, "%s: op %d pointers / strides must be 16-byte aligned", what, i);
+    B2_REQUIRE(!o.norm_weight || (o.ssq_in && o.ssq_in_slots > 0 && aligned16(o.norm_weight) && aligned16(o.ssq_in)),
+               B2TTS_EINVAL, "%s: op %d fused norm needs ssq_in", what, i);
+    B2_REQUIRE(!o.ssq_out || o.epilogue != B2TTS_GEMM_SILU_MUL, B2TTS_EINVAL, "%s: op %d ssq_out with SiLU*mul", what, i);
+    ChainOp& c = p.op[i];
+    c.wp = static_cast<const uint8_t*>(o.w_packed);
+    c.norm_w = static_cast<const __nv_bfloat16*>(o.norm_weight);
+    c.ssq_in = o.ssq_in;
+    c.res = static_cast<const __nv_bfloat16*>(o.residual);
+    c.out = static_cast<__nv_bfloat16*>(o.out);
+    c.ssq_out = o.ssq_out;
+    c.res_stride = o.residual_row_stride; c.out_stride = o.out_row_stride;
+    c.n = o.n; c.k = o.k; c.kblocks = o.k / G_BK; c.n_tiles = o.n / G_BN;
+    c.splits = chain_choose_splits(c.n_tiles, c.kblocks, ctas);
+    c.epilogue = o.epilogue;
+    c.ssq_in_slots = o.ssq_in_slots;
+    c.ssq_lanes = 1;
+    if (o.norm_weight) {
+      int g = 128 / p.mpad;
+      if (g > 8) g = 8;
+      if (g < 1) g = 1;
+      while (g > 1 && (o.ssq_in_slots % g)) g >>= 1;
+      while (g > 1 && ((o.ssq_in_slots / g) % 4)) g >>= 1;
+      c.ssq_lanes = g;
+      B2_REQUIRE(o.ssq_in_slots % 4 == 0 || g == 1, B2TTS_EALIGN, "%s: op %d ssq_in_slots %d", what, i, o.ssq_in_slots);
+    }
+    const size_t b = (size_t)c.splits * c.n * p.mpad * 4;
+    if (b > part) part = b;
+    int rc = make_x_tensor_map(&tmaps[i], o.x, o.x_row_stride, m, o.k, p.mpad, what);
+    if (rc) return rc;
+  }
+  for (int i = nops; i < C_MAX_OPS; ++i) tmaps[i] = tmaps[0];
+  B2_REQUIRE(workspace_bytes >= C_SYNC_WORDS * 4 + 192 + part, B2TTS_EINVAL, "%s: workspace %zu < %zu bytes", what,
+             workspace_bytes, (size_t)(C_SYNC_WORDS * 4 + 192 + part));
+  p.trace = nullptr;
+  if (g_trace_base && g_trace_next < g_trace_slots) p.trace = g_trace_base + (g_trace_next++) * 4096 * 8;
+  p.sync = static_cast<unsigned*>(workspace);
+  p.partial = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + 256);
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return cuda_fail(e, "gemm_chain(smem attr)");
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(ctas, 1, 1);
+  cfg.blockDim = dim3(C_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = chain_smem_bytes(p.mpad, p.nw, p.nx);
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attrs[1];
+  int na = 0;
+  if (pdl) {
+    attrs[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attrs;
+  cfg.numAttrs = na;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_chain_kernel, p, tmaps[0], tmaps[1], tmaps[2], tmaps[3]);
+  count_launch();
+  if (e != cudaSuccess) return cuda_fail(e, what);
+  return B2TTS_OK;
+}
+
 // Debug aid (tools/gemm_trace.py): every following GEMM launch records 8 globaltimer stamps per CTA into
 // buffer + launch_index * 4096 * 8 (uint64), for `launches` launches.  NULL switches tracing off.
 extern "C" B2TTS_API int b2tts_debug_gemm_trace(void* buffer, int launches) {

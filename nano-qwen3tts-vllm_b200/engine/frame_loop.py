@@ -78,10 +78,14 @@ class DeviceFrameLoop:
                 slots=(pg * self.page + g + 1).contiguous()))
         self.graph = None
         self.launches_per_frame = None
+        self.unit_noise = False
 
     # ------------------------------------------------------------------ sampling
     def _sample(self, logits, temps, out):
-        noise = torch.empty(logits.shape, dtype=torch.float32, device=self.dev).exponential_(1)
+        if self.unit_noise:          # tests: argmax(p / 1) = first maximum, so exact bf16 ties do not depend on the RNG
+            noise = torch.ones(logits.shape, dtype=torch.float32, device=self.dev)
+        else:
+            noise = torch.empty(logits.shape, dtype=torch.float32, device=self.dev).exponential_(1)
         nat.topk_sample(logits, temps, noise, top_k=self.top_k, out=out)
 
     # ------------------------------------------------------------------ prompt

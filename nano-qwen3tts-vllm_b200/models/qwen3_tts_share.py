@@ -26,12 +26,13 @@ from ..layers.activation import SiluAndMul
 from ..layers.attention import Attention
 from ..layers.layernorm import Qwen3TTSRMSNorm
 from ..layers.linear import (GEMM_NATIVE_MAX_M, MergedColumnParallelLinear, QKVParallelLinear, RowParallelLinear,
-                             RowNorm, linear, linear_residual, linear_silu_mul)
+                             RowNorm, linear, linear_residual, linear_silu_mul, packed_weight)
 from ..layers.rotary_embedding import get_rope
 from ..utils.context import get_context
 
 
 FUSED_DECODE_ATTENTION = True     # False: separate qknorm_rope_kvwrite + paged_attn_decode launches
+GEMM_CHAIN = False                # decode: the 4 projections between two attention calls as ONE persistent launch
 
 
 class Qwen3TTSAttention(nn.Module):
@@ -60,9 +61,12 @@ class Qwen3TTSAttention(nn.Module):
     def attend(self, positions: torch.Tensor, hidden_states: torch.Tensor, norm: RowNorm | None = None) -> torch.Tensor:
         """Everything up to (not including) o_proj: [n, heads * head_dim].  With ``norm`` the input is the
         un-normalised residual stream and the QKV GEMM applies the input RMSNorm while staging it."""
+        return self.attend_qkv(positions, linear(hidden_states, self.qkv_proj.weight, norm=norm))
+
+    def attend_qkv(self, positions: torch.Tensor, qkv: torch.Tensor) -> torch.Tensor:
+        """``attend`` from the rows of the QKV projection (the GEMM chain of the previous layer produced them)."""
         ctx = get_context()
-        n = hidden_states.shape[0]
-        qkv = linear(hidden_states, self.qkv_proj.weight, norm=norm)
+        n = qkv.shape[0]
         q = qkv[:, :self.q_size].view(n, self.num_heads, self.head_dim)
         k = qkv[:, self.q_size:self.q_size + self.kv_size].view(n, self.num_kv_heads, self.head_dim)
         v = qkv[:, self.q_size + self.kv_size:].view(n, self.num_kv_heads, self.head_dim)
@@ -157,8 +161,69 @@ class DecoderStack(nn.Module):
         self.layers = nn.ModuleList([Qwen3TTSDecoderLayer(config, rounding) for _ in range(config.num_hidden_layers)])
         self.norm = Qwen3TTSRMSNorm(config.hidden_size, eps=config.rms_norm_eps, rounding=rounding)
 
+    def _chain_supported(self) -> bool:
+        ok = getattr(self, "_chain_ok", None)
+        if ok is None:
+            c = self.config
+            ok = self._chain_ok = all(nat.gemm_supported(1, n, k) for n, k in (
+                (c.hidden_size, c.q_size), (2 * c.intermediate_size, c.hidden_size),
+                (c.hidden_size, c.intermediate_size), (c.q_size + 2 * c.kv_size, c.hidden_size)))
+        return ok
+
+    def _chain_workspace(self, device) -> torch.Tensor:
+        ws = getattr(self, "_chain_ws", None)
+        if ws is None or ws.device != torch.device(device):
+            c = self.config
+            shapes = [(c.hidden_size, c.q_size), (2 * c.intermediate_size, c.hidden_size),
+                      (c.hidden_size, c.intermediate_size), (c.q_size + 2 * c.kv_size, c.hidden_size)]
+            ws = self._chain_ws = nat.gemm_chain_workspace(GEMM_NATIVE_MAX_M, shapes, device)
+        return ws
+
+    def run_layers_chained(self, input_embeds: torch.Tensor, positions: torch.Tensor,
+                           input_ssq: torch.Tensor | None = None) -> torch.Tensor:
+        """Decode (n <= GEMM_NATIVE_MAX_M rows): per layer ONE attention launch and ONE persistent GEMM-chain
+        launch (o_proj + residual, gate_up with the post-attention norm and SiLU*mul, down_proj + residual, the
+        next layer's qkv_proj with its input norm) - 2 launches per layer instead of 5, and the weight stream
+        does not stop between the projections.  Same rounding points as ``forward_decode``."""
+        c, eps, rnd = self.config, self.config.rms_norm_eps, self.rounding
+        m, dev = input_embeds.shape[0], input_embeds.device
+        ws = self._chain_workspace(dev)
+        first = self.layers[0]
+        if input_ssq is None:
+            h = nat.rmsnorm(input_embeds, first.input_layernorm.weight, eps, rnd)
+            qkv = linear(h, first.self_attn.qkv_proj.weight)
+        else:
+            qkv = linear(input_embeds, first.self_attn.qkv_proj.weight,
+                         norm=RowNorm(first.input_layernorm.weight, input_ssq, eps, rnd))
+        residual = input_embeds
+        slots = nat.gemm_chain_ssq_slots(c.hidden_size)
+        ssq1 = torch.empty(m, slots, dtype=torch.float32, device=dev)
+        ssq2 = torch.empty(m, slots, dtype=torch.float32, device=dev)
+        act = torch.empty(m, c.intermediate_size, dtype=input_embeds.dtype, device=dev)
+        nlayers = len(self.layers)
+        for i, layer in enumerate(self.layers):
+            o = layer.self_attn.attend_qkv(positions, qkv)
+            out = residual if i > 0 else torch.empty_like(residual)      # the caller's embeddings stay intact
+            ops = [dict(x=o, packed=packed_weight(layer.self_attn.o_proj.weight), n=c.hidden_size, residual=residual,
+                        out=out, epilogue=nat.GEMM_RESIDUAL, ssq_out=ssq1),
+                   dict(x=out, packed=packed_weight(layer.mlp.gate_up_proj.weight, nat.PACK_GATE_UP),
+                        n=2 * c.intermediate_size, out=act, epilogue=nat.GEMM_SILU_MUL,
+                        norm_weight=layer.post_attention_layernorm.weight, ssq_in=ssq1),
+                   dict(x=act, packed=packed_weight(layer.mlp.down_proj.weight), n=c.hidden_size, residual=out, out=out,
+                        epilogue=nat.GEMM_RESIDUAL, ssq_out=ssq2)]
+            if i + 1 < nlayers:
+                nxt = self.layers[i + 1]
+                qkv = torch.empty(m, c.q_size + 2 * c.kv_size, dtype=input_embeds.dtype, device=dev)
+                ops.append(dict(x=out, packed=packed_weight(nxt.self_attn.qkv_proj.weight), n=qkv.shape[1], out=qkv,
+                                norm_weight=nxt.input_layernorm.weight, ssq_in=ssq2))
+            nat.gemm_chain(ops, m, ws, eps=eps, rounding=rnd)
+            residual = out
+        return nat.rmsnorm(residual, self.norm.weight, eps, rnd)
+
     def run_layers(self, input_embeds: torch.Tensor, positions: torch.Tensor,
                    input_ssq: torch.Tensor | None = None) -> torch.Tensor:
+        if GEMM_CHAIN and 1 <= input_embeds.shape[0] <= GEMM_NATIVE_MAX_M and self._chain_supported():
+            return self.run_layers_chained(input_embeds, positions, input_ssq)
         if input_embeds.shape[0] <= GEMM_NATIVE_MAX_M:
             residual, ssq = input_embeds, input_ssq
             for i, layer in enumerate(self.layers):

@@ -36,5 +36,5 @@ base = int(t[0, :ncta, 0].min())
 print(f"M={m} N={n} K={k} splits={splits} CTAs={ncta}; times in us relative to first CTA entry of launch 0")
 for i in range(chain):
     tt = (t[i, :ncta].double() - base) / 1e3
-    row = "  ".join(f"{names[j][:14]:>14s} {tt[:, j].min():6.2f}/{tt[:, j].median():6.2f}/{tt[:, j].max():6.2f}" for j in (2, 3, 4, 5, 6, 7))
+    row = "  ".join(f"{names[j][:9]:>9s} {tt[:, j].min():5.1f}/{tt[:, j].median():5.1f}/{tt[:, j].max():5.1f}" for j in (0, 1, 2, 3, 4, 5, 6, 7))
     print(f"launch {i}: {row}")

@@ -105,6 +105,52 @@ def gemm_case(m, n, k, splits=0, pdl=False, epilogue=0, chain=16):
                       "cublas_us": round(ms_c * 1e3, 2), "cublas_GBps": round(gb_c, 1)}), flush=True)
 
 
+def chain_case(m, h, inter, nq, layers=8):
+    """`layers` GEMM chains (o + gate_up + down + next qkv) back to back over different weights in one graph,
+    against the same 4 x layers projections as separate b2tts_gemm_norm_bf16 launches."""
+    g = torch.Generator(device=DEV).manual_seed(1)
+    mk = lambda n, k: (torch.randn(n, k, device=DEV, generator=g) * 0.03).to(BF16)
+    L = []
+    for _ in range(layers):
+        L.append(dict(o=nat.gemm_pack_weight(mk(h, nq // 2)), gu=nat.gemm_pack_weight(mk(2 * inter, h), nat.PACK_GATE_UP),
+                      down=nat.gemm_pack_weight(mk(h, inter)), qkv=nat.gemm_pack_weight(mk(nq, h)),
+                      ln1=torch.ones(h, device=DEV, dtype=BF16), ln2=torch.ones(h, device=DEV, dtype=BF16)))
+    attn = torch.randn(m, nq // 2, device=DEV, dtype=BF16)
+    r = torch.randn(m, h, device=DEV, dtype=BF16)
+    act = torch.empty(m, inter, device=DEV, dtype=BF16); qkv = torch.empty(m, nq, device=DEV, dtype=BF16)
+    s1 = torch.empty(m, h // 16, device=DEV, dtype=torch.float32); s2 = torch.empty_like(s1)
+    ws = nat.gemm_chain_workspace(m, [(h, nq // 2), (2 * inter, h), (h, inter), (nq, h)], DEV)
+    t1 = torch.empty(m, nat.gemm_ssq_slots(m, h, nq // 2), device=DEV, dtype=torch.float32)
+    t2 = torch.empty(m, nat.gemm_ssq_slots(m, h, inter), device=DEV, dtype=torch.float32)
+
+    def chained():
+        for w in L:
+            nat.gemm_chain([
+                dict(x=attn, packed=w["o"], n=h, residual=r, out=r, epilogue=nat.GEMM_RESIDUAL, ssq_out=s1),
+                dict(x=r, packed=w["gu"], n=2 * inter, out=act, epilogue=nat.GEMM_SILU_MUL, norm_weight=w["ln1"], ssq_in=s1),
+                dict(x=act, packed=w["down"], n=h, residual=r, out=r, epilogue=nat.GEMM_RESIDUAL, ssq_out=s2),
+                dict(x=r, packed=w["qkv"], n=nq, out=qkv, norm_weight=w["ln2"], ssq_in=s2)], m, ws)
+
+    def separate():
+        for w in L:
+            nat.gemm_bf16(attn, w["o"], h, residual=r, epilogue=nat.GEMM_RESIDUAL, out=r, ssq_out=t1, pdl=True)
+            nat.gemm_bf16(r, w["gu"], 2 * inter, epilogue=nat.GEMM_SILU_MUL, out=act, norm_weight=w["ln1"], ssq_in=t1, pdl=True)
+            nat.gemm_bf16(act, w["down"], h, residual=r, epilogue=nat.GEMM_RESIDUAL, out=r, ssq_out=t2, pdl=True)
+            nat.gemm_bf16(r, w["qkv"], nq, out=qkv, norm_weight=w["ln2"], ssq_in=t2, pdl=True)
+    res = {}
+    for name, fn in (("chain", chained), ("separate", separate)):
+        fn(); torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            fn()
+        res[name] = time_ms(lambda i: gr.replay()) / layers * 1e3
+    alg = float(2 * (h * nq // 2 + 2 * inter * h + h * inter + nq * h))
+    print(json.dumps({"kernel": "gemm_chain", "M": m, "hidden": h, "inter": inter, "qkv": nq, "chain_us": round(res["chain"], 2),
+                      "separate_us": round(res["separate"], 2), "chain_GBps": round(alg / res["chain"] / 1e3, 1),
+                      "frac_measured_peak": round(alg / res["chain"] / 1e3 / peaks(), 4),
+                      "env": {k: v for k, v in os.environ.items() if k.startswith("B2TTS_")}}), flush=True)
+
+
 def fattn_case(b, l, layers=28, page=256, kvh=8, h=16, hd=128):
     """Fused decode attention vs the three separate launches, `layers` launches per graph over different
     caches (cold KV), uniform context l."""
@@ -155,6 +201,7 @@ def main():
     ap.add_argument("--gemm-cases", default="64:4096:2048,64:2048:2048,64:12288:2048,64:2048:6144,64:4096:1024,"
                                             "64:1024:2048,64:6144:1024,64:1024:3072,64:2048:1024,1:4096:2048,8:4096:2048,"
                                             "256:4096:2048")
+    ap.add_argument("--chain-cases", default="64:2048:6144:4096,64:1024:3072:4096,8:2048:6144:4096,1:2048:6144:4096")
     ap.add_argument("--splits", default="0")
     ap.add_argument("--pdl", type=int, default=1)
     a = ap.parse_args()
@@ -165,6 +212,10 @@ def main():
                 if s_ and (s_ > k // 64):
                     continue
                 gemm_case(m, n, k, splits=s_, pdl=bool(a.pdl))
+    if a.what == "chain":
+        for c in a.chain_cases.split(","):
+            m, h, inter, nq = map(int, c.split(":"))
+            chain_case(m, h, inter, nq)
     if a.what == "fattn":
         for c in a.cases.split(","):
             b, l = map(int, c.split(":"))
