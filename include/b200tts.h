@@ -251,7 +251,7 @@ B2TTS_API int    b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const
  * thread keeps a deep shared-memory ring of packed weight tiles full across the whole chain while the CTAs
  * reduce split-K partials through L2 and cross a grid barrier between GEMMs.  Every op is a b2tts_gemm_norm_bf16
  * (same packed weights, epilogues, fused input norm and rounding points); op i+1 may read what op i wrote
- * (x, residual, ssq_in).  ssq_out of an op has b2tts_gemm_chain_ssq_slots(n) = n/16 slots per row.
+ * (x, residual, ssq_in).  ssq_out of an op has b2tts_gemm_chain_ssq_slots(n) = n/128 slots per row.
  * 1 <= nops <= 4, 1 <= m <= 128.  workspace: b2tts_gemm_chain_workspace_bytes(...) bytes, ZERO-FILLED once by the
  * caller (the kernel leaves its barrier counters zero); one workspace must not be used by two launches that
  * can run concurrently.  The grid needs every SM of the device: do not run two chains concurrently. */
@@ -261,7 +261,7 @@ typedef struct b2tts_gemm_op {
   const void* residual;     int64_t residual_row_stride;  /* B2TTS_GEMM_RESIDUAL */
   void* out;                int64_t out_row_stride;       /* [m, n] (or [m, n/2] for SiLU*mul); may alias residual */
   const void* norm_weight;  const float* ssq_in;          /* fused input RMSNorm (or NULL) */
-  float* ssq_out;                                         /* [m, n/16] partial row sums of squares (or NULL) */
+  float* ssq_out;                                         /* [m, n/128] partial row sums of squares (or NULL) */
   int n, k, epilogue, ssq_in_slots;
 } b2tts_gemm_op;
 B2TTS_API int    b2tts_gemm_chain_ssq_slots(int n);

@@ -475,7 +475,7 @@ def gemm_chain(ops: list[dict], m: int, workspace: torch.Tensor, eps: float = 1e
                pdl: bool = True):
     """Up to 4 dependent GEMMs in one persistent launch (``b2tts_gemm_chain``).  Each op is a dict with
     ``x`` [m, k] bf16, ``packed`` (``gemm_pack_weight`` image), ``n``, ``out``, and optionally ``residual``,
-    ``epilogue``, ``norm_weight`` + ``ssq_in`` [m, slots] fp32, ``ssq_out`` [m, n/16] fp32."""
+    ``epilogue``, ``norm_weight`` + ``ssq_in`` [m, slots] fp32, ``ssq_out`` [m, n/128] fp32."""
     arr = (GemmOp * len(ops))()
     keep = []
     for i, o in enumerate(ops):
@@ -489,8 +489,8 @@ def gemm_chain(ops: list[dict], m: int, workspace: torch.Tensor, eps: float = 1e
         res = o.get("residual")
         ssq_in, ssq_out = o.get("ssq_in"), o.get("ssq_out")
         n, k = int(o["n"]), int(x.shape[1])
-        if ssq_out is not None and (ssq_out.dtype != F32 or not ssq_out.is_contiguous() or ssq_out.shape[1] != n // 16):
-            raise ValueError(f"gemm_chain op {i}: ssq_out must be a contiguous [>=m, {n // 16}] fp32 tensor")
+        if ssq_out is not None and (ssq_out.dtype != F32 or not ssq_out.is_contiguous() or ssq_out.shape[1] != n // 128):
+            raise ValueError(f"gemm_chain op {i}: ssq_out must be a contiguous [>=m, {n // 128}] fp32 tensor")
         if ssq_in is not None and (ssq_in.dtype != F32 or not ssq_in.is_contiguous()):
             raise ValueError(f"gemm_chain op {i}: ssq_in must be a contiguous [>=m, slots] fp32 tensor")
         a = arr[i]

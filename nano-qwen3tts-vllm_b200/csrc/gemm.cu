@@ -779,7 +779,8 @@ namespace b2 {
 constexpr int C_MAX_OPS = 4;
 constexpr int C_THREADS = 224;
 constexpr int C_EPI0 = 96;                       // first epilogue thread
-constexpr int C_UNIT = 16;                       // features per reduce unit = one ssq slot
+constexpr int C_SSQ_FEATS = 128;                 // output features per ssq slot (16 lanes x 8 features)
+constexpr int C_NORMW_MAX = 4096;                // largest K whose norm weight is staged in shared memory
 constexpr int C_SYNC_WORDS = 16;                 // 2 * C_MAX_OPS barrier counters + exit counter, padded
 
 struct ChainOp {
@@ -795,12 +796,15 @@ struct ChainOp {
 
 struct ChainParams {
   ChainOp op[C_MAX_OPS];
-  int nops, m, mpad, tmem_cols, nw, nx, rounding;
+  int nops, m, mpad, tmem_cols, nw, nx, cg, rounding;   // nw == nx ring slots, released in groups of cg k-blocks
   float eps;
   float* partial;                                // [splits][n][mpad] fp32, reused by every op
   unsigned* sync;                                // C_SYNC_WORDS counters, zero between launches
   unsigned long long* trace;                     // debug: 8 globaltimer stamps per (CTA, op) (null = off)
 };
+// debug: per-k-block clock64 stamps of CTA 0, op 1: stream e (0 TMA x issue, 1 x landed at the hop, 2 hop done, 3 MMA has W,
+// 4 MMA has x) x 64 k-blocks at trace[8192 + e * 64 + idx]
+#define C_KB_TRACE(e, idx) do { if (p.trace && cta == 0 && i == 1 && (idx) < 64) p.trace[8192 + (e) * 64 + (idx)] = (unsigned long long)clock64(); } while (0)
 #define C_TRACE(op_i, slot) do { if (p.trace && te == 0) p.trace[((int64_t)cta * C_MAX_OPS + (op_i)) * 8 + (slot)] = gtimer(); } while (0)
 
 __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
@@ -822,7 +826,7 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
                   const __grid_constant__ CUtensorMap tm2, const __grid_constant__ CUtensorMap tm3) {
   extern __shared__ uint8_t smem_dyn[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
-  const int mpad = p.mpad, NW = p.nw, NX = p.nx;
+  const int mpad = p.mpad, NW = p.nw, NX = p.nx, CG = p.cg;
   const int xstage = mpad * 128;
   uint8_t* wring = smem;
   uint8_t* xring = wring + NW * G_WTILE_BYTES;
@@ -834,7 +838,8 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
   uint64_t* accfull = xempty + G_MAX_STAGES;
   uint64_t* accempty = accfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accempty + 2);
-  float* rstd_s = reinterpret_cast<float*>(tmem_slot + 2);
+  float* rstd_s = reinterpret_cast<float*>(tmem_slot + 4);                         // keeps normw_s 16-byte aligned
+  __nv_bfloat16* normw_s = reinterpret_cast<__nv_bfloat16*>(rstd_s + G_MAX_M);     // [C_NORMW_MAX], 16-byte aligned
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -842,8 +847,10 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
   const int cta = blockIdx.x;
 
   if (threadIdx.x == 0) {
+    // wempty[g]: ring slots g*CG .. g*CG+CG-1 of BOTH rings are free again (one tcgen05.commit per CG k-blocks:
+    // a commit costs the issuing thread ~0.2 us, so one per k-block per ring would pace the whole stream)
     for (int s = 0; s < NW; ++s) { mbar_init(wfull + s, 1); mbar_init(wempty + s, 1); }
-    for (int s = 0; s < NX; ++s) { mbar_init(xraw + s, 1); mbar_init(xfull + s, 4); mbar_init(xempty + s, 1); }
+    for (int s = 0; s < NX; ++s) { mbar_init(xraw + s, 1); mbar_init(xfull + s, 1); }
     for (int b = 0; b < 2; ++b) { mbar_init(accfull + b, 1); mbar_init(accempty + b, 4); }
     mbar_fence_init();
   }
@@ -866,7 +873,7 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
           const uint8_t* src = op.wp + ((int64_t)tile * op.kblocks + kb0) * G_WTILE_BYTES;
           for (int kb = kb0; kb < kb1; ++kb, ++j, src += G_WTILE_BYTES) {
             const uint32_t slot = j % NW;
-            mbar_wait(wempty + slot, ((j / NW) & 1) ^ 1);
+            mbar_wait(wempty + slot / CG, ((j / NW) & 1) ^ 1);
             mbar_expect_tx(wfull + slot, G_WTILE_BYTES);
             bulk_g2s(wring + slot * G_WTILE_BYTES, src, G_WTILE_BYTES, wfull + slot);
           }
@@ -882,6 +889,8 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
       for (int i = 0; i < p.nops; ++i) {
         const ChainOp& op = p.op[i];
         const int S = op.splits, items = op.n_tiles * S;
+        unsigned long long wait_w = 0, wait_x = 0;
+        int kbi = 0;
         for (int t = cta; t < items; t += G, ++it) {
           const int tile = t / S, s = t - tile * S;
           const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
@@ -891,8 +900,13 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
           const uint32_t d_addr = tmem_base + b * (uint32_t)mpad;
           for (int kb = kb0; kb < kb1; ++kb, ++j) {
             const uint32_t sw = j % NW, sx = j % NX;
+            const long long c0 = p.trace ? clock64() : 0;
             mbar_wait(wfull + sw, (j / NW) & 1);
+            const long long c1 = p.trace ? clock64() : 0;
+            C_KB_TRACE(3, kbi);
             mbar_wait(xfull + sx, (j / NX) & 1);
+            C_KB_TRACE(4, kbi); ++kbi;
+            if (p.trace) { wait_w += (unsigned long long)(c1 - c0); wait_x += (unsigned long long)(clock64() - c1); }
             tc_fence_after();
             const uint32_t a_addr = smem_u32(wring + sw * G_WTILE_BYTES);
             const uint32_t b_addr = smem_u32(xring + sx * xstage);
@@ -900,11 +914,11 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
             for (int k = 0; k < G_BK / 16; ++k)
               umma_bf16(d_addr, umma_desc_sw128(a_addr + k * 32), umma_desc_sw128(b_addr + k * 32), idesc,
                         (uint32_t)((kb > kb0) || (k > 0)));
-            umma_commit(wempty + sw);
-            umma_commit(xempty + sx);
+            if ((sw + 1) % CG == 0) umma_commit(wempty + sw / CG);
           }
           umma_commit(accfull + b);
         }
+        if (p.trace) p.trace[((int64_t)cta * C_MAX_OPS + i) * 8 + 7] = (wait_w << 32) | (wait_x & 0xffffffffull);
       }
     }
     __syncwarp();
@@ -921,16 +935,28 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
           grid_wait(p.sync + 2 * (i - 1) + 1, (unsigned)G);
           fence_proxy_async_all();
         }
-        const CUtensorMap* tm = i == 0 ? &tm0 : i == 1 ? &tm1 : i == 2 ? &tm2 : &tm3;
         const int S = op.splits, items = op.n_tiles * S;
+        const bool normed = op.norm_w != nullptr;
+        int kbi = 0;
         for (int t = cta; t < items; t += G) {
           const int tile = t / S, s = t - tile * S;
           const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
           for (int kb = kb0; kb < kb1; ++kb, ++j) {
             const uint32_t slot = j % NX;
-            mbar_wait(xempty + slot, ((j / NX) & 1) ^ 1);
-            mbar_expect_tx(xraw + slot, xbytes);
-            tma_load_2d(xring + slot * xstage, tm, kb * G_BK, 0, xraw + slot);
+            mbar_wait(wempty + slot / CG, ((j / NX) & 1) ^ 1);
+            C_KB_TRACE(0, kbi); ++kbi;
+            // with a fused norm the tile lands "raw" and an epilogue warp releases it after the transform;
+            // otherwise the copy completes straight on the barrier the MMA issuer waits on
+            uint64_t* landed = normed ? xraw + slot : xfull + slot;
+            mbar_expect_tx(landed, xbytes);
+            // the tensor map must be addressed in param space: selecting a pointer at run time would make the
+            // compiler copy the maps to local memory, and every copy would then fetch its descriptor from DRAM
+            switch (i) {
+              case 0: tma_load_2d(xring + slot * xstage, &tm0, kb * G_BK, 0, landed); break;
+              case 1: tma_load_2d(xring + slot * xstage, &tm1, kb * G_BK, 0, landed); break;
+              case 2: tma_load_2d(xring + slot * xstage, &tm2, kb * G_BK, 0, landed); break;
+              default: tma_load_2d(xring + slot * xstage, &tm3, kb * G_BK, 0, landed); break;
+            }
           }
         }
       }
@@ -941,7 +967,9 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
     const int te = threadIdx.x - C_EPI0;
     const int q = warp & 3;                     // TMEM lane quarter this warp may read
     const bool eager = p.rounding == B2TTS_ROUND_EAGER;
-    uint32_t j = 0, it = 0;
+    const int M = p.m;
+    const int wq = warp - 3;                    // 0..3
+    uint32_t j = 0, it = 0, xraw_ph = 0;
     C_TRACE(0, 0);
     pdl_wait();
     for (int i = 0; i < p.nops; ++i) {
@@ -952,83 +980,88 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
       }
       C_TRACE(i, 1);
       const bool normed = op.norm_w != nullptr;
+      const bool w_in_smem = normed && op.k <= C_NORMW_MAX;
       if (normed) {
-        const int GL = op.ssq_lanes, rows_per_pass = 128 / GL;
-        const int gl = te % GL, chunk = op.ssq_in_slots / GL;
-        for (int r0 = 0; r0 < mpad; r0 += rows_per_pass) {
-          const int r = r0 + te / GL;
+        // rstd[m]: one thread per row sums the row's partial sums of squares in slot order (deterministic)
+        if (te < mpad) {
           float sum = 0.f;
-          if (r < p.m) {
-            const float* src = op.ssq_in + (int64_t)r * op.ssq_in_slots + gl * chunk;
-            if ((chunk & 3) == 0) {
-              for (int c = 0; c < chunk; c += 4) {
+          if (te < M) {
+            const float* src = op.ssq_in + (int64_t)te * op.ssq_in_slots;
+            if ((op.ssq_in_slots & 3) == 0) {
+#pragma unroll 4
+              for (int c = 0; c < op.ssq_in_slots; c += 4) {
                 const float4 v = __ldcg(reinterpret_cast<const float4*>(src + c));
                 sum += v.x; sum += v.y; sum += v.z; sum += v.w;
               }
             } else {
-              for (int c = 0; c < chunk; ++c) sum += __ldcg(src + c);
+#pragma unroll 4
+              for (int c = 0; c < op.ssq_in_slots; ++c) sum += __ldcg(src + c);
             }
           }
-          for (int o = 1; o < GL; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-          if (r < mpad && gl == 0) {
-            const float var = sum / (float)op.k + p.eps;
-            rstd_s[r] = eager ? 1.0f / sqrtf(var) : rsqrtf(var);
-          }
+          const float var = sum / (float)op.k + p.eps;
+          rstd_s[te] = eager ? 1.0f / sqrtf(var) : rsqrtf(var);
         }
+        if (w_in_smem)                                    // the norm weight once per op, not once per k-block
+          for (int c = te; c < op.k / 8; c += 128)
+            reinterpret_cast<uint4*>(normw_s)[c] = ldg_v4(op.norm_w + c * 8);
         epi_bar();
       }
       C_TRACE(i, 2);
       const int S = op.splits, items = op.n_tiles * S;
+      int kbi = 0;
       for (int t = cta; t < items; t += G, ++it) {
         const int tile = t / S, s = t - tile * S;
         const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
-        for (int kb = kb0; kb < kb1; ++kb, ++j) {
-          const uint32_t sx = j % NX;
-          mbar_wait(xraw + sx, (j / NX) & 1);
-          if (kb == kb0 && t == cta) C_TRACE(i, 3);
-          if (normed) {
+        if (!normed) {
+          j += (uint32_t)(kb1 - kb0);                    // the x tiles go from the TMA unit straight to the MMA issuer
+        } else {
+          // slot sx = j % NX (NX a multiple of 4) always belongs to epilogue warp sx & 3: the four warps transform
+          // four consecutive k-blocks concurrently, and each tracks the phase of its own slots' xraw barriers
+          for (int kb = kb0; kb < kb1; ++kb, ++j, ++kbi) {
+            const uint32_t sx = j % NX;
+            if ((int)(sx & 3) != wq) continue;
+            mbar_wait(xraw + sx, (xraw_ph >> sx) & 1);
+            xraw_ph ^= 1u << sx;
+            if (lane == 0) C_KB_TRACE(1, kbi);
+            if (kb == kb0 && t == cta) C_TRACE(i, 3);
             uint8_t* xs = xring + sx * xstage;
-            const uint4 wv = ldg_v4(op.norm_w + (int64_t)kb * G_BK + (te & 7) * 8);
-            for (int idx = te; idx < mpad * 8; idx += 128) {
-              const int r = idx >> 3, c = idx & 7;
-              if (r < p.m) {
-                uint4* cell = reinterpret_cast<uint4*>(xs + r * 128 + ((c ^ (r & 7)) << 4));
-                *cell = norm8(*cell, wv, rstd_s[r], eager);
-              }
+            const int c = lane & 7;
+            const uint4 wv = w_in_smem ? reinterpret_cast<const uint4*>(normw_s)[kb * 8 + c]
+                                       : ldg_v4(op.norm_w + (int64_t)kb * G_BK + c * 8);
+#pragma unroll 4
+            for (int r = lane >> 3; r < M; r += 4) {
+              uint4* cell = reinterpret_cast<uint4*>(xs + r * 128 + ((c ^ (r & 7)) << 4));
+              *cell = norm8(*cell, wv, rstd_s[r], eager);
             }
             fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(xfull + sx);
+            if (lane == 0) C_KB_TRACE(2, kbi);
           }
-          __syncwarp();
-          if (lane == 0) mbar_arrive(xfull + sx);
         }
-        // drain the accumulator of this item to the split-K scratch: thread = feature row, mpad columns
+        // drain the accumulator of this item to the split-K scratch [split][row m][feature n]: thread = feature,
+        // so for each batch row a warp stores 32 consecutive floats
         const uint32_t b = it & 1;
         mbar_wait(accfull + b, (it >> 1) & 1);
         tc_fence_after();
-        float* row = p.partial + ((int64_t)s * op.n + (int64_t)tile * G_BN + q * 32 + lane) * mpad;
-        for (int c0 = 0; c0 < mpad; c0 += 64) {
-          uint32_t v[64];
-          const int nq = min(4, (mpad - c0) >> 4);
-#pragma unroll
-          for (int qq = 0; qq < 4; ++qq)
-            if (qq < nq) tmem_ld16_nowait(tmem_base + ((uint32_t)(q * 32) << 16) + b * (uint32_t)mpad + (uint32_t)(c0 + 16 * qq), v + 16 * qq);
+        float* dst = p.partial + (int64_t)s * M * op.n + (int64_t)tile * G_BN + q * 32 + lane;
+        for (int c0 = 0; c0 < M; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld16_nowait(tmem_base + ((uint32_t)(q * 32) << 16) + b * (uint32_t)mpad + (uint32_t)c0, v);
+          if (c0 + 16 < mpad)
+            tmem_ld16_nowait(tmem_base + ((uint32_t)(q * 32) << 16) + b * (uint32_t)mpad + (uint32_t)(c0 + 16), v + 16);
           tmem_ld_wait();
 #pragma unroll
-          for (int qq = 0; qq < 4; ++qq)
-            if (qq < nq) {
-#pragma unroll
-              for (int jj = 0; jj < 16; jj += 4)
-                __stcg(reinterpret_cast<uint4*>(row + c0 + 16 * qq + jj),
-                       make_uint4(v[16 * qq + jj], v[16 * qq + jj + 1], v[16 * qq + jj + 2], v[16 * qq + jj + 3]));
-            }
+          for (int c = 0; c < 32; ++c)
+            if (c0 + c < M) __stcg(dst + (int64_t)(c0 + c) * op.n, __uint_as_float(v[c]));
         }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(accempty + b);
       }
-      // ---- grid barrier A(i): every partial of op i is in L2
+      // ---- grid barrier A(i): every partial of op i is in L2 (release by one thread after the CTA-wide
+      // barrier is cumulative over the other threads' stores, as in a cooperative-groups grid sync)
       C_TRACE(i, 4);
-      __threadfence();
       epi_bar();
       if (te == 0) {
         grid_arrive(p.sync + 2 * i);
@@ -1037,26 +1070,34 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
       epi_bar();
       C_TRACE(i, 5);
       if (i == p.nops - 1) pdl_launch();
-      // ---- reduce phase: unit = (row m, 16 features); lanes run along m (coalesced scratch reads)
+      // ---- reduce phase: unit = (row m, 8 consecutive features), lanes run along the features: 32-byte
+      // scratch reads per split and 16-byte stores, all coalesced; the sums of squares of 16 lanes (128
+      // features) fold in a fixed shuffle tree into one ssq slot
       {
-        const int M = p.m, N = op.n;
-        const int units = M * (N / C_UNIT);
-        const int slots = N / C_UNIT;
-        for (int u = cta * 128 + te; u < units; u += G * 128) {
-          const int ch = u / M, m = u - ch * M;
-          float qsum = 0.f;
+        const int N = op.n;
+        const int per_row = N >> 3;                       // units per row (a multiple of 16)
+        const int units = M * per_row;
+        const int slots = N / C_SSQ_FEATS;
+        for (int u0 = cta * 128 + (te & ~31); u0 < units; u0 += G * 128) {
+          const int u = u0 + lane;
+          const bool valid = u < units;
+          const int m = valid ? u / per_row : 0;
+          const int n = valid ? (u - m * per_row) * 8 : 0;
+          float acc[8];
 #pragma unroll
-          for (int g8 = 0; g8 < C_UNIT / 8; ++g8) {
-            const int n = ch * C_UNIT + g8 * 8;
-            float acc[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-            for (int sp = 0; sp < S; ++sp) {
-              const float* src = p.partial + ((int64_t)sp * N + n) * mpad + m;
-#pragma unroll
-              for (int e = 0; e < 8; ++e) acc[e] += __ldcg(src + e * mpad);
+          for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+          if (valid) {
+            const float* src = p.partial + (int64_t)m * N + n;
+            for (int sp = 0; sp < S; ++sp, src += (int64_t)M * N) {
+              const float4 a = __ldcg(reinterpret_cast<const float4*>(src));
+              const float4 c = __ldcg(reinterpret_cast<const float4*>(src) + 1);
+              acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
+              acc[4] += c.x; acc[5] += c.y; acc[6] += c.z; acc[7] += c.w;
             }
-            if (op.epilogue == B2TTS_GEMM_SILU_MUL) {
+          }
+          float qsum = 0.f;
+          if (op.epilogue == B2TTS_GEMM_SILU_MUL) {
+            if (valid) {
               float o[4];
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
@@ -1066,8 +1107,10 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
               uint2 w;
               w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
               stg_v2(op.out + (int64_t)m * op.out_stride + (n >> 1), w);
-              continue;
             }
+            continue;
+          }
+          if (valid) {
             if (op.epilogue == B2TTS_GEMM_RESIDUAL) {
               const uint4 rw = __ldcg(reinterpret_cast<const uint4*>(op.res + (int64_t)m * op.res_stride + n));
               acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
@@ -1084,13 +1127,16 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
             qsum = fmaf(bf16lo(w.z), bf16lo(w.z), qsum); qsum = fmaf(bf16hi(w.z), bf16hi(w.z), qsum);
             qsum = fmaf(bf16lo(w.w), bf16lo(w.w), qsum); qsum = fmaf(bf16hi(w.w), bf16hi(w.w), qsum);
           }
-          if (op.ssq_out) op.ssq_out[(int64_t)m * slots + ch] = qsum;
+          if (op.ssq_out) {                               // warp-uniform
+#pragma unroll
+            for (int o = 1; o < 16; o <<= 1) qsum += __shfl_xor_sync(0xffffffffu, qsum, o);
+            if (valid && (lane & 15) == 0) op.ssq_out[(int64_t)m * slots + n / C_SSQ_FEATS] = qsum;
+          }
         }
       }
       // ---- barrier B(i): the rows op i+1 reads are complete (arrive only; the readers wait)
       C_TRACE(i, 6);
       if (i + 1 < p.nops) {
-        __threadfence();
         epi_bar();
         if (te == 0) grid_arrive(p.sync + 2 * i + 1);
       }
@@ -1112,7 +1158,8 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
 }
 
 static size_t chain_smem_bytes(int mpad, int nw, int nx) {
-  return (size_t)nw * G_WTILE_BYTES + (size_t)nx * mpad * 128 + (5 * G_MAX_STAGES + 4) * 8 + 16 + (size_t)mpad * 4 + 1024;
+  return (size_t)nw * G_WTILE_BYTES + (size_t)nx * mpad * 128 + (5 * G_MAX_STAGES + 4) * 8 + 16 + (size_t)G_MAX_M * 4 +
+         (size_t)C_NORMW_MAX * 2 + 1024;
 }
 
 // K split of one chain op: minimise k-blocks on the busiest CTA (+ a term for the reduce cost of many splits)
@@ -1132,7 +1179,7 @@ static int chain_choose_splits(int n_tiles, int kblocks, int ctas) {
 }
 }  // namespace b2
 
-extern "C" B2TTS_API int b2tts_gemm_chain_ssq_slots(int n) { return n > 0 && n % b2::C_UNIT == 0 ? n / b2::C_UNIT : 0; }
+extern "C" B2TTS_API int b2tts_gemm_chain_ssq_slots(int n) { return n > 0 && n % b2::C_SSQ_FEATS == 0 ? n / b2::C_SSQ_FEATS : 0; }
 
 extern "C" B2TTS_API size_t b2tts_gemm_chain_workspace_bytes(int m, const int* n, const int* k, int nops) {
   using namespace b2;
@@ -1160,12 +1207,15 @@ extern "C" B2TTS_API int b2tts_gemm_chain(const b2tts_gemm_op* ops, int nops, in
   p.nops = nops; p.m = m; p.mpad = (m + 15) & ~15; p.rounding = rounding; p.eps = eps;
   p.tmem_cols = 32;
   while (p.tmem_cols < 2 * p.mpad) p.tmem_cols <<= 1;
-  p.nx = p.mpad <= 64 ? 4 : 3;
-  p.nw = 10;
-  while (p.nw > 4 && chain_smem_bytes(p.mpad, p.nw, p.nx) > 227 * 1024) --p.nw;
+  p.nx = p.nw = p.mpad <= 64 ? 8 : 4;           // 192 KiB / 128 KiB of ring; both rings share slot indices
   if (const char* e = getenv("B2TTS_CHAIN_NW")) {                // experiments only
     const int v = atoi(e);
-    if (v >= 2 && v <= G_MAX_STAGES && chain_smem_bytes(p.mpad, v, p.nx) <= 227 * 1024) p.nw = v;
+    if ((v == 4 || v == 8) && chain_smem_bytes(p.mpad, v, v) <= 227 * 1024) p.nw = p.nx = v;
+  }
+  p.cg = p.nw >= 8 ? 4 : 2;
+  if (const char* e = getenv("B2TTS_CHAIN_CG")) {                // experiments only
+    const int v = atoi(e);
+    if (v >= 1 && v <= p.nw / 2 && p.nw % v == 0) p.cg = v;
   }
   const int ctas = sm_count();
   CUtensorMap tmaps[C_MAX_OPS];
@@ -1207,7 +1257,7 @@ extern "C" B2TTS_API int b2tts_gemm_chain(const b2tts_gemm_op* ops, int nops, in
       c.ssq_lanes = g;
       B2_REQUIRE(o.ssq_in_slots % 4 == 0 || g == 1, B2TTS_EALIGN, "%s: op %d ssq_in_slots %d", what, i, o.ssq_in_slots);
     }
-    const size_t b = (size_t)c.splits * c.n * p.mpad * 4;
+    const size_t b = (size_t)c.splits * c.n * m * 4;
     if (b > part) part = b;
     int rc = make_x_tensor_map(&tmaps[i], o.x, o.x_row_stride, m, o.k, p.mpad, what);
     if (rc) return rc;

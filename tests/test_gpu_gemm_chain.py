@@ -46,8 +46,8 @@ def _chain(native, w, attn, resid, rounding, nops=4, in_place=False):
     res_in = r if in_place else resid
     act = torch.empty(m, inter, dtype=BF16, device="cuda")
     qkv = torch.empty(m, nq, dtype=BF16, device="cuda")
-    ssq1 = torch.empty(m, h // 16, dtype=torch.float32, device="cuda")
-    ssq2 = torch.empty(m, h // 16, dtype=torch.float32, device="cuda")
+    ssq1 = torch.empty(m, h // 128, dtype=torch.float32, device="cuda")
+    ssq2 = torch.empty(m, h // 128, dtype=torch.float32, device="cuda")
     ops = [dict(x=attn, packed=packed["o"], n=h, residual=res_in, out=r, epilogue=native.GEMM_RESIDUAL, ssq_out=ssq1),
            dict(x=r, packed=packed["gu"], n=2 * inter, out=act, epilogue=native.GEMM_SILU_MUL, norm_weight=w["ln1"], ssq_in=ssq1),
            dict(x=act, packed=packed["down"], n=h, residual=r, out=r, epilogue=native.GEMM_RESIDUAL, ssq_out=ssq2),
@@ -111,7 +111,7 @@ def test_chain_is_deterministic_and_graph_replayable(native):
     ws = native.gemm_chain_workspace(m, [(h, nq // 2), (2 * inter, h), (h, inter), (nq, h)], "cuda")
     r = resid.clone()
     act = torch.empty(m, inter, dtype=BF16, device="cuda"); qkv = torch.empty(m, nq, dtype=BF16, device="cuda")
-    s1 = torch.empty(m, h // 16, dtype=torch.float32, device="cuda"); s2 = torch.empty_like(s1)
+    s1 = torch.empty(m, h // 128, dtype=torch.float32, device="cuda"); s2 = torch.empty_like(s1)
 
     def body():
         for _ in range(5):

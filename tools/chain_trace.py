@@ -19,7 +19,7 @@ ln = torch.ones(h, device=DEV, dtype=BF16)
 attn = torch.randn(m, nq // 2, device=DEV, dtype=BF16)
 r = torch.randn(m, h, device=DEV, dtype=BF16)
 act = torch.empty(m, inter, device=DEV, dtype=BF16); qkv = torch.empty(m, nq, device=DEV, dtype=BF16)
-s1 = torch.empty(m, h // 16, device=DEV, dtype=torch.float32); s2 = torch.empty_like(s1)
+s1 = torch.empty(m, h // 128, device=DEV, dtype=torch.float32); s2 = torch.empty_like(s1)
 ws = nat.gemm_chain_workspace(m, [(h, nq // 2), (2 * inter, h), (h, inter), (nq, h)], DEV)
 
 
@@ -54,4 +54,14 @@ for l in range(chain):
         for k in range(1 if i else 0, 7):
             v = tt[:, k][t[l, :, i, k] > 0]
             cols.append(f"{names[k]:>9s} {v.min():6.1f}/{v.median():6.1f}/{v.max():6.1f}" if v.numel() else f"{names[k]:>9s}   -")
-        print(f"L{l} {ops[i]:8s}", "  ".join(cols))
+        raw = trace.view(chain, 4096 * 8)[l, :148 * 4 * 8].view(148, 4, 8)[:, i, 7].cpu()
+        ww, wx = (raw >> 32).double() / 1.965e3, (raw & 0xffffffff).double() / 1.965e3
+        print(f"L{l} {ops[i]:8s}", "  ".join(cols), f"  MMA waits us: W {ww.median():.1f}/{ww.max():.1f}  x {wx.median():.1f}/{wx.max():.1f}")
+
+kb = trace.view(chain, 4096 * 8)[chain - 1, 8192:8192 + 5 * 64].view(5, 64).cpu().double()
+t0 = kb[kb > 0].min()
+print("CTA 0, gate_up, per k-block (us since first stamp): x TMA issued | x landed (hop) | hop done | MMA has W | MMA has x")
+for idx in range(64):
+    if kb[0, idx] == 0:
+        break
+    print(f"  kb {idx:2d}: " + "  ".join(f"{(kb[e, idx] - t0) / 1965:7.2f}" for e in range(5)))

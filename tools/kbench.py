@@ -118,7 +118,7 @@ def chain_case(m, h, inter, nq, layers=8):
     attn = torch.randn(m, nq // 2, device=DEV, dtype=BF16)
     r = torch.randn(m, h, device=DEV, dtype=BF16)
     act = torch.empty(m, inter, device=DEV, dtype=BF16); qkv = torch.empty(m, nq, device=DEV, dtype=BF16)
-    s1 = torch.empty(m, h // 16, device=DEV, dtype=torch.float32); s2 = torch.empty_like(s1)
+    s1 = torch.empty(m, h // 128, device=DEV, dtype=torch.float32); s2 = torch.empty_like(s1)
     ws = nat.gemm_chain_workspace(m, [(h, nq // 2), (2 * inter, h), (h, inter), (nq, h)], DEV)
     t1 = torch.empty(m, nat.gemm_ssq_slots(m, h, nq // 2), device=DEV, dtype=torch.float32)
     t2 = torch.empty(m, nat.gemm_ssq_slots(m, h, inter), device=DEV, dtype=torch.float32)
