@@ -185,6 +185,98 @@ def time_attention_kernel(talker_runner, loop, iters: int = 3):
     return ms, alg, float(ctx.float().mean())
 
 
+def ncu_traffic() -> dict:
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures
+    (profiles/ncu_traffic.json, written from the .ncu-rep files by hand; see profiles/*_ncu_*.md)."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")
+    try:
+        with open(path) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return {}
+
+
+def _graph_ms(fn, launches: int, iters: int = 3):
+    """Median duration of one launch: `fn` issues `launches` launches; they are captured into one CUDA graph (no host
+    gaps) and the replay is bracketed by CUDA events on the launching stream."""
+    import torch
+    fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        fn()
+    times = []
+    for it in range(iters + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        if it:
+            times.append(e0.elapsed_time(e1) / launches)
+    return sorted(times)[len(times) // 2]
+
+
+def time_gemm_kernel(talker_runner, streams: int):
+    """The weight-streaming GEMM (gemm_stream_kernel) as the talker runs it: the 4 projections of every layer at
+    M = streams, over the model's own packed weights (2.8 GB, far larger than L2), with the production epilogues
+    and programmatic dependent launch.  Returns (ms per launch, algorithmic bytes per launch, launches)."""
+    import torch
+    import nano_qwen3tts_vllm_b200._native as nat
+    from nano_qwen3tts_vllm_b200.layers.linear import RowNorm, linear, linear_residual, linear_silu_mul
+    r = talker_runner
+    c = r.stack_config
+    dev = r.device
+    layers = r.model.model.layers if hasattr(r.model, "model") and hasattr(r.model.model, "layers") else None
+    if layers is None:
+        layers = [m for m in r.model.modules() if m.__class__.__name__ == "Qwen3TTSDecoderLayer"]
+    m = streams
+    resid = (torch.randn(m, c.hidden_size, device=dev) * 0.5).to(torch.bfloat16)
+    attn = (torch.randn(m, c.q_size, device=dev) * 0.5).to(torch.bfloat16)
+    eps, rnd = c.rms_norm_eps, nat.ROUND_EAGER
+
+    def launches():
+        x = resid.clone()
+        _, ssq = linear_residual(attn, layers[0].self_attn.o_proj.weight, x, out=x, want_ssq=True)
+        for layer in layers:
+            linear(x, layer.self_attn.qkv_proj.weight, norm=RowNorm(layer.input_layernorm.weight, ssq, eps, rnd))
+            _, ssq = linear_residual(attn, layer.self_attn.o_proj.weight, x, out=x, want_ssq=True)
+            act = linear_silu_mul(x, layer.mlp.gate_up_proj.weight, rnd,
+                                  norm=RowNorm(layer.post_attention_layernorm.weight, ssq, eps, rnd))
+            _, ssq = linear_residual(act, layer.mlp.down_proj.weight, x, out=x, want_ssq=True)
+    n = 4 * len(layers) + 1
+    ms = _graph_ms(launches, n)
+    w_bytes = 2.0 * (c.hidden_size * (c.q_size + 2 * c.kv_size) + c.q_size * c.hidden_size + 3 * c.hidden_size * c.intermediate_size)
+    io_bytes = 2.0 * m * (c.hidden_size + (c.q_size + 2 * c.kv_size) + c.q_size + c.hidden_size + c.hidden_size
+                          + c.intermediate_size + c.intermediate_size + c.hidden_size)
+    alg = (w_bytes + io_bytes) / 4.0                     # average over the 4 projections of a layer
+    return ms, alg, n
+
+
+def time_attention_long(device, streams: int = 64, ctx_len: int = 4096, layers: int = 3):
+    """paged_attn_kernel at the north-star shape (BASELINE configs[3]: ~4k-token KV): `streams` sequences of `ctx_len`
+    cached tokens, scattered pages, `layers` launches over different caches (each 2 x streams x ctx_len x 2 KiB)."""
+    import torch
+    import nano_qwen3tts_vllm_b200._native as nat
+    page, kvh, h, hd = 256, 8, 16, 128
+    pages_per = (ctx_len + page - 1) // page
+    npages = streams * pages_per
+    caches = [(torch.randn(npages, page, kvh, hd, device=device, dtype=torch.bfloat16),
+               torch.randn(npages, page, kvh, hd, device=device, dtype=torch.bfloat16)) for _ in range(layers)]
+    bt = torch.randperm(npages, generator=torch.Generator().manual_seed(13)).to(torch.int32).view(streams, pages_per).to(device)
+    lens = torch.full((streams,), ctx_len, dtype=torch.int32, device=device)
+    q = torch.randn(streams, h, hd, device=device, dtype=torch.bfloat16)
+    out = torch.empty_like(q)
+    max_ctx = pages_per * page
+    ws = torch.empty(max(16, nat.paged_attn_decode_workspace_bytes(streams, h, hd, max_ctx)), dtype=torch.uint8, device=device)
+
+    def launches():
+        for kc, vc in caches:
+            nat.paged_attn_decode(q, kc, vc, bt, lens, hd ** -0.5, max_ctx, out=out, workspace=ws)
+    ms = _graph_ms(launches, layers)
+    return ms, float(streams * (4096.0 * ctx_len + 8192.0))
+
+
 def run_device_loop(talker, predictor, mc, streams, steps, warmup, sampler: ClockSampler | None, dist_barrier=None):
     import torch
     import nano_qwen3tts_vllm_b200._native as nat
@@ -381,15 +473,32 @@ def main():
     if rank == 0:
         peak, peak_src = peaks()
         att_ms, att_alg, mean_ctx = time_attention_kernel(talker.model_runner, loop)
+        gemm_ms, gemm_alg, gemm_n = time_gemm_kernel(talker.model_runner, a.streams)
+        long_ms, long_alg = time_attention_long(device)
         lens_sum = float((loop.seq_lens - 1).sum())
         step_bytes = frame_bytes(mc, lens_sum)
-        att_gbs = att_alg / att_ms / 1e6
-        roofline = {"kernel": "paged_attn_kernel<2,false> (+ attn_combine_kernel when split-KV)", "bound": "hbm",
-                    "achieved": round(att_gbs, 1), "peak": peak, "unit": "GB/s", "frac": round(att_gbs / peak, 4),
-                    "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": att_alg, "launch_ms": round(att_ms, 5), "mean_context": round(mean_ctx, 1),
-                    "how": "CUDA events around a graph of 28 per-layer launches at the bench's end-of-run context lengths; "
-                           "bytes = sum_b(4096*L_b + 8192)"}
+        traffic = ncu_traffic()
+        att_gbs, gemm_gbs, long_gbs = att_alg / att_ms / 1e6, gemm_alg / gemm_ms / 1e6, long_alg / long_ms / 1e6
+        # the dominant kernel of the frame by time share (profiles/*_launches_summary.txt): the weight-streaming GEMM
+        roofline = {"kernel": "gemm_stream_kernel (qkv / o / gate_up / down projections, tcgen05 + TMEM)", "bound": "hbm",
+                    "achieved": round(gemm_gbs, 1), "peak": peak, "unit": "GB/s", "frac": round(gemm_gbs / peak, 4),
+                    "traffic": traffic.get("gemm_stream_kernel"), "traffic_note": traffic.get("_gemm_stream_kernel"),
+                    "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": gemm_alg, "launch_ms": round(gemm_ms, 5), "launches_timed": gemm_n,
+                    "how": f"CUDA events around one graph of the talker's {gemm_n} projection launches at M={a.streams} over the "
+                           "model's own weights (2.8 GB >> L2), production epilogues + PDL; bytes = 2*(K*N + M*K + M*N) "
+                           "averaged over the 4 projections of a layer"}
+        roofline_kernels = [
+            {"kernel": "paged_attn_kernel<2,false> (+ attn_combine_kernel when split-KV), bench contexts", "bound": "hbm",
+             "achieved": round(att_gbs, 1), "peak": peak, "unit": "GB/s", "frac": round(att_gbs / peak, 4),
+             "traffic": None, "algorithmic_bytes_per_launch": att_alg, "launch_ms": round(att_ms, 5),
+             "mean_context": round(mean_ctx, 1),
+             "how": "graph of 28 per-layer launches at the bench's end-of-run context lengths; bytes = sum_b(4096*L_b + 8192)"},
+            {"kernel": "paged_attn_kernel<2,false>, 64 sequences x 4096 cached tokens (BASELINE configs[3] KV length)",
+             "bound": "hbm", "achieved": round(long_gbs, 1), "peak": peak, "unit": "GB/s", "frac": round(long_gbs / peak, 4),
+             "traffic": traffic.get("paged_attn_kernel"), "traffic_note": traffic.get("_paged_attn_kernel"),
+             "algorithmic_bytes_per_launch": long_alg,
+             "launch_ms": round(long_ms, 5), "how": "graph of 3 launches over different 1 GiB caches, scattered pages"}]
         step_roof = {"bound": "hbm", "achieved": round(step_bytes / (ms_per_step / 1e3) / 1e9, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(step_bytes / (ms_per_step / 1e3) / 1e9 / peak, 4), "algorithmic_bytes_per_step": step_bytes,
                      "note": "whole frame: weights streamed once per pass (talker + 15 predictor passes) + talker KV"}
@@ -398,7 +507,7 @@ def main():
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                 "config": workload_config(a, a.streams), "clocks": clocks,
                 "rtf_per_stream": round(ms_per_step / 1e3 * FRAME_HZ, 5),
-                "roofline": roofline, "step_roofline": step_roof,
+                "roofline": roofline, "roofline_kernels": roofline_kernels, "step_roofline": step_roof,
                 "gpu_launches": int(lib_per_frame * a.steps),
                 "launches_per_step": {"libb200tts": int(lib_per_frame), "note": "includes the tcgen05 GEMMs; exponential_ noise and small torch copies are extra"}}
     # ---- end to end through the step API with host buffers

@@ -134,6 +134,8 @@ class ModelRunner:
         self.graphs = {}
         self.graph_pool = None
         torch.cuda.synchronize()
+        from ...layers.linear import release_packed
+        release_packed(self.model)
 
     def call(self, method_name, *args):
         return getattr(self, method_name)(*args)

@@ -30,9 +30,21 @@ def packed_weight(weight: torch.Tensor, mode: int = nat.PACK_PLAIN) -> torch.Ten
     if ent is None or ent[0] != ver:
         if torch.cuda.is_current_stream_capturing():
             raise RuntimeError("libb200tts: weight packed for the first time under graph capture; run a warm-up first")
-        ent = (ver, nat.gemm_pack_weight(weight, mode))
+        # the entry keeps `weight` alive: while it exists the allocator cannot hand the same address to another
+        # weight, so an address-keyed hit is always the right image (release_packed() drops a dead model's entries)
+        ent = (ver, nat.gemm_pack_weight(weight, mode), weight)
         _packed[key] = ent
     return ent[1]
+
+
+def release_packed(module: nn.Module) -> int:
+    """Drop the packed images of every weight that lives inside ``module``'s parameters (call when the model is
+    torn down, after its CUDA graphs are gone).  Returns the number of entries released."""
+    spans = [(p.data_ptr(), p.data_ptr() + p.numel() * p.element_size()) for p in module.parameters()]
+    dead = [k for k in _packed if any(lo <= k[0] < hi for lo, hi in spans)]
+    for k in dead:
+        del _packed[k]
+    return len(dead)
 
 
 def native_ok(m: int, n: int, k: int) -> bool:
