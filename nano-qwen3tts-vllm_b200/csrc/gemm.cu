@@ -104,6 +104,13 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "}"
       :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// one lane of a converged warp; the surrounding code stays warp-uniform, so operand descriptors live in uniform
+// registers instead of being broadcast lane by lane in front of every tcgen05.mma
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
 }
@@ -208,7 +215,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(recv_bar + 1);
   float* rstd_s = reinterpret_cast<float*>(tmem_slot + 2);        // [mpad]
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);       // provably warp-uniform
   const int lane = threadIdx.x & 31;
   const int S = p.splits;
   const int rank = blockIdx.x;                  // gridDim.x == S == cluster size: rank in cluster
@@ -269,23 +276,28 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     }
     __syncwarp();
   } else if (warp == 1) {
-    // =========================== MMA issuer
-    if (lane == 0) {
+    // =========================== MMA issuer: the whole warp walks the ring (uniform control flow and operands),
+    // one elected lane issues
+    {
       const uint32_t idesc = umma_idesc_bf16(mpad);
+      int stage = 0;
+      uint32_t ph = 0;
       for (int i = 0; i < nkb; ++i) {
-        const int stage = i % NS;
-        const uint32_t ph = (i / NS) & 1;
         mbar_wait(full_bar + stage, ph);
         tc_fence_after();
         const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
         const uint32_t b_addr = a_addr + G_WTILE_BYTES;
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < G_BK / 16; ++k)
-          umma_bf16(tmem_base, umma_desc_sw128(a_addr + k * 32), umma_desc_sw128(b_addr + k * 32), idesc,
-                    (uint32_t)((i | k) != 0));
-        umma_commit(empty_bar + stage);         // stage reusable once these MMAs have read it
+          for (int k = 0; k < G_BK / 16; ++k)
+            umma_bf16(tmem_base, umma_desc_sw128(a_addr + k * 32), umma_desc_sw128(b_addr + k * 32), idesc,
+                      (uint32_t)((i | k) != 0));
+          umma_commit(empty_bar + stage);       // stage reusable once these MMAs have read it
+        }
+        __syncwarp();
+        if (++stage == NS) { stage = 0; ph ^= 1; }
       }
-      umma_commit(accum_bar);                   // accumulator complete
+      if (elect_one()) umma_commit(accum_bar);  // accumulator complete
     }
     __syncwarp();
   } else {
