@@ -65,9 +65,17 @@ topk_sample_kernel(const void* __restrict__ logits, int64_t row_stride, const fl
       __syncthreads();
       const uint32_t prefix = sel_prefix;
       const uint32_t himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-      for (int i = tid; i < vocab; i += SMP_THREADS) {
-        const uint32_t key = f2key(vals[i]);
-        if ((key & himask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+      // logits of one row share a handful of sign/exponent bytes, so plain atomics would serialise on 2-8 bins:
+      // lanes with the same bin are grouped (match.any) and their leader adds the group's count once
+      for (int i0 = 0; i0 < vocab; i0 += SMP_THREADS) {
+        const int i = i0 + tid;
+        uint32_t bin = 256u;                         // 256 = not a candidate
+        if (i < vocab) {
+          const uint32_t key = f2key(vals[i]);
+          if ((key & himask) == prefix) bin = (key >> shift) & 255u;
+        }
+        const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+        if (bin < 256u && lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (uint32_t)__popc(peers));
       }
       __syncthreads();
       if (warp == 0) {

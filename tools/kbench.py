@@ -105,6 +105,26 @@ def gemm_case(m, n, k, splits=0, pdl=False, epilogue=0, chain=16):
                       "cublas_us": round(ms_c * 1e3, 2), "cublas_GBps": round(gb_c, 1)}), flush=True)
 
 
+def sampler_case(b, v, top_k=50, reps=16):
+    """`reps` top-k sampler launches per graph over different logits rows (lm_head output shape [b, v] bf16)."""
+    logits = [(torch.randn(b, v, device=DEV) * 2).to(BF16) for _ in range(reps)]
+    noise = torch.empty(b, v, device=DEV, dtype=torch.float32).exponential_(1)
+    temps = torch.full((b,), 0.9, device=DEV, dtype=torch.float32)
+    out = torch.empty(b, device=DEV, dtype=torch.int64)
+
+    def fn():
+        for lg in logits:
+            nat.topk_sample(lg, temps, noise, top_k=top_k, out=out)
+    fn(); torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        fn()
+    us = time_ms(lambda i: g.replay()) / reps * 1e3
+    alg = float(b * (2 * v + 4 * v + 12))
+    print(json.dumps({"kernel": "topk_sample", "B": b, "V": v, "top_k": top_k, "us": round(us, 2),
+                      "GBps": round(alg / us / 1e3, 1)}), flush=True)
+
+
 def chain_case(m, h, inter, nq, layers=8):
     """`layers` GEMM chains (o + gate_up + down + next qkv) back to back over different weights in one graph,
     against the same 4 x layers projections as separate b2tts_gemm_norm_bf16 launches."""
@@ -212,6 +232,9 @@ def main():
                 if s_ and (s_ > k // 64):
                     continue
                 gemm_case(m, n, k, splits=s_, pdl=bool(a.pdl))
+    if a.what == "sampler":
+        for b, v in ((64, 2048), (64, 3072), (1, 3072), (512, 2048)):
+            sampler_case(b, v)
     if a.what == "chain":
         for c in a.chain_cases.split(","):
             m, h, inter, nq = map(int, c.split(":"))
