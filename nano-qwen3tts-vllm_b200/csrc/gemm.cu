@@ -789,7 +789,9 @@ extern "C" int b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const v
 // Rounding points are those of gemm_stream_kernel (bf16(residual + bf16(acc)), norm of the rounded sum).
 namespace b2 {
 constexpr int C_MAX_OPS = 4;
-constexpr int C_THREADS = 224;
+constexpr int C_THREADS = 480;                   // warps 0-2 producers/MMA, 3-6 epilogue, 7-14 fused-norm warps
+constexpr int C_NORM0 = 224;                     // first norm-warp thread
+constexpr int C_WORKERS = 384;                   // epilogue + norm threads: the reduce phase uses all of them
 constexpr int C_EPI0 = 96;                       // first epilogue thread
 constexpr int C_SSQ_FEATS = 128;                 // output features per ssq slot (16 lanes x 8 features)
 constexpr int C_NORMW_MAX = 4096;                // largest K whose norm weight is staged in shared memory
@@ -816,7 +818,7 @@ struct ChainParams {
 };
 // debug: per-k-block clock64 stamps of CTA 0, op 1: stream e (0 TMA x issue, 1 x landed at the hop, 2 hop done, 3 MMA has W,
 // 4 MMA has x) x 64 k-blocks at trace[8192 + e * 64 + idx]
-#define C_KB_TRACE(e, idx) do { if (p.trace && cta == 0 && i == 1 && (idx) < 64) p.trace[8192 + (e) * 64 + (idx)] = (unsigned long long)clock64(); } while (0)
+#define C_KB_TRACE(e, idx) do { if (p.trace && cta == 0 && i == 2 && (idx) < 64) p.trace[8192 + (e) * 64 + (idx)] = (unsigned long long)clock64(); } while (0)
 #define C_TRACE(op_i, slot) do { if (p.trace && te == 0) p.trace[((int64_t)cta * C_MAX_OPS + (op_i)) * 8 + (slot)] = gtimer(); } while (0)
 
 __device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
@@ -832,13 +834,82 @@ __device__ __forceinline__ void grid_arrive(unsigned* ctr) {
 }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
+__device__ __forceinline__ void workers_bar() { asm volatile("bar.sync 3, 384;" ::: "memory"); }
+
+// Reduce phase of one chain op (all C_WORKERS worker threads of every CTA): unit = (row m, 8 consecutive features), lanes
+// run along the features: 32-byte scratch reads per split and 16-byte stores, all coalesced; the sums of squares of
+// 16 lanes (128 features) fold in a fixed shuffle tree into one ssq slot.  Splits are added in order: deterministic.
+__device__ __forceinline__ void chain_reduce(const ChainParams& p, const ChainOp& op, int S, int cta, int G, int tr, int lane,
+                                             bool eager) {
+    const int M = p.m;
+    const int N = op.n;
+    const int per_row = N >> 3;                       // units per row (a multiple of 16)
+    const int units = M * per_row;
+    const int slots = N / C_SSQ_FEATS;
+    for (int u0 = cta * C_WORKERS + (tr & ~31); u0 < units; u0 += G * C_WORKERS) {
+      const int u = u0 + lane;
+      const bool valid = u < units;
+      const int m = valid ? u / per_row : 0;
+      const int n = valid ? (u - m * per_row) * 8 : 0;
+      float acc[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+      if (valid) {
+        const float* src = p.partial + (int64_t)m * N + n;
+        for (int sp = 0; sp < S; ++sp, src += (int64_t)M * N) {
+          const float4 a = __ldcg(reinterpret_cast<const float4*>(src));
+          const float4 c = __ldcg(reinterpret_cast<const float4*>(src) + 1);
+          acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
+          acc[4] += c.x; acc[5] += c.y; acc[6] += c.z; acc[7] += c.w;
+        }
+      }
+      float qsum = 0.f;
+      if (op.epilogue == B2TTS_GEMM_SILU_MUL) {
+        if (valid) {
+          float o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float gt = rbf(acc[e]), up = rbf(acc[4 + e]);
+            o[e] = eager ? rbf(gsilu_f(gt)) * up : gsilu_f(gt) * up;
+          }
+          uint2 w;
+          w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
+          stg_v2(op.out + (int64_t)m * op.out_stride + (n >> 1), w);
+        }
+        continue;
+      }
+      if (valid) {
+        if (op.epilogue == B2TTS_GEMM_RESIDUAL) {
+          const uint4 rw = __ldcg(reinterpret_cast<const uint4*>(op.res + (int64_t)m * op.res_stride + n));
+          acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
+          acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
+          acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
+          acc[6] = rbf(acc[6]) + bf16lo(rw.w); acc[7] = rbf(acc[7]) + bf16hi(rw.w);
+        }
+        uint4 w;
+        w.x = pack_bf16(acc[0], acc[1]); w.y = pack_bf16(acc[2], acc[3]);
+        w.z = pack_bf16(acc[4], acc[5]); w.w = pack_bf16(acc[6], acc[7]);
+        stg_v4(op.out + (int64_t)m * op.out_stride + n, w);
+        qsum = fmaf(bf16lo(w.x), bf16lo(w.x), qsum); qsum = fmaf(bf16hi(w.x), bf16hi(w.x), qsum);
+        qsum = fmaf(bf16lo(w.y), bf16lo(w.y), qsum); qsum = fmaf(bf16hi(w.y), bf16hi(w.y), qsum);
+        qsum = fmaf(bf16lo(w.z), bf16lo(w.z), qsum); qsum = fmaf(bf16hi(w.z), bf16hi(w.z), qsum);
+        qsum = fmaf(bf16lo(w.w), bf16lo(w.w), qsum); qsum = fmaf(bf16hi(w.w), bf16hi(w.w), qsum);
+      }
+      if (op.ssq_out) {                               // warp-uniform
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) qsum += __shfl_xor_sync(0xffffffffu, qsum, o);
+        if (valid && (lane & 15) == 0) op.ssq_out[(int64_t)m * slots + n / C_SSQ_FEATS] = qsum;
+      }
+    }
+}
 
 __global__ void __launch_bounds__(C_THREADS, 1)
 gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
                   const __grid_constant__ CUtensorMap tm2, const __grid_constant__ CUtensorMap tm3) {
   extern __shared__ uint8_t smem_dyn[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
-  const int mpad = p.mpad, NW = p.nw, NX = p.nx, CG = p.cg;
+  const int mpad = p.mpad, NW = p.nw, NX = p.nx, CG = p.cg;          // NW == NX in {4, 8}; CG a power of two
+  const uint32_t CGL = 31 - __clz(CG);
   const int xstage = mpad * 128;
   uint8_t* wring = smem;
   uint8_t* xring = wring + NW * G_WTILE_BYTES;
@@ -853,7 +924,7 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
   float* rstd_s = reinterpret_cast<float*>(tmem_slot + 4);                         // keeps normw_s 16-byte aligned
   __nv_bfloat16* normw_s = reinterpret_cast<__nv_bfloat16*>(rstd_s + G_MAX_M);     // [C_NORMW_MAX], 16-byte aligned
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);       // provably warp-uniform
   const int lane = threadIdx.x & 31;
   const int G = gridDim.x;
   const int cta = blockIdx.x;
@@ -875,29 +946,30 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
   if (warp == 0) {
     // =========================== W producer: never waits for activations
     if (lane == 0) {
-      uint32_t j = 0;
+      uint32_t slot = 0, ph = 1;                 // ring slot and "empty" parity as counters: no div/mod per k-block
       for (int i = 0; i < p.nops; ++i) {
         const ChainOp& op = p.op[i];
         const int S = op.splits, items = op.n_tiles * S;
         for (int t = cta; t < items; t += G) {
           const int tile = t / S, s = t - tile * S;
-          const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
+          const int kb0 = (s * op.kblocks) / S, kb1 = ((s + 1) * op.kblocks) / S;     // 32-bit: splits <= 16, kblocks < 2^20
           const uint8_t* src = op.wp + ((int64_t)tile * op.kblocks + kb0) * G_WTILE_BYTES;
-          for (int kb = kb0; kb < kb1; ++kb, ++j, src += G_WTILE_BYTES) {
-            const uint32_t slot = j % NW;
-            mbar_wait(wempty + slot / CG, ((j / NW) & 1) ^ 1);
+          for (int kb = kb0; kb < kb1; ++kb, src += G_WTILE_BYTES) {
+            mbar_wait(wempty + (slot >> CGL), ph);
             mbar_expect_tx(wfull + slot, G_WTILE_BYTES);
             bulk_g2s(wring + slot * G_WTILE_BYTES, src, G_WTILE_BYTES, wfull + slot);
+            if (++slot == (uint32_t)NW) { slot = 0; ph ^= 1; }
           }
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
-    // =========================== MMA issuer
-    if (lane == 0) {
+    // =========================== MMA issuer: the whole warp walks the schedule (uniform control flow, operand
+    // descriptors in uniform registers), one elected lane issues; ring slot / phase / commit group are counters
+    {
       const uint32_t idesc = umma_idesc_bf16(mpad);
-      uint32_t j = 0, it = 0;
+      uint32_t it = 0, sw = 0, ph = 0, cgc = 0;
       for (int i = 0; i < p.nops; ++i) {
         const ChainOp& op = p.op[i];
         const int S = op.splits, items = op.n_tiles * S;
@@ -905,39 +977,45 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
         int kbi = 0;
         for (int t = cta; t < items; t += G, ++it) {
           const int tile = t / S, s = t - tile * S;
-          const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
+          const int kb0 = (s * op.kblocks) / S, kb1 = ((s + 1) * op.kblocks) / S;     // 32-bit: splits <= 16, kblocks < 2^20
           const uint32_t b = it & 1;
           mbar_wait(accempty + b, ((it >> 1) & 1) ^ 1);
           tc_fence_after();
           const uint32_t d_addr = tmem_base + b * (uint32_t)mpad;
-          for (int kb = kb0; kb < kb1; ++kb, ++j) {
-            const uint32_t sw = j % NW, sx = j % NX;
+          for (int kb = kb0; kb < kb1; ++kb) {
             const long long c0 = p.trace ? clock64() : 0;
-            mbar_wait(wfull + sw, (j / NW) & 1);
+            mbar_wait(wfull + sw, ph);
             const long long c1 = p.trace ? clock64() : 0;
-            C_KB_TRACE(3, kbi);
-            mbar_wait(xfull + sx, (j / NX) & 1);
-            C_KB_TRACE(4, kbi); ++kbi;
+            if (lane == 0) C_KB_TRACE(3, kbi);
+            mbar_wait(xfull + sw, ph);
+            if (lane == 0) C_KB_TRACE(4, kbi);
+            ++kbi;
             if (p.trace) { wait_w += (unsigned long long)(c1 - c0); wait_x += (unsigned long long)(clock64() - c1); }
             tc_fence_after();
             const uint32_t a_addr = smem_u32(wring + sw * G_WTILE_BYTES);
-            const uint32_t b_addr = smem_u32(xring + sx * xstage);
+            const uint32_t b_addr = smem_u32(xring + sw * xstage);
+            const bool release = ++cgc == (uint32_t)CG;
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < G_BK / 16; ++k)
-              umma_bf16(d_addr, umma_desc_sw128(a_addr + k * 32), umma_desc_sw128(b_addr + k * 32), idesc,
-                        (uint32_t)((kb > kb0) || (k > 0)));
-            if ((sw + 1) % CG == 0) umma_commit(wempty + sw / CG);
+              for (int k = 0; k < G_BK / 16; ++k)
+                umma_bf16(d_addr, umma_desc_sw128(a_addr + k * 32), umma_desc_sw128(b_addr + k * 32), idesc,
+                          (uint32_t)((kb > kb0) || (k > 0)));
+              if (release) umma_commit(wempty + (sw >> CGL));
+              if (kb == kb1 - 1) umma_commit(accfull + b);
+            }
+            __syncwarp();
+            if (release) cgc = 0;
+            if (++sw == (uint32_t)NW) { sw = 0; ph ^= 1; }
           }
-          umma_commit(accfull + b);
         }
-        if (p.trace) p.trace[((int64_t)cta * C_MAX_OPS + i) * 8 + 7] = (wait_w << 32) | (wait_x & 0xffffffffull);
+        if (p.trace && lane == 0) p.trace[((int64_t)cta * C_MAX_OPS + i) * 8 + 7] = (wait_w << 32) | (wait_x & 0xffffffffull);
       }
     }
     __syncwarp();
   } else if (warp == 2) {
     // =========================== x producer
     if (lane == 0) {
-      uint32_t j = 0;
+      uint32_t slot = 0, ph = 1;
       const uint32_t xbytes = (uint32_t)xstage;
       for (int i = 0; i < p.nops; ++i) {
         const ChainOp& op = p.op[i];
@@ -952,10 +1030,9 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
         int kbi = 0;
         for (int t = cta; t < items; t += G) {
           const int tile = t / S, s = t - tile * S;
-          const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
-          for (int kb = kb0; kb < kb1; ++kb, ++j) {
-            const uint32_t slot = j % NX;
-            mbar_wait(wempty + slot / CG, ((j / NX) & 1) ^ 1);
+          const int kb0 = (s * op.kblocks) / S, kb1 = ((s + 1) * op.kblocks) / S;     // 32-bit: splits <= 16, kblocks < 2^20
+          for (int kb = kb0; kb < kb1; ++kb) {
+            mbar_wait(wempty + (slot >> CGL), ph);
             C_KB_TRACE(0, kbi); ++kbi;
             // with a fused norm the tile lands "raw" and an epilogue warp releases it after the transform;
             // otherwise the copy completes straight on the barrier the MMA issuer waits on
@@ -969,19 +1046,61 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
               case 2: tma_load_2d(xring + slot * xstage, &tm2, kb * G_BK, 0, landed); break;
               default: tma_load_2d(xring + slot * xstage, &tm3, kb * G_BK, 0, landed); break;
             }
+            if (++slot == (uint32_t)NX) { slot = 0; ph ^= 1; }
           }
         }
       }
     }
     __syncwarp();
+  } else if (warp >= 7) {
+    // =========================== fused-norm warps: ring slot sx belongs to norm warp sx & 7 (or & 3 with a 4-slot
+    // ring), which tracks the phase of its slots' xraw barriers; 8 k-blocks are transformed concurrently.  They also
+    // take their share of every reduce phase.
+    const int wn = warp - 7;
+    const int tr = threadIdx.x - C_EPI0;        // 128..383 among the workers
+    const bool eager = p.rounding == B2TTS_ROUND_EAGER;
+    const int M = p.m;
+    const uint32_t own_mask = (uint32_t)(NX >= 8 ? 7 : 3);
+    uint32_t sx = 0, xraw_ph = 0;
+    for (int i = 0; i < p.nops; ++i) {
+      const ChainOp& op = p.op[i];
+      const bool normed = op.norm_w != nullptr;
+      const bool w_in_smem = normed && op.k <= C_NORMW_MAX;
+      const int S = op.splits, items = op.n_tiles * S;
+      if (normed) workers_bar();                // rstd_s / normw_s of this op are ready
+      for (int t = cta; t < items; t += G) {
+        const int tile = t / S, s = t - tile * S;
+        const int kb0 = (s * op.kblocks) / S, kb1 = ((s + 1) * op.kblocks) / S;     // 32-bit: splits <= 16, kblocks < 2^20
+        if (!normed) { sx = (sx + (uint32_t)(kb1 - kb0)) & (uint32_t)(NX - 1); continue; }   // NX is a power of two
+        for (int kb = kb0; kb < kb1; ++kb, sx = (sx + 1) & (uint32_t)(NX - 1)) {
+          if ((int)(sx & own_mask) != wn) continue;
+          mbar_wait(xraw + sx, (xraw_ph >> sx) & 1);
+          xraw_ph ^= 1u << sx;
+          uint8_t* xs = xring + sx * xstage;
+          const int c = lane & 7;
+          const uint4 wv = w_in_smem ? reinterpret_cast<const uint4*>(normw_s)[kb * 8 + c]
+                                     : ldg_v4(op.norm_w + (int64_t)kb * G_BK + c * 8);
+#pragma unroll 4
+          for (int r = lane >> 3; r < M; r += 4) {
+            uint4* cell = reinterpret_cast<uint4*>(xs + r * 128 + ((c ^ (r & 7)) << 4));
+            *cell = norm8(*cell, wv, rstd_s[r], eager);
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(xfull + sx);
+        }
+      }
+      workers_bar();                            // barrier A(i) passed (the epilogue warps waited on it)
+      chain_reduce(p, op, S, cta, G, tr, lane, eager);
+      workers_bar();                            // this CTA's share of the reduce is complete
+    }
   } else {
-    // =========================== epilogue warps: x norm hop, accumulator drain, reduce phase
+    // =========================== epilogue warps: accumulator drain, grid barriers, reduce phase
     const int te = threadIdx.x - C_EPI0;
     const int q = warp & 3;                     // TMEM lane quarter this warp may read
     const bool eager = p.rounding == B2TTS_ROUND_EAGER;
     const int M = p.m;
-    const int wq = warp - 3;                    // 0..3
-    uint32_t j = 0, it = 0, xraw_ph = 0;
+    uint32_t it = 0;
     C_TRACE(0, 0);
     pdl_wait();
     for (int i = 0; i < p.nops; ++i) {
@@ -1016,41 +1135,14 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
         if (w_in_smem)                                    // the norm weight once per op, not once per k-block
           for (int c = te; c < op.k / 8; c += 128)
             reinterpret_cast<uint4*>(normw_s)[c] = ldg_v4(op.norm_w + c * 8);
-        epi_bar();
+        workers_bar();                            // releases the norm warps into this op
       }
       C_TRACE(i, 2);
       const int S = op.splits, items = op.n_tiles * S;
       int kbi = 0;
       for (int t = cta; t < items; t += G, ++it) {
         const int tile = t / S, s = t - tile * S;
-        const int kb0 = (int)(((int64_t)s * op.kblocks) / S), kb1 = (int)(((int64_t)(s + 1) * op.kblocks) / S);
-        if (!normed) {
-          j += (uint32_t)(kb1 - kb0);                    // the x tiles go from the TMA unit straight to the MMA issuer
-        } else {
-          // slot sx = j % NX (NX a multiple of 4) always belongs to epilogue warp sx & 3: the four warps transform
-          // four consecutive k-blocks concurrently, and each tracks the phase of its own slots' xraw barriers
-          for (int kb = kb0; kb < kb1; ++kb, ++j, ++kbi) {
-            const uint32_t sx = j % NX;
-            if ((int)(sx & 3) != wq) continue;
-            mbar_wait(xraw + sx, (xraw_ph >> sx) & 1);
-            xraw_ph ^= 1u << sx;
-            if (lane == 0) C_KB_TRACE(1, kbi);
-            if (kb == kb0 && t == cta) C_TRACE(i, 3);
-            uint8_t* xs = xring + sx * xstage;
-            const int c = lane & 7;
-            const uint4 wv = w_in_smem ? reinterpret_cast<const uint4*>(normw_s)[kb * 8 + c]
-                                       : ldg_v4(op.norm_w + (int64_t)kb * G_BK + c * 8);
-#pragma unroll 4
-            for (int r = lane >> 3; r < M; r += 4) {
-              uint4* cell = reinterpret_cast<uint4*>(xs + r * 128 + ((c ^ (r & 7)) << 4));
-              *cell = norm8(*cell, wv, rstd_s[r], eager);
-            }
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(xfull + sx);
-            if (lane == 0) C_KB_TRACE(2, kbi);
-          }
-        }
+        const int kb0 = (s * op.kblocks) / S, kb1 = ((s + 1) * op.kblocks) / S;     // 32-bit: splits <= 16, kblocks < 2^20
         // drain the accumulator of this item to the split-K scratch [split][row m][feature n]: thread = feature,
         // so for each batch row a warp stores 32 consecutive floats
         const uint32_t b = it & 1;
@@ -1082,76 +1174,12 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
       epi_bar();
       C_TRACE(i, 5);
       if (i == p.nops - 1) pdl_launch();
-      // ---- reduce phase: unit = (row m, 8 consecutive features), lanes run along the features: 32-byte
-      // scratch reads per split and 16-byte stores, all coalesced; the sums of squares of 16 lanes (128
-      // features) fold in a fixed shuffle tree into one ssq slot
-      {
-        const int N = op.n;
-        const int per_row = N >> 3;                       // units per row (a multiple of 16)
-        const int units = M * per_row;
-        const int slots = N / C_SSQ_FEATS;
-        for (int u0 = cta * 128 + (te & ~31); u0 < units; u0 += G * 128) {
-          const int u = u0 + lane;
-          const bool valid = u < units;
-          const int m = valid ? u / per_row : 0;
-          const int n = valid ? (u - m * per_row) * 8 : 0;
-          float acc[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-          if (valid) {
-            const float* src = p.partial + (int64_t)m * N + n;
-            for (int sp = 0; sp < S; ++sp, src += (int64_t)M * N) {
-              const float4 a = __ldcg(reinterpret_cast<const float4*>(src));
-              const float4 c = __ldcg(reinterpret_cast<const float4*>(src) + 1);
-              acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
-              acc[4] += c.x; acc[5] += c.y; acc[6] += c.z; acc[7] += c.w;
-            }
-          }
-          float qsum = 0.f;
-          if (op.epilogue == B2TTS_GEMM_SILU_MUL) {
-            if (valid) {
-              float o[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float gt = rbf(acc[e]), up = rbf(acc[4 + e]);
-                o[e] = eager ? rbf(gsilu_f(gt)) * up : gsilu_f(gt) * up;
-              }
-              uint2 w;
-              w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
-              stg_v2(op.out + (int64_t)m * op.out_stride + (n >> 1), w);
-            }
-            continue;
-          }
-          if (valid) {
-            if (op.epilogue == B2TTS_GEMM_RESIDUAL) {
-              const uint4 rw = __ldcg(reinterpret_cast<const uint4*>(op.res + (int64_t)m * op.res_stride + n));
-              acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
-              acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
-              acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
-              acc[6] = rbf(acc[6]) + bf16lo(rw.w); acc[7] = rbf(acc[7]) + bf16hi(rw.w);
-            }
-            uint4 w;
-            w.x = pack_bf16(acc[0], acc[1]); w.y = pack_bf16(acc[2], acc[3]);
-            w.z = pack_bf16(acc[4], acc[5]); w.w = pack_bf16(acc[6], acc[7]);
-            stg_v4(op.out + (int64_t)m * op.out_stride + n, w);
-            qsum = fmaf(bf16lo(w.x), bf16lo(w.x), qsum); qsum = fmaf(bf16hi(w.x), bf16hi(w.x), qsum);
-            qsum = fmaf(bf16lo(w.y), bf16lo(w.y), qsum); qsum = fmaf(bf16hi(w.y), bf16hi(w.y), qsum);
-            qsum = fmaf(bf16lo(w.z), bf16lo(w.z), qsum); qsum = fmaf(bf16hi(w.z), bf16hi(w.z), qsum);
-            qsum = fmaf(bf16lo(w.w), bf16lo(w.w), qsum); qsum = fmaf(bf16hi(w.w), bf16hi(w.w), qsum);
-          }
-          if (op.ssq_out) {                               // warp-uniform
-#pragma unroll
-            for (int o = 1; o < 16; o <<= 1) qsum += __shfl_xor_sync(0xffffffffu, qsum, o);
-            if (valid && (lane & 15) == 0) op.ssq_out[(int64_t)m * slots + n / C_SSQ_FEATS] = qsum;
-          }
-        }
-      }
+      workers_bar();
+      chain_reduce(p, op, S, cta, G, te, lane, eager);
+      workers_bar();
       // ---- barrier B(i): the rows op i+1 reads are complete (arrive only; the readers wait)
       C_TRACE(i, 6);
-      if (i + 1 < p.nops) {
-        epi_bar();
-        if (te == 0) grid_arrive(p.sync + 2 * i + 1);
-      }
+      if (i + 1 < p.nops && te == 0) grid_arrive(p.sync + 2 * i + 1);
     }
   }
   pdl_launch();
