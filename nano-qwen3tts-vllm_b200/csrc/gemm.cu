@@ -252,26 +252,38 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     // x: one 2-D tensor-map copy per k-block (SWIZZLE_128B: lands as the UMMA B tile, rows >= M
     // zero-filled), requested after the wait.  Both go through the TMA unit, so neither the HBM nor
     // the L2 round trip is ever paid per block by a waiting thread.
-    if (lane == 0) {
+    {
+      // the whole warp walks the ring (uniform addresses and barriers), one elected lane issues each copy
       const uint8_t* src = p.wp + ((int64_t)tile * p.kblocks + kb_begin) * G_WTILE_BYTES;
       const uint32_t xbytes = (uint32_t)mpad * 128u;
       const int first = min(nkb, NS);
-      for (int i = 0; i < first; ++i) {
-        mbar_expect_tx(full_bar + i, G_WTILE_BYTES);
-        bulk_g2s(smem + i * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + i);
+      if (elect_one()) {
+        for (int i = 0; i < first; ++i) {
+          mbar_expect_tx(full_bar + i, G_WTILE_BYTES);
+          bulk_g2s(smem + i * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + i);
+        }
       }
+      __syncwarp();
       pdl_wait();
-      for (int i = 0; i < first; ++i) {
-        mbar_expect_tx(raw_bar + i, xbytes);
-        tma_load_2d(smem + i * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, 0, raw_bar + i);
+      if (elect_one()) {
+        for (int i = 0; i < first; ++i) {
+          mbar_expect_tx(raw_bar + i, xbytes);
+          tma_load_2d(smem + i * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, 0, raw_bar + i);
+        }
       }
+      __syncwarp();
+      int stage = first == NS ? 0 : first;
+      uint32_t ph = 1;                              // parity of the "empty" wait: first reuse of a stage waits on phase 0
       for (int i = first; i < nkb; ++i) {
-        const int stage = i % NS;
-        mbar_wait(empty_bar + stage, ((i / NS) & 1) ^ 1);
-        mbar_expect_tx(full_bar + stage, G_WTILE_BYTES);
-        bulk_g2s(smem + stage * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + stage);
-        mbar_expect_tx(raw_bar + stage, xbytes);
-        tma_load_2d(smem + stage * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, 0, raw_bar + stage);
+        mbar_wait(empty_bar + stage, ph ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(full_bar + stage, G_WTILE_BYTES);
+          bulk_g2s(smem + stage * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + stage);
+          mbar_expect_tx(raw_bar + stage, xbytes);
+          tma_load_2d(smem + stage * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, 0, raw_bar + stage);
+        }
+        __syncwarp();
+        if (++stage == NS) { stage = 0; ph ^= 1; }
       }
     }
     __syncwarp();
@@ -944,8 +956,9 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // =========================== W producer: never waits for activations
-    if (lane == 0) {
+    // =========================== W producer: never waits for activations (whole warp walks the schedule, one
+    // elected lane issues: addresses and barriers stay in uniform registers)
+    {
       uint32_t slot = 0, ph = 1;                 // ring slot and "empty" parity as counters: no div/mod per k-block
       for (int i = 0; i < p.nops; ++i) {
         const ChainOp& op = p.op[i];
@@ -956,8 +969,11 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
           const uint8_t* src = op.wp + ((int64_t)tile * op.kblocks + kb0) * G_WTILE_BYTES;
           for (int kb = kb0; kb < kb1; ++kb, src += G_WTILE_BYTES) {
             mbar_wait(wempty + (slot >> CGL), ph);
-            mbar_expect_tx(wfull + slot, G_WTILE_BYTES);
-            bulk_g2s(wring + slot * G_WTILE_BYTES, src, G_WTILE_BYTES, wfull + slot);
+            if (elect_one()) {
+              mbar_expect_tx(wfull + slot, G_WTILE_BYTES);
+              bulk_g2s(wring + slot * G_WTILE_BYTES, src, G_WTILE_BYTES, wfull + slot);
+            }
+            __syncwarp();
             if (++slot == (uint32_t)NW) { slot = 0; ph ^= 1; }
           }
         }
@@ -1013,8 +1029,8 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
     }
     __syncwarp();
   } else if (warp == 2) {
-    // =========================== x producer
-    if (lane == 0) {
+    // =========================== x producer (warp-uniform as well)
+    {
       uint32_t slot = 0, ph = 1;
       const uint32_t xbytes = (uint32_t)xstage;
       for (int i = 0; i < p.nops; ++i) {
@@ -1022,7 +1038,8 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
         if (i == 0) {
           pdl_wait();
         } else {
-          grid_wait(p.sync + 2 * (i - 1) + 1, (unsigned)G);
+          if (lane == 0) grid_wait(p.sync + 2 * (i - 1) + 1, (unsigned)G);
+          __syncwarp();
           fence_proxy_async_all();
         }
         const int S = op.splits, items = op.n_tiles * S;
@@ -1033,10 +1050,12 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
           const int kb0 = (s * op.kblocks) / S, kb1 = ((s + 1) * op.kblocks) / S;     // 32-bit: splits <= 16, kblocks < 2^20
           for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(wempty + (slot >> CGL), ph);
-            C_KB_TRACE(0, kbi); ++kbi;
+            if (lane == 0) C_KB_TRACE(0, kbi);
+            ++kbi;
             // with a fused norm the tile lands "raw" and an epilogue warp releases it after the transform;
             // otherwise the copy completes straight on the barrier the MMA issuer waits on
             uint64_t* landed = normed ? xraw + slot : xfull + slot;
+            if (elect_one()) {
             mbar_expect_tx(landed, xbytes);
             // the tensor map must be addressed in param space: selecting a pointer at run time would make the
             // compiler copy the maps to local memory, and every copy would then fetch its descriptor from DRAM
@@ -1046,6 +1065,8 @@ gemm_chain_kernel(const ChainParams p, const __grid_constant__ CUtensorMap tm0, 
               case 2: tma_load_2d(xring + slot * xstage, &tm2, kb * G_BK, 0, landed); break;
               default: tma_load_2d(xring + slot * xstage, &tm3, kb * G_BK, 0, landed); break;
             }
+            }
+            __syncwarp();
             if (++slot == (uint32_t)NX) { slot = 0; ph ^= 1; }
           }
         }
