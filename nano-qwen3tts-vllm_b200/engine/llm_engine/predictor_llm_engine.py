@@ -25,10 +25,71 @@ class PredictorLLMEngine(LLMEngine):
                 self.scheduler.request_id_to_seq[request_id] = seq
             self.scheduler.add(seq)
 
+    # The predictor never stops on an EOS id (config.eos stays -1: no tokenizer, predictor_llm_engine.py:33-66 of the
+    # reference finishes on max_tokens), so the sampled codes are only needed on the host when a sequence finishes.
+    # With ``defer_tokens`` the per-step ``.tolist()`` of the reference (one PCIe round trip and one stream
+    # synchronisation per codebook) becomes one read per burst; results are identical.
+    defer_tokens = True
+    PENDING = -2                                  # placeholder id in Sequence.token_ids until the codes are read back
+
+    def _resolve(self, seqs):
+        """Read every deferred step back in one transfer and patch the placeholders of ``seqs``."""
+        steps = getattr(self, "_steps", None)
+        if not steps:
+            return
+        sizes = [int(t.numel()) for t in steps]
+        flat = torch.cat(steps).tolist()                                     # the one synchronisation of the burst
+        offs = [0]
+        for n in sizes:
+            offs.append(offs[-1] + n)
+        for s in seqs:
+            refs = getattr(s, "_deferred", None)
+            if not refs:
+                continue
+            base = len(s.token_ids) - len(refs)
+            for k, (step, row) in enumerate(refs):
+                s.token_ids[base + k] = flat[offs[step] + row]
+            s.last_token = s.token_ids[-1]
+            s._deferred = []
+
+    def _step_deferred(self, seqs, is_prefill):
+        steps = self.__dict__.setdefault("_steps", [])
+        prev = None
+        if not is_prefill:
+            last = len(steps) - 1
+            rows = [s._deferred[-1] if getattr(s, "_deferred", None) else None for s in seqs]
+            if all(r is not None and r[0] == last for r in rows):
+                idx = [r[1] for r in rows]
+                prev = steps[last] if idx == list(range(steps[last].numel())) else \
+                    steps[last][torch.tensor(idx, device=steps[last].device)]
+            elif any(r is not None for r in rows):
+                self._resolve(seqs)                                          # mixed batch: fall back to host tokens
+        tokens = self.model_runner.call("run_deferred", seqs, is_prefill, prev)
+        steps.append(tokens)
+        for row, s in enumerate(seqs):
+            if not hasattr(s, "_deferred"):
+                s._deferred = []
+            s._deferred.append((len(steps) - 1, row))
+        self.scheduler.postprocess(seqs, [self.PENDING] * len(seqs))
+        finished = [s for s in seqs if s.is_finished]
+        if finished:
+            self._resolve(finished)
+        if not self.scheduler.running and not self.scheduler.waiting:
+            steps.clear()                                                    # nothing refers to the old steps any more
+        elif len(steps) > 64:                                                # continuous traffic: bound the backlog
+            self._resolve(list(self.scheduler.running))
+            steps.clear()
+
     def step(self):
         seqs, is_prefill = self.scheduler.schedule()
         if not seqs:
             return [], 0
+        if self.defer_tokens and self.scheduler.eos < 0 and all(not s.token_ids or hasattr(s, "_deferred") for s in seqs):
+            self._step_deferred(seqs, is_prefill)
+            for s in seqs:
+                s.generation_steps += 1
+            outputs = [(s.request_id, s.seq_id, s.completion_token_ids) for s in seqs if s.is_finished]
+            return outputs, (sum(len(s) for s in seqs) if is_prefill else -len(seqs))
         token_ids = self.model_runner.call("run", seqs, is_prefill)
         self.scheduler.postprocess(seqs, token_ids)
         for s in seqs:

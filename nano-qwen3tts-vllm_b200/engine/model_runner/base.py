@@ -43,27 +43,57 @@ class StepLayout:
             self.offsets[name] = (off, nbytes, dt, w)
             off += (nbytes + 15) // 16 * 16
         self.nbytes = off
-        self.host = torch.zeros(off, dtype=torch.uint8)
-        if torch.cuda.is_available():
-            self.host = self.host.pin_memory()
+        # a RING of pinned staging buffers: a step's upload is asynchronous and the host may already be filling the
+        # layout of a later step (the predictor's deferred-token burst never synchronises in between), so a buffer
+        # is rewritten only after the copy that read it has completed (per-buffer event)
         self.dev = torch.zeros(off, dtype=torch.uint8, device=device)
-        hn = self.host.numpy()
-        self.h, self.d = {}, {}
         tdt = {np.int64: torch.int64, np.int32: torch.int32, np.float32: torch.float32}
+        self.d = {}
         for name, (o, n, dt, w) in self.offsets.items():
-            hv = hn[o:o + n].view(dt)
             dv = self.dev[o:o + n].view(tdt[dt])
             if w > 1 or name == "block_tables":
-                hv, dv = hv.reshape(max_bs, w), dv.view(max_bs, w)
-            self.h[name], self.d[name] = hv, dv
-        self.h["slot_mapping"][:] = -1
-        self.h["block_tables"][:] = -1
-        self.h["temperatures"][:] = 1.0
-        self.h["gen_steps"][:] = 1
+                dv = dv.view(max_bs, w)
+            self.d[name] = dv
+        self.hosts, self.hviews, self.events = [], [], []
+        for _ in range(self.RING):
+            host = torch.zeros(off, dtype=torch.uint8)
+            if torch.cuda.is_available():
+                host = host.pin_memory()
+            hn = host.numpy()
+            views = {}
+            for name, (o, n, dt, w) in self.offsets.items():
+                hv = hn[o:o + n].view(dt)
+                if w > 1 or name == "block_tables":
+                    hv = hv.reshape(max_bs, w)
+                views[name] = hv
+            views["slot_mapping"][:] = -1
+            views["block_tables"][:] = -1
+            views["temperatures"][:] = 1.0
+            views["gen_steps"][:] = 1
+            self.hosts.append(host)
+            self.hviews.append(views)
+            self.events.append(None)
+        self.cur = 0
+        self.host, self.h = self.hosts[0], self.hviews[0]
         self.upload()
+
+    RING = 24
+
+    def begin(self):
+        """Rotate to the next staging buffer (waits only if its last upload is still pending) and return its views."""
+        self.cur = (self.cur + 1) % self.RING
+        ev = self.events[self.cur]
+        if ev is not None:
+            ev.synchronize()
+        self.host, self.h = self.hosts[self.cur], self.hviews[self.cur]
+        return self.h
 
     def upload(self):
         self.dev.copy_(self.host, non_blocking=True)
+        if torch.cuda.is_available():
+            ev = self.events[self.cur] or torch.cuda.Event()
+            ev.record()
+            self.events[self.cur] = ev
 
 
 class ModelRunner:
@@ -223,19 +253,24 @@ class ModelRunner:
     def fill_decode_layout(self, seqs: list[Sequence], padded: int):
         """Write the decode layout of ``seqs`` into the staging buffer (rows >= len(seqs) up to
         ``padded`` are graph padding: slot -1, context 0) and upload it."""
-        h, bs, n = self.layout.h, self.block_size, len(seqs)
+        h, bs, n = self.layout.begin(), self.block_size, len(seqs)
+        # one bulk numpy assignment per field (a per-element store costs ~100 ns each: 7 x 64 of them per step)
+        lens = [s.num_tokens for s in seqs]
+        h["positions"][:n] = [self.decode_position(s) for s in seqs]
+        h["context_lens"][:n] = lens
+        h["slot_mapping"][:n] = [s.block_table[-1] * bs + s.last_block_num_tokens - 1 for s in seqs]    # base.py:227
+        h["temperatures"][:n] = [s.temperature for s in seqs]
+        h["gen_steps"][:n] = [s.generation_steps for s in seqs]
+        h["last_tokens"][:n] = [s.last_token if s.last_token is not None else 0 for s in seqs]
+        bt = h["block_tables"]
         for i, s in enumerate(seqs):
-            ln = len(s)
-            h["positions"][i] = self.decode_position(s)
-            h["context_lens"][i] = ln
-            h["slot_mapping"][i] = s.block_table[-1] * bs + s.last_block_num_tokens - 1      # base.py:227
-            h["temperatures"][i] = s.temperature
-            h["gen_steps"][i] = s.generation_steps
-            h["last_tokens"][i] = s.last_token if s.last_token is not None else 0
             nb = len(s.block_table)
             if nb > self.max_blocks:
-                raise RuntimeError(f"sequence of {ln} tokens exceeds max_model_len={self.config.max_model_len}")
-            h["block_tables"][i, :nb] = s.block_table
+                raise RuntimeError(f"sequence of {lens[i]} tokens exceeds max_model_len={self.config.max_model_len}")
+            if nb == 1:
+                bt[i, 0] = s.block_table[0]
+            else:
+                bt[i, :nb] = s.block_table
         if padded > n:
             h["positions"][n:padded] = 0
             h["context_lens"][n:padded] = 0

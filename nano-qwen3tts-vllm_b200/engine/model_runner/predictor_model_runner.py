@@ -34,7 +34,9 @@ class PredictorModelRunner(ModelRunner):
         return self.model(emb, d["positions"][:rows])
 
     @torch.inference_mode()
-    def run_model(self, seqs: list[Sequence], is_prefill: bool):
+    def run_model(self, seqs: list[Sequence], is_prefill: bool, prev_tokens: torch.Tensor | None = None):
+        """``prev_tokens`` [n] (device): the codes sampled by the previous step for these rows, used instead of
+        the host-side ``seq.last_token`` (deferred-token mode: the ids have not crossed PCIe yet)."""
         n = len(seqs)
         steps = [s.generation_steps for s in seqs]
         if is_prefill:
@@ -44,6 +46,8 @@ class PredictorModelRunner(ModelRunner):
         gb = self.pick_graph(n)
         rows = gb or n
         self.fill_decode_layout(seqs, rows)
+        if prev_tokens is not None:
+            self.layout.d["last_tokens"][:n].copy_(prev_tokens)              # stream-ordered after the upload
         self.set_decode_context(rows)
         if gb is None:
             hidden = self.decode_body(rows)
@@ -59,3 +63,14 @@ class PredictorModelRunner(ModelRunner):
         token_ids = self.sampler(logits, temperatures, top_k=self.top_k).tolist()
         reset_context()
         return token_ids
+
+    @torch.inference_mode()
+    def run_deferred(self, seqs: list[Sequence], is_prefill: bool, prev_tokens: torch.Tensor | None) -> torch.Tensor:
+        """``run`` without the device->host read: returns the sampled codes as a device tensor [n].  The 15-step
+        predictor burst then costs ONE synchronisation (when the sequences finish) instead of one per step; the
+        next step's input embedding is gathered from ``prev_tokens`` on the device."""
+        logits = self.run_model(seqs, is_prefill, prev_tokens)
+        temperatures = self.layout.d["temperatures"][:len(seqs)] if not is_prefill else self.prepare_sample(seqs)
+        tokens = self.sampler(logits, temperatures, top_k=self.top_k)
+        reset_context()
+        return tokens
