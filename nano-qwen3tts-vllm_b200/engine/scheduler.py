@@ -45,6 +45,14 @@ class Scheduler:
         return True
 
     def _schedule_decode(self) -> list[Sequence]:
+        # fast path (every steady-state decode step): all running sequences fit, all are ready and none opens a new
+        # KV page this step, so the batch is the running queue in order and the queue is left as it is - exactly what
+        # the general loop below produces, without its per-sequence pops and allocator calls
+        n = len(self.running)
+        if 0 < n <= self.max_num_seqs:
+            bs, ready = self.block_manager.block_size, self._ready
+            if all(s.num_tokens % bs != 1 and ready(s) for s in self.running):
+                return list(self.running)
         picked = []
         for _ in range(len(self.running)):
             if not self.running or len(picked) >= self.max_num_seqs:
