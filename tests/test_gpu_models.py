@@ -171,3 +171,43 @@ def test_step_api_frame_protocol(engines):
         talker.clear_request(rid)
     assert talker.is_finished()
     assert len(talker.scheduler.block_manager.free_block_ids) == 8
+
+
+def test_predictor_deferred_tokens_equal_per_step_readback(engines):
+    """``PredictorLLMEngine.defer_tokens`` (codes stay on the device until a sequence finishes: one read per burst)
+    returns exactly the codes of the reference's per-step ``.tolist()`` protocol, including staggered arrivals
+    (a request added in the middle of another one's burst: mixed generation steps, fallback to host tokens)."""
+    from nano_qwen3tts_vllm_b200.sampling_params import SamplingParams
+    _, predictor, (td, pd, tw, pw) = engines
+    g = torch.Generator().manual_seed(77)
+    inputs = [(torch.randn(1, 2, td.hidden_size, generator=g) * 0.05).to(BF16).pin_memory() for _ in range(5)]
+    sp = SamplingParams(temperature=0.9, max_tokens=17)      # 2 prompt rows count as completion tokens (interface.py:1196)
+
+    def burst(defer: bool):
+        predictor.defer_tokens = defer
+        predictor.model_runner.kv_cache.zero_()
+        torch.manual_seed(1234)                    # same sampler noise in both runs
+        torch.cuda.manual_seed(1234)
+        done, steps = {}, 0
+        for i in range(3):
+            predictor.add_request([inputs[i]], sp, request_id=f"r{i}")
+        while len(done) < 5:
+            if steps == 4:                         # two late arrivals while r0..r2 are mid-burst
+                for i in (3, 4):
+                    predictor.add_request([inputs[i]], sp, request_id=f"r{i}")
+            fin, _ = predictor.step()
+            steps += 1
+            for rid, _, codes in fin:
+                done[rid] = list(codes)
+            assert steps < 200
+        return done
+
+    try:
+        want = burst(False)
+        got = burst(True)
+    finally:
+        predictor.defer_tokens = True
+    assert set(got) == set(want) == {f"r{i}" for i in range(5)}
+    for rid in want:
+        assert len(want[rid]) == 15 and all(0 <= c < pd.vocab_size for c in got[rid]), rid
+        assert got[rid] == want[rid], rid
