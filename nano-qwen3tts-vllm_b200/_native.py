@@ -153,6 +153,9 @@ def paged_attn_decode(q, k_cache, v_cache, block_table, context_lens, scale, max
     return out
 
 
+_PDL_ATTN = os.environ.get("B2TTS_PDL_ATTN", "1") != "0"       # experiments: launch the fused attention without PDL
+
+
 def fused_decode_attn_workspace(batch, num_heads, head_dim, max_ctx, device) -> torch.Tensor:
     """Zero-filled scratch for ``fused_decode_attn`` (split partials + per-row tickets; the kernel leaves the
     tickets zero, so one allocation serves every later launch of up to ``batch`` rows)."""
@@ -181,7 +184,7 @@ def fused_decode_attn(q, k, v, q_weight, k_weight, eps, positions, inv_freq, slo
         _ptr(modality), float(attention_scaling), slot_mapping.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
         block_table.data_ptr(), block_table.stride(0), context_lens.data_ptr(), out.data_ptr(),
         workspace.data_ptr(), workspace.numel() * workspace.element_size(), b, h, kvh, hd, page, float(scale),
-        int(max_ctx), int(rounding), int(bool(pdl)), _stream()), "fused_decode_attn")
+        int(max_ctx), int(rounding), int(bool(pdl) and _PDL_ATTN), _stream()), "fused_decode_attn")
     return out
 
 

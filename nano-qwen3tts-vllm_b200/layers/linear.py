@@ -13,7 +13,8 @@ from torch import nn
 from .. import _native as nat
 
 GEMM_NATIVE_MAX_M = nat.GEMM_MAX_M
-PDL = True                      # programmatic dependent launch of the native GEMM (weight stream starts early)
+import os
+PDL = os.environ.get("B2TTS_PDL_GEMM", "1") != "0"     # programmatic dependent launch of the native GEMM (weight stream starts early)
 _packed: dict = {}
 
 
