@@ -347,13 +347,18 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       }
       bar_sync_producers();
     }
+    // the norm weights of the NEXT k-block are requested before waiting for this one's x tile: the global-load
+    // latency (~0.7 us) would otherwise sit on the critical path of every k-block
+    uint4 wv_next = make_uint4(0, 0, 0, 0);
+    if (normed && nkb > 0) wv_next = ldg_v4(p.norm_w + (int64_t)kb_begin * G_BK + (tp & 7) * 8);
+    int stage = 0;
+    uint32_t ph = 0;
     for (int i = 0; i < nkb; ++i) {
-      const int stage = i % NS;
-      const uint32_t ph = (i / NS) & 1;
+      const uint4 wv = wv_next;
+      if (normed && i + 1 < nkb) wv_next = ldg_v4(p.norm_w + (int64_t)(kb_begin + i + 1) * G_BK + (tp & 7) * 8);
       mbar_wait(raw_bar + stage, ph);
       if (normed) {
         uint8_t* xs = smem + stage * stage_bytes + G_WTILE_BYTES;
-        const uint4 wv = ldg_v4(p.norm_w + (int64_t)(kb_begin + i) * G_BK + (tp & 7) * 8);
 #pragma unroll
         for (int j = 0; j < NCH; ++j) {
           const int idx = tp + 128 * j;
@@ -368,6 +373,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       __syncwarp();
       if (lane == 0) mbar_arrive(full_bar + stage);
       if (threadIdx.x == 64 && i == 0) G_TRACE(3);
+      if (++stage == NS) { stage = 0; ph ^= 1; }
     }
   }
 
