@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=24)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-streams", type=int, default=8)
+    ap.add_argument("--cpu-streams", type=int, default=0, help="streams of the CPU legs (0 = the same as --streams)")
     ap.add_argument("--also-streams", default="1,8", help="extra stream counts reported under other_workloads")
     return ap.parse_args()
 
@@ -123,12 +123,12 @@ def build_engines(model_size: str, streams: int, max_frames: int, device: str):
     return mc, talker, predictor
 
 
-def synthetic_prompts(streams: int, hidden: int, pinned: bool):
+def synthetic_prompts(streams: int, hidden: int, pinned: bool, prompt_len: int = PROMPT_LEN):
     import torch
     out = []
     for s in range(streams):
         g = torch.Generator().manual_seed(1000 + s)
-        p = (torch.randn(1, PROMPT_LEN, hidden, generator=g) * 0.05).to(torch.bfloat16)
+        p = (torch.randn(1, prompt_len, hidden, generator=g) * 0.05).to(torch.bfloat16)
         out.append(p.pin_memory() if pinned else p)
     pad = (torch.randn(1, hidden, generator=torch.Generator().manual_seed(999)) * 0.05).to(torch.bfloat16)
     return out, pad
@@ -330,7 +330,8 @@ def run_e2e(talker, predictor, mc, streams, steps):
 
 
 # ------------------------------------------------------------------------------------------ CPU arm
-def cpu_oracle_frames(model_size: str, streams: int, frames: int, warm_frames: int, budget_s: float):
+def cpu_oracle_frames(model_size: str, streams: int, frames: int, warm_frames: int, budget_s: float,
+                      prompt_len: int = PROMPT_LEN):
     """The CPU oracle (oracle/model.py: the reference's torch path restated op by op) timed on the
     host cores: `streams` streams with a PROMPT_LEN-token prompt, `frames` whole frames after
     `warm_frames`.  Returns (frames/s, cores, description, seconds)."""
@@ -382,10 +383,10 @@ def cpu_oracle_frames(model_size: str, streams: int, frames: int, warm_frames: i
     pw = fast_weights(pd, pextra)
     if td.hidden_size != pd.hidden_size:
         pw["small_to_mtp_projection.bias"] = torch.zeros(pd.hidden_size, dtype=torch.bfloat16)
-    pages = (PROMPT_LEN + frames + warm_frames + 2 + 255) // 256
+    pages = (prompt_len + frames + warm_frames + 2 + 255) // 256
     talker = OM.Talker(td, tw, streams * pages)
     predictor = OM.Predictor(pd, pw, streams, td.hidden_size)
-    prompts, pad = synthetic_prompts(streams, td.hidden_size, pinned=False)
+    prompts, pad = synthetic_prompts(streams, td.hidden_size, pinned=False, prompt_len=prompt_len)
     gen = torch.Generator().manual_seed(42)
     stamps = []
 
@@ -409,25 +410,27 @@ def cpu_oracle_frames(model_size: str, streams: int, frames: int, warm_frames: i
         dt = stamps[-1] - stamps[warm_frames]
     fps = streams * done / dt
     what = (f"oracle/model.py run_frames, {model_size} shapes, {streams} streams x {done} frames after {warm_frames} warm, "
-            f"prompt {PROMPT_LEN}, torch {torch.__version__} CPU bf16, {cores} threads")
+            f"prompt {prompt_len}, torch {torch.__version__} CPU bf16, {cores} threads")
     return fps, cores, what, dt
 
 
 def reference_arm(a):
-    """`--impl reference`: the reference's CPU path (oracle port) on the host cores, one step = one
-    frame of a bounded sample (`--cpu-streams` streams) of the workload."""
+    """`--impl reference`: the reference's CPU path (oracle port) on the host cores, one step = one frame of
+    the SAME workload as the GPU arm (the same stream count: `config` describes the work that ran), bounded in
+    time: the run stops after ~150 s of frames and reports the frames it completed."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     steps = max(1, a.steps)
-    fps, cores, what, dt = cpu_oracle_frames(a.model, a.cpu_streams, steps, max(1, min(a.warmup, 2)), budget_s=150.0)
+    streams = a.cpu_streams or a.streams
+    fps, cores, what, dt = cpu_oracle_frames(a.model, streams, steps, max(1, min(a.warmup, 2)), budget_s=150.0)
     line = {"impl": "reference", "metric": "codec frames/s", "value": round(fps, 3), "unit": "frames/s",
-            "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(1000 * a.cpu_streams / fps, 3),
+            "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(1000 * streams / fps, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": workload_config(a, a.streams),
+            "config": workload_config(a, streams),
             "cpu_baseline": {"value": round(fps, 3), "unit": "frames/s", "cores": cores, "kind": "port", "sample": what},
             "e2e": {"value": round(fps, 3), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "rtf_per_stream": round(FRAME_HZ * a.cpu_streams / fps, 4)}
+            "rtf_per_stream": round(FRAME_HZ * streams / fps, 4)}
     print(json.dumps(line), flush=True)
 
 
@@ -536,8 +539,12 @@ def main():
                               "rtf_per_stream": round(ms_b / a.steps / 1e3 * FRAME_HZ, 5)}
         line["other_workloads"] = others
     if rank == 0 and not a.no_cpu_baseline and world == 1:
-        fps, cores, what, dt = cpu_oracle_frames(a.model, a.cpu_streams, 3, 1, budget_s=25.0)
+        fps, cores, what, dt = cpu_oracle_frames(a.model, a.cpu_streams or a.streams, 2, 1, budget_s=25.0)
         line["cpu_baseline"] = {"value": round(fps, 3), "unit": "frames/s", "cores": cores, "kind": "port", "sample": what}
+        # BASELINE configs[0]: 0.6B, 1 stream, ~20-word (40-token) prompt - the reference's own CPU-runnable case
+        fps0, cores0, what0, _ = cpu_oracle_frames("0.6B", 1, 8, 2, budget_s=20.0, prompt_len=40)
+        line["cpu_baseline_configs0"] = {"value": round(fps0, 3), "unit": "frames/s", "cores": cores0, "kind": "port",
+                                         "rtf": round(FRAME_HZ / fps0, 4), "sample": what0}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist:

@@ -167,14 +167,15 @@ B2TTS_API int b2tts_topk_sample(const void* logits, int64_t logits_row_stride, i
  *   replaces the per-sequence loop codec_embedding[g_i-1](id_i)   models/qwen3_tts_predictor.py:94-98
  *   tables = base pointer of a stacked [num_tables, rows_per_table, cols] tensor;
  *   table_index NULL = table 0; an index < 0 writes a zero row.
- * b2tts_codec_embed_sum: out[i] = bf16(sum_{c<ncb} f32(E_c[codes[i,c]])) + extra[i]
- *   replaces the 16-codebook gather-sum + trailing-text add        interface.py:1276-1286 */
+ * b2tts_codec_embed_sum: out[i] = bf16(sum_{c<ncb} f32(E_c[codes[i,c]])) + extra[extra_index ? extra_index[i] : i]
+ *   replaces the 16-codebook gather-sum + trailing-text add        interface.py:1276-1286
+ *   (extra_index selects trailing_text_hiddens[:, generation_step] or the tts_pad_embed row per stream) */
 B2TTS_API int b2tts_gather_rows(const void* tables, int64_t table_stride, int rows_per_table,
                       const int64_t* row_index, const int32_t* table_index,
                       void* out, int64_t out_row_stride, int n, int cols, void* stream);
 B2TTS_API int b2tts_codec_embed_sum(const void* table0, const void* tables_rest, int64_t table_stride,
                           const int64_t* codes, int64_t codes_row_stride,
-                          const void* extra, int64_t extra_row_stride,
+                          const void* extra, int64_t extra_row_stride, const int64_t* extra_index,
                           void* out, int n, int num_codebooks, int cols, void* stream);
 
 /* ---- a12 on the device: decode batch layout -------------------------------------------------------
@@ -182,11 +183,23 @@ B2TTS_API int b2tts_codec_embed_sum(const void* table0, const void* tables_rest,
  *                          engine/model_runner/base.py:218-234, talker_mode_runner.py:116-140
  * seq_lens [n] int32 (device) = tokens of each stream INCLUDING the one decoded this step, 0 =
  * inactive row.  Writes context_lens = len, slot = block_table[i][(len-1)/page]*page + (len-1)%page,
- * positions = len-1+position_offset (1 = talker quirk, 0 = predictor); inactive rows get slot -1,
- * context 0.  advance != 0 then adds `advance` to the active seq_lens (next step's length). */
-B2TTS_API int b2tts_decode_layout(int32_t* seq_lens, const int32_t* block_table, int bt_stride, int page_size,
-                        int position_offset, int advance, int64_t* positions, int32_t* slot_mapping,
-                        int32_t* context_lens, int n, void* stream);
+ * positions = len-1+position_offset (1 = talker quirk, 0 = predictor); inactive rows - and rows whose
+ * token would fall beyond the bt_width pages of their table row - get slot -1, context 0.
+ * advance != 0 then adds `advance` to the active seq_lens (next step's length). */
+B2TTS_API int b2tts_decode_layout(int32_t* seq_lens, const int32_t* block_table, int bt_stride, int bt_width,
+                        int page_size, int position_offset, int advance, int64_t* positions,
+                        int32_t* slot_mapping, int32_t* context_lens, int n, void* stream);
+
+/* ---- f1: per-frame stream state of the on-device frame loop ---------------------------------------
+ * replaces the host bookkeeping of generate_async                      interface.py:1233-1239, 1282-1285
+ * code0 [n] int64 = the talker code sampled for this frame.  A stream whose code0 == eos_id (2150; eos_id < 0
+ * ignores EOS) or that has produced max_frames frames goes inactive BEFORE the frame is produced: active[i] = 0,
+ * seq_lens[i] = 0 (a padding row for b2tts_decode_layout from now on).  extra_row[i] = i*(trail_rows+1) +
+ * min(gen_step[i], trail_rows) indexes a [n, trail_rows+1, H] buffer whose row trail_rows holds tts_pad_embed
+ * (b2tts_codec_embed_sum's extra_index).  Active streams then count the frame: gen_step += 1, frames_done += 1. */
+B2TTS_API int b2tts_frame_advance(const int64_t* code0, int eos_id, int32_t* active, int32_t* seq_lens,
+                        int32_t* gen_step, int32_t* frames_done, int64_t* extra_row, int trail_rows,
+                        int max_frames, int n, void* stream);
 
 /* ---- a7: the projections (weight-streaming tcgen05 GEMM) -------------------------------------------
  * replaces F.linear in ColumnParallelLinear / RowParallelLinear.forward   layers/linear.py:72-73, 149-153
@@ -278,7 +291,9 @@ B2TTS_API int    b2tts_gemm_chain(const b2tts_gemm_op* ops, int nops, int m, flo
  * (arguments as b2tts_paged_attn_decode) and folds the split-KV partials itself (the last CTA of a
  * sequence to finish does it, in split order).  K cache bytes and attention outputs equal those of the
  * separate calls.  workspace: b2tts_fused_decode_attn_workspace_bytes(...) bytes, ZERO-FILLED once by the
- * caller before the first launch (the kernel leaves its tickets zero).  pdl as b2tts_gemm_bf16. */
+ * caller before the first launch (the kernel leaves its tickets zero).  The tickets occupy a fixed span at the
+ * start of the workspace, so ONE workspace sized for the largest batch serves launches of every smaller batch
+ * (batch <= 4096).  pdl as b2tts_gemm_bf16. */
 B2TTS_API size_t b2tts_fused_decode_attn_workspace_bytes(int batch, int num_heads, int head_dim, int max_ctx);
 B2TTS_API int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, const void* k, int64_t k_row_stride,
                             const void* v, int64_t v_row_stride,

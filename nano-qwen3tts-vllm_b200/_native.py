@@ -55,8 +55,9 @@ def _load():
         "b2tts_silu_and_mul": (I, [P, P, L, P, I, I, I, P]),
         "b2tts_topk_sample": (I, [P, L, I, P, P, P, P, I, I, I, F, I, P]),
         "b2tts_gather_rows": (I, [P, L, I, P, P, P, L, I, I, P]),
-        "b2tts_codec_embed_sum": (I, [P, P, L, P, L, P, L, P, I, I, I, P]),
-        "b2tts_decode_layout": (I, [P, P, I, I, I, I, P, P, P, I, P]),
+        "b2tts_codec_embed_sum": (I, [P, P, L, P, L, P, L, P, P, I, I, I, P]),
+        "b2tts_decode_layout": (I, [P, P, I, I, I, I, I, P, P, P, I, P]),
+        "b2tts_frame_advance": (I, [P, I, P, P, P, P, P, I, I, I, P]),
         "b2tts_gemm_bf16_supported": (I, [I, I, I]),
         "b2tts_gemm_packed_bytes": (Z, [I, I]),
         "b2tts_gemm_pack_weight": (I, [P, L, P, I, I, I, P]),
@@ -329,8 +330,9 @@ def gather_rows(tables, row_index, table_index=None, out=None):
     return out
 
 
-def codec_embed_sum(table0, tables_rest, codes, extra=None, out=None):
-    """table0 [V0, cols]; tables_rest [ncb-1, V, cols]; codes [n, ncb] int64; extra [n, cols] or [1, cols]."""
+def codec_embed_sum(table0, tables_rest, codes, extra=None, out=None, extra_index=None):
+    """table0 [V0, cols]; tables_rest [ncb-1, V, cols]; codes [n, ncb] int64; extra [n, cols] or [1, cols], or any
+    [rows, cols] with ``extra_index`` [n] int64 picking the row of each stream."""
     _cuda(table0, BF16, "table0"); _cuda(codes, I64, "codes")
     n, ncb = codes.shape
     cols = table0.shape[-1]
@@ -339,10 +341,15 @@ def codec_embed_sum(table0, tables_rest, codes, extra=None, out=None):
     es = 0
     if extra is not None:
         _cuda(extra, BF16, "extra")
-        es = extra.stride(0) if extra.shape[0] == n else 0      # one row broadcasts
+        if extra_index is not None:
+            _cuda(extra_index, I64, "extra_index")
+            es = extra.stride(0)
+        else:
+            es = extra.stride(0) if extra.shape[0] == n else 0      # one row broadcasts
     _check(_load().b2tts_codec_embed_sum(table0.data_ptr(), _ptr(tables_rest),
                                          0 if tables_rest is None else tables_rest.stride(0),
-                                         codes.data_ptr(), codes.stride(0), _ptr(extra), es, out.data_ptr(),
+                                         codes.data_ptr(), codes.stride(0), _ptr(extra), es,
+                                         _ptr(extra_index) if extra is not None else None, out.data_ptr(),
                                          n, ncb, cols, _stream()), "codec_embed_sum")
     return out
 
@@ -353,18 +360,25 @@ def decode_layout(seq_lens, block_table, page_size, position_offset, advance, po
     _cuda(slot_mapping, I32, "slot_mapping"); _cuda(context_lens, I32, "context_lens")
     n = seq_lens.numel()
     _check(_load().b2tts_decode_layout(seq_lens.data_ptr(), block_table.data_ptr(), block_table.stride(0),
-                                       int(page_size), int(position_offset), int(advance), positions.data_ptr(),
-                                       slot_mapping.data_ptr(), context_lens.data_ptr(), n, _stream()), "decode_layout")
+                                       block_table.shape[1], int(page_size), int(position_offset), int(advance),
+                                       positions.data_ptr(), slot_mapping.data_ptr(), context_lens.data_ptr(), n,
+                                       _stream()), "decode_layout")
+
+
+def frame_advance(code0, eos_id, active, seq_lens, gen_step, frames_done, extra_row, trail_rows, max_frames):
+    """Per-frame stream bookkeeping on the device (``b2tts_frame_advance``): EOS / frame-budget retirement,
+    trailing-text row selection, frame counters.  ``eos_id`` < 0 ignores EOS."""
+    _cuda(code0, I64, "code0"); _cuda(active, I32, "active"); _cuda(seq_lens, I32, "seq_lens")
+    _cuda(gen_step, I32, "gen_step"); _cuda(frames_done, I32, "frames_done"); _cuda(extra_row, I64, "extra_row")
+    _check(_load().b2tts_frame_advance(code0.data_ptr(), int(eos_id), active.data_ptr(), seq_lens.data_ptr(),
+                                       gen_step.data_ptr(), frames_done.data_ptr(), extra_row.data_ptr(),
+                                       int(trail_rows), int(max_frames), code0.numel(), _stream()), "frame_advance")
 
 
 # ------------------------------------------------------------------------------------------ a7
 GEMM_BIAS, GEMM_RESIDUAL, GEMM_SILU_MUL = 0, 1, 2
 PACK_PLAIN, PACK_GATE_UP = 0, 1
 GEMM_MAX_M = 128
-
-
-def has_gemm() -> bool:
-    return True
 
 
 def launch_count() -> int:

@@ -40,7 +40,7 @@ int sm_count() {
 
 extern "C" {
 
-int b2tts_version(void) { return 1; }
+int b2tts_version(void) { return 2; }
 
 const char* b2tts_last_error(void) { return b2::g_err; }
 

@@ -25,6 +25,11 @@ namespace b2 {
 constexpr int FA_HD = 128;
 constexpr int FA_TILE = 8;
 constexpr int FA_NSTAGE = 3;
+// The per-row split-KV tickets live in a FIXED span at the start of the workspace, whatever the batch size of the
+// launch: one workspace serves every batch size / graph of a runner, and the partial accumulators of one launch
+// must never land on the (always-zero-between-launches) tickets another launch will read.
+constexpr int FA_MAX_ROWS = 4096;
+constexpr size_t FA_TICKET_BYTES = (size_t)FA_MAX_ROWS * sizeof(int);
 
 struct FusedAttnParams {
   const __nv_bfloat16 *q, *k, *v;          // rows of the QKV projection
@@ -429,8 +434,8 @@ static int fa_choose_nsplit(int rows, int max_ctx) {
 extern "C" size_t b2tts_fused_decode_attn_workspace_bytes(int batch, int num_heads, int head_dim, int max_ctx) {
   if (batch <= 0 || num_heads <= 0 || head_dim <= 0 || max_ctx <= 0) return 0;
   const int nsplit = b2::fa_choose_nsplit(batch, max_ctx);
-  // partials + (m, l) + one ticket per row (the tickets must be zero before the first launch)
-  return (size_t)batch * nsplit * num_heads * (head_dim + 2) * sizeof(float) + (size_t)batch * sizeof(int) + 16;
+  // fixed ticket span (zero before the first launch, left zero by every launch) + partials + (m, l)
+  return b2::FA_TICKET_BYTES + (size_t)batch * nsplit * num_heads * (head_dim + 2) * sizeof(float) + 16;
 }
 
 extern "C" int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, const void* k, int64_t k_row_stride,
@@ -448,6 +453,7 @@ extern "C" int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, cons
   B2_REQUIRE(batch >= 0 && max_ctx > 0 && page_size > 0 && bt_stride > 0, B2TTS_EINVAL,
              "%s: batch=%d max_ctx=%d page_size=%d bt_stride=%d", what, batch, max_ctx, page_size, bt_stride);
   if (batch == 0) return B2TTS_OK;
+  B2_REQUIRE(batch <= FA_MAX_ROWS, B2TTS_EUNSUPPORTED, "%s: batch %d > %d rows", what, batch, FA_MAX_ROWS);
   B2_REQUIRE(q && k && v && positions && inv_freq && slot_mapping && k_cache && v_cache && block_table && context_lens &&
                  out && workspace, B2TTS_EINVAL, "%s: null pointer", what);
   B2_REQUIRE(head_dim == FA_HD, B2TTS_EUNSUPPORTED, "%s: head_dim %d unsupported (128)", what, head_dim);
@@ -488,9 +494,9 @@ extern "C" int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, cons
   const size_t acc_elems = (size_t)batch * p.nsplit * num_heads * head_dim;
   const size_t need = b2tts_fused_decode_attn_workspace_bytes(batch, num_heads, head_dim, max_ctx);
   B2_REQUIRE(workspace_bytes >= need, B2TTS_EWORKSPACE, "%s: workspace %zu B < %zu B needed", what, workspace_bytes, need);
-  p.part_acc = static_cast<float*>(workspace);
+  p.tickets = static_cast<int*>(workspace);
+  p.part_acc = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + FA_TICKET_BYTES);
   p.part_ml = p.part_acc + acc_elems;
-  p.tickets = reinterpret_cast<int*>(p.part_ml + (size_t)batch * p.nsplit * num_heads * 2);
 
   const int group = num_heads / num_kv_heads;
   const bool eager = rounding == B2TTS_ROUND_EAGER;

@@ -57,8 +57,10 @@ __global__ void __launch_bounds__(256)
 codec_embed_sum_kernel(const __nv_bfloat16* __restrict__ table0, const __nv_bfloat16* __restrict__ tables_rest,
                        int64_t table_stride, const int64_t* __restrict__ codes, int64_t codes_stride,
                        const __nv_bfloat16* __restrict__ extra, int64_t extra_stride,
+                       const int64_t* __restrict__ extra_index,
                        __nv_bfloat16* __restrict__ out, int ncb, int cols) {
   const int i = blockIdx.x;
+  const int64_t erow = extra_index ? __ldg(extra_index + i) : (int64_t)i;
   for (int v = threadIdx.x; v < (cols >> 3); v += blockDim.x) {
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int c = 0; c < ncb; ++c) {
@@ -69,7 +71,7 @@ codec_embed_sum_kernel(const __nv_bfloat16* __restrict__ table0, const __nv_bflo
       acc[4] += bf16lo(r.z); acc[5] += bf16hi(r.z); acc[6] += bf16lo(r.w); acc[7] += bf16hi(r.w);
     }
     if (extra) {
-      const uint4 e = ldg_v4(extra + (int64_t)i * extra_stride + 8 * v);
+      const uint4 e = ldg_v4(extra + erow * extra_stride + 8 * v);
       acc[0] = rbf(acc[0]) + bf16lo(e.x); acc[1] = rbf(acc[1]) + bf16hi(e.x);
       acc[2] = rbf(acc[2]) + bf16lo(e.y); acc[3] = rbf(acc[3]) + bf16hi(e.y);
       acc[4] = rbf(acc[4]) + bf16lo(e.z); acc[5] = rbf(acc[5]) + bf16hi(e.z);
@@ -126,7 +128,7 @@ extern "C" int b2tts_gather_rows(const void* tables, int64_t table_stride, int r
 
 extern "C" int b2tts_codec_embed_sum(const void* table0, const void* tables_rest, int64_t table_stride,
                                      const int64_t* codes, int64_t codes_row_stride,
-                                     const void* extra, int64_t extra_row_stride,
+                                     const void* extra, int64_t extra_row_stride, const int64_t* extra_index,
                                      void* out, int n, int num_codebooks, int cols, void* stream) {
   using namespace b2;
   B2_REQUIRE(n >= 0 && cols > 0 && num_codebooks >= 1, B2TTS_EINVAL, "codec_embed_sum: n=%d cols=%d ncb=%d", n, cols, num_codebooks);
@@ -137,8 +139,8 @@ extern "C" int b2tts_codec_embed_sum(const void* table0, const void* tables_rest
              B2TTS_EALIGN, "codec_embed_sum: cols/strides must be multiples of 8 and pointers 16-byte aligned");
   codec_embed_sum_kernel<<<n, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(table0), static_cast<const __nv_bfloat16*>(tables_rest), table_stride, codes,
-      codes_row_stride, static_cast<const __nv_bfloat16*>(extra), extra_row_stride, static_cast<__nv_bfloat16*>(out),
-      num_codebooks, cols);
+      codes_row_stride, static_cast<const __nv_bfloat16*>(extra), extra_row_stride, extra ? extra_index : nullptr,
+      static_cast<__nv_bfloat16*>(out), num_codebooks, cols);
   B2_CHECK_LAUNCH("codec_embed_sum");
   return B2TTS_OK;
 }
@@ -152,7 +154,7 @@ extern "C" int b2tts_codec_embed_sum(const void* table0, const void* tables_rest
 // then, if advance != 0, seq_lens[i] += advance for active rows (the next step's length).
 namespace b2 {
 __global__ void decode_layout_kernel(int32_t* __restrict__ seq_lens, const int32_t* __restrict__ block_table,
-                                     int bt_stride, int page, int position_offset, int advance,
+                                     int bt_stride, int bt_width, int page, int position_offset, int advance,
                                      int64_t* __restrict__ positions, int32_t* __restrict__ slot_mapping,
                                      int32_t* __restrict__ context_lens, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -163,6 +165,10 @@ __global__ void decode_layout_kernel(int32_t* __restrict__ seq_lens, const int32
     return;
   }
   const int t = len - 1;
+  if (t / page >= bt_width) {            // beyond the table: never index another stream's row (the row goes idle)
+    positions[i] = 0; slot_mapping[i] = -1; context_lens[i] = 0;
+    return;
+  }
   const int pg = block_table[(int64_t)i * bt_stride + t / page];
   positions[i] = (int64_t)t + position_offset;
   slot_mapping[i] = pg < 0 ? -1 : pg * page + t % page;
@@ -171,15 +177,61 @@ __global__ void decode_layout_kernel(int32_t* __restrict__ seq_lens, const int32
 }
 }  // namespace b2
 
-extern "C" int b2tts_decode_layout(int32_t* seq_lens, const int32_t* block_table, int bt_stride, int page_size,
-                                   int position_offset, int advance, int64_t* positions, int32_t* slot_mapping,
-                                   int32_t* context_lens, int n, void* stream) {
+extern "C" int b2tts_decode_layout(int32_t* seq_lens, const int32_t* block_table, int bt_stride, int bt_width,
+                                   int page_size, int position_offset, int advance, int64_t* positions,
+                                   int32_t* slot_mapping, int32_t* context_lens, int n, void* stream) {
   using namespace b2;
-  B2_REQUIRE(n >= 0 && page_size > 0 && bt_stride > 0, B2TTS_EINVAL, "decode_layout: n=%d page=%d bt_stride=%d", n, page_size, bt_stride);
+  B2_REQUIRE(n >= 0 && page_size > 0 && bt_stride > 0 && bt_width > 0 && bt_width <= bt_stride, B2TTS_EINVAL,
+             "decode_layout: n=%d page=%d bt_stride=%d bt_width=%d", n, page_size, bt_stride, bt_width);
   if (n == 0) return B2TTS_OK;
   B2_REQUIRE(seq_lens && block_table && positions && slot_mapping && context_lens, B2TTS_EINVAL, "decode_layout: null pointer");
   decode_layout_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      seq_lens, block_table, bt_stride, page_size, position_offset, advance, positions, slot_mapping, context_lens, n);
+      seq_lens, block_table, bt_stride, bt_width, page_size, position_offset, advance, positions, slot_mapping,
+      context_lens, n);
   B2_CHECK_LAUNCH("decode_layout");
+  return B2TTS_OK;
+}
+
+// ---- f1: per-frame stream bookkeeping of the frame loop (interface.py:1233-1239, 1282-1285) on the device.
+// For stream i, with code0[i] the talker code sampled for this frame:
+//   * code0 == eos_id (2150) ends the stream BEFORE the frame is produced (`send_clear_request; break`): active = 0,
+//     seq_lens = 0, so the row becomes CUDA-graph padding for the rest of the run; so does a stream that has
+//     produced max_frames frames;
+//   * extra_row[i] = i * (trail_rows + 1) + min(gen_step, trail_rows): the row of a [n, trail_rows + 1, H] buffer
+//     holding trailing_text_hiddens[:, generation_step] for generation_step < trail_rows and tts_pad_embed after;
+//   * active streams count the frame: gen_step += 1, frames_done += 1.
+namespace b2 {
+__global__ void frame_advance_kernel(const int64_t* __restrict__ code0, int eos_id, int32_t* __restrict__ active,
+                                     int32_t* __restrict__ seq_lens, int32_t* __restrict__ gen_step,
+                                     int32_t* __restrict__ frames_done, int64_t* __restrict__ extra_row,
+                                     int trail_rows, int max_frames, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int a = active[i];
+  if (a && ((eos_id >= 0 && code0[i] == (int64_t)eos_id) || frames_done[i] >= max_frames)) {
+    a = 0;
+    active[i] = 0;
+    seq_lens[i] = 0;
+  }
+  const int g = gen_step[i];
+  extra_row[i] = (int64_t)i * (trail_rows + 1) + (g < trail_rows ? g : trail_rows);
+  if (a) {
+    gen_step[i] = g + 1;
+    frames_done[i] += 1;
+  }
+}
+}  // namespace b2
+
+extern "C" int b2tts_frame_advance(const int64_t* code0, int eos_id, int32_t* active, int32_t* seq_lens,
+                                   int32_t* gen_step, int32_t* frames_done, int64_t* extra_row, int trail_rows,
+                                   int max_frames, int n, void* stream) {
+  using namespace b2;
+  B2_REQUIRE(n >= 0 && trail_rows >= 0 && max_frames >= 0, B2TTS_EINVAL, "frame_advance: n=%d trail_rows=%d max_frames=%d",
+             n, trail_rows, max_frames);
+  if (n == 0) return B2TTS_OK;
+  B2_REQUIRE(code0 && active && seq_lens && gen_step && frames_done && extra_row, B2TTS_EINVAL, "frame_advance: null pointer");
+  frame_advance_kernel<<<(n + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      code0, eos_id, active, seq_lens, gen_step, frames_done, extra_row, trail_rows, max_frames, n);
+  B2_CHECK_LAUNCH("frame_advance");
   return B2TTS_OK;
 }

@@ -26,9 +26,21 @@ BF16 = torch.bfloat16
 
 
 class DeviceFrameLoop:
+    """One codec frame per ``step()`` for ``num_streams`` streams in lock-step, all state on the device.
+
+    Protocol of the reference's ``generate_async`` (interface.py:1207-1290), per stream: the talker's code0 ==
+    codec EOS (2150) ends the stream before the frame is produced (``ignore_eos`` keeps it running, the benchmark /
+    parity setting of SURVEY.md section 8d); the next talker input is the 16-codebook embedding sum plus
+    ``trailing_text_hiddens[:, generation_step]`` while the trailing text lasts and ``tts_pad_embed`` after.
+    Finished streams stay in the batch as padding rows (slot -1, context 0) until every stream is done.
+
+    Test hooks: ``force(frames)`` teacher-forces the codes fed forward (the sampled ones are kept in ``sampled``),
+    ``keep_logits`` copies every decision's logits into ``logit_log`` each frame."""
+
     def __init__(self, talker_runner, predictor_runner, num_streams: int, max_frames: int, max_prompt_len: int,
                  top_k: int = 50, talker_temperature: float = 1.0, predictor_temperature: float = 0.9,
-                 scatter_pages: bool = True, seed: int = 13):
+                 scatter_pages: bool = True, seed: int = 13, ignore_eos: bool = True, codec_eos: int = 2150,
+                 max_trailing: int = 0):
         self.tr, self.pr = talker_runner, predictor_runner
         self.talker, self.predictor = talker_runner.model, predictor_runner.model
         self.dev = talker_runner.device
@@ -36,6 +48,7 @@ class DeviceFrameLoop:
         self.page = talker_runner.block_size
         self.top_k = top_k
         self.max_frames = max_frames
+        self.eos_id = -1 if ignore_eos else int(codec_eos)
         tc, pc = talker_runner.stack_config, predictor_runner.stack_config
         self.ncb = pc.num_code_groups                                        # 16 codes per frame
         self.width = (max_prompt_len + max_frames + 1 + self.page - 1) // self.page
@@ -49,20 +62,30 @@ class DeviceFrameLoop:
             perm = torch.arange(need_t, dtype=torch.int32)
         self.t_tables = perm.view(b, self.width).contiguous().to(dev)
         self.t_tables_host = perm.view(b, self.width)
-        self.seq_lens = torch.zeros(b, dtype=torch.int32, device=dev)       # length INCLUDING the next decode token
+        i32 = dict(dtype=torch.int32, device=dev)
+        self.seq_lens = torch.zeros(b, **i32)                                # length INCLUDING the next decode token
+        self.active = torch.zeros(b, **i32)
+        self.gen_step = torch.zeros(b, **i32)                                # interface.py: generation_step
+        self.frames_done = torch.zeros(b, **i32)
+        self.extra_row = torch.zeros(b, dtype=torch.int64, device=dev)
         self.t_pos = torch.zeros(b, dtype=torch.int64, device=dev)
-        self.t_slots = torch.full((b,), -1, dtype=torch.int32, device=dev)
-        self.t_ctx = torch.zeros(b, dtype=torch.int32, device=dev)
+        self.t_slots = torch.full((b,), -1, **i32)
+        self.t_ctx = torch.zeros(b, **i32)
         self.t_temp = torch.full((b,), talker_temperature, dtype=torch.float32, device=dev)
         self.p_temp = torch.full((b,), predictor_temperature, dtype=torch.float32, device=dev)
         self.embeds = torch.zeros(b, tc.hidden_size, dtype=BF16, device=dev)        # next talker input
         self.hidden = torch.zeros(b, tc.hidden_size, dtype=BF16, device=dev)        # last talker hidden
         self.codes_t = torch.zeros(self.ncb, b, dtype=torch.int64, device=dev)      # codebook-major: row g contiguous
         self.codes = torch.zeros(b, self.ncb, dtype=torch.int64, device=dev)        # [code0 | 15 predictor codes]
-        self.extra = torch.zeros(1, tc.hidden_size, dtype=BF16, device=dev)         # tts_pad_embed / trailing text
+        # trailing_text_hiddens[:, step] for step < trail_rows, tts_pad_embed in row trail_rows     interface.py:1282-1285
+        self.trail_rows = int(max_trailing)
+        self.trail = torch.zeros(b, self.trail_rows + 1, tc.hidden_size, dtype=BF16, device=dev)
         self.frames = torch.zeros(max_frames, b, self.ncb, dtype=torch.int64, device=dev)
         self.frame_idx = torch.zeros(1, dtype=torch.int64, device=dev)
         self.one = torch.ones(1, dtype=torch.int64, device=dev)
+        # Exp(1) draws of the frame's 16 samplers (torch.multinomial's noise): ONE generator launch per frame
+        self.vt, self.vp = tc.vocab_size, pc.vocab_size
+        self.noise = torch.ones(b * (self.vt + (self.ncb - 1) * self.vp), dtype=torch.float32, device=dev)
         # predictor static layouts: stream i owns page i; prefill rows (2i, 2i+1) -> slots page*P + {0,1}
         pg = torch.arange(b, dtype=torch.int32, device=dev)
         self.p_tables = pg.view(b, 1).contiguous()
@@ -79,23 +102,69 @@ class DeviceFrameLoop:
         self.graph = None
         self.launches_per_frame = None
         self.unit_noise = False
+        self.frames_run = 0
+        self.forced = None                 # [max_frames + 1, 16, B] codes fed forward instead of the sampled ones
+        self.sampled = None                # [max_frames + 1, 16, B] what the sampler chose at each forced decision
+        self.keep_logits = False
+        self.logit_log: dict[int, torch.Tensor] = {}
+
+    # ------------------------------------------------------------------ test hooks
+    def force(self, frames: torch.Tensor):
+        """Teacher forcing: ``frames`` [F, B, 16] are fed forward (code0 of frame f at the end of frame f - 1, the
+        predictor codes inside frame f) whatever the samplers choose; the choices land in ``self.sampled``."""
+        f = frames.shape[0]
+        assert frames.shape[1:] == (self.b, self.ncb) and f <= self.max_frames
+        self.forced = torch.zeros(self.max_frames + 1, self.ncb, self.b, dtype=torch.int64, device=self.dev)
+        self.forced[:f] = frames.to(self.dev, torch.int64).permute(0, 2, 1)
+        self.sampled = torch.full_like(self.forced, -1)
+
+    def _noise_view(self, g: int) -> torch.Tensor:
+        b = self.b
+        if g == 0:
+            return self.noise[:b * self.vt].view(b, self.vt)
+        o = b * self.vt + (g - 1) * b * self.vp
+        return self.noise[o:o + b * self.vp].view(b, self.vp)
 
     # ------------------------------------------------------------------ sampling
-    def _sample(self, logits, temps, out):
-        if self.unit_noise:          # tests: argmax(p / 1) = first maximum, so exact bf16 ties do not depend on the RNG
-            noise = torch.ones(logits.shape, dtype=torch.float32, device=self.dev)
-        else:
-            noise = torch.empty(logits.shape, dtype=torch.float32, device=self.dev).exponential_(1)
-        nat.topk_sample(logits, temps, noise, top_k=self.top_k, out=out)
+    def _sample(self, logits, temps, g: int):
+        """Decision ``g`` of the current frame (0 = the talker's code0 of the NEXT frame): sampler.py:15-24 on the
+        frame's pre-drawn Exp(1) noise; argmax(p / 1) = first maximum under ``unit_noise`` (tests)."""
+        out = self.codes_t[g]
+        nat.topk_sample(logits, temps, self._noise_view(g), top_k=self.top_k, out=out)
+        if self.keep_logits:
+            buf = self.logit_log.get(g)
+            if buf is None or buf.shape != logits.shape:
+                buf = self.logit_log[g] = torch.empty_like(logits)
+            buf.copy_(logits)
+        if self.forced is not None:
+            row = self.frame_idx * self.ncb + g                           # device index: graph-capturable
+            self.sampled.view(-1, self.b).index_copy_(0, row, out.unsqueeze(0))
+            out.copy_(self.forced.view(-1, self.b).index_select(0, row)[0])
+
+    def _draw_noise(self):
+        if not self.unit_noise:
+            self.noise.exponential_(1)
 
     # ------------------------------------------------------------------ prompt
     @torch.inference_mode()
-    def start(self, prompts: list[torch.Tensor], extra: torch.Tensor | None = None):
-        """Prefill every stream (packed varlen, one pass), sample the first code of each."""
+    def start(self, prompts: list[torch.Tensor], extra: torch.Tensor | None = None,
+              trailing: list[torch.Tensor | None] | None = None):
+        """Prefill every stream (packed varlen, one pass), sample the first code of each.  ``extra`` =
+        tts_pad_embed [1, H] (or one row per stream); ``trailing[i]`` = trailing_text_hiddens of stream i [T_i, H]."""
         assert len(prompts) == self.b
         lens = [int(p.shape[-2]) for p in prompts]
+        if max(lens) + self.max_frames + 1 > self.width * self.page:
+            raise RuntimeError(f"prompt of {max(lens)} tokens + {self.max_frames} frames exceeds the {self.width}-page tables")
+        self.trail.zero_()
         if extra is not None:
-            self.extra.copy_(extra.reshape(1, -1))
+            self.trail.copy_(extra.to(self.dev, BF16).reshape(-1, 1, self.trail.shape[-1]).expand_as(self.trail))
+        if trailing is not None:
+            for i, t in enumerate(trailing):
+                if t is not None and t.numel():
+                    n = t.shape[-2]
+                    if n > self.trail_rows:
+                        raise RuntimeError(f"trailing text of {n} rows > max_trailing={self.trail_rows}")
+                    self.trail[i, :n].copy_(t.reshape(n, -1))
         pos, slots, cu = [], [], [0]
         for i, n in enumerate(lens):
             pos += list(range(n))
@@ -109,10 +178,15 @@ class DeviceFrameLoop:
         last = (cu_t[1:] - 1).to(torch.int64)
         self.hidden.copy_(nat.gather_rows(h, last))
         logits = linear(self.hidden, self.talker.codec_head.weight)
-        self._sample(logits, self.t_temp, self.codes_t[0])
+        self.frame_idx.zero_()
+        self._draw_noise() if not self.unit_noise else self.noise.fill_(1.0)
+        self._sample(logits, self.t_temp, 0)
         reset_context()
         self.seq_lens.copy_(torch.tensor([n + 1 for n in lens], dtype=torch.int32))
-        self.frame_idx.zero_()
+        self.active.fill_(1)
+        self.gen_step.zero_()
+        self.frames_done.zero_()
+        self.frames_run = 0
         self.first_logits = logits
 
     # ------------------------------------------------------------------ one frame
@@ -120,6 +194,10 @@ class DeviceFrameLoop:
         b, tr, pr = self.b, self.tr, self.pr
         talker, predictor = self.talker, self.predictor
         code0 = self.codes_t[0]
+        # ---- stream state: EOS / frame budget retire a stream before its frame         interface.py:1233-1239
+        nat.frame_advance(code0, self.eos_id, self.active, self.seq_lens, self.gen_step, self.frames_done,
+                          self.extra_row, self.trail_rows, self.max_frames)
+        self._draw_noise()
         # ---- predictor prefill on [hidden_i, embed(code0_i)]                   interface.py:1242-1252
         x3 = self.p_x.view(b, 2, -1)
         x3[:, 0].copy_(self.hidden)
@@ -127,7 +205,7 @@ class DeviceFrameLoop:
         set_context(True, self.p_cu, self.p_cu, 2, 2, self.p_pre_slots, None, None)
         h = predictor(self.p_x, self.p_pre_pos)
         last = h.view(b, 2, -1)[:, 1]
-        self._sample(linear(last, predictor.lm_head[0]), self.p_temp, self.codes_t[1])
+        self._sample(linear(last, predictor.lm_head[0]), self.p_temp, 1)
         # ---- 14 predictor decode passes                                 predictor_model_runner.py:134-157
         for g in range(1, self.ncb - 1):
             lay = self.p_dec[g - 1]
@@ -135,42 +213,55 @@ class DeviceFrameLoop:
             set_context(False, slot_mapping=lay["slots"], context_lens=lay["ctx"], block_tables=self.p_tables,
                         max_context_len=g + 2)           # exact: no split-KV, no combine launch
             h = predictor(emb, lay["pos"])
-            self._sample(linear(h, predictor.lm_head[g]), self.p_temp, self.codes_t[g + 1])
+            self._sample(linear(h, predictor.lm_head[g]), self.p_temp, g + 1)
         # ---- emit the frame, build the next talker input                       interface.py:1269-1286
         self.codes.copy_(self.codes_t.t())
         self.frames.index_copy_(0, self.frame_idx, self.codes.unsqueeze(0))
         self.frame_idx.add_(self.one)
         nat.codec_embed_sum(talker.model.codec_embedding.weight, predictor.model.codec_embedding, self.codes,
-                            extra=self.extra, out=self.embeds)
+                            extra=self.trail.view(-1, self.trail.shape[-1]), extra_index=self.extra_row, out=self.embeds)
         # ---- talker decode step                                        talker_mode_runner.py:116-153
         nat.decode_layout(self.seq_lens, self.t_tables, self.page, 1, 1, self.t_pos, self.t_slots, self.t_ctx)
         set_context(False, slot_mapping=self.t_slots, context_lens=self.t_ctx, block_tables=self.t_tables,
                     max_context_len=self.width * self.page)
         th = talker(self.embeds, self.t_pos)
         self.hidden.copy_(th)
-        self._sample(linear(th, talker.codec_head.weight), self.t_temp, self.codes_t[0])
+        self._sample(linear(th, talker.codec_head.weight), self.t_temp, 0)
         reset_context()
+
+    def _state(self):
+        st = [self.seq_lens, self.hidden, self.codes_t, self.embeds, self.frame_idx, self.frames, self.active,
+              self.gen_step, self.frames_done, self.noise]
+        if self.sampled is not None:
+            st.append(self.sampled)
+        return st
 
     @torch.inference_mode()
     def capture(self):
         """Capture one frame.  Device state is saved around the warm-up so capture has no side effects."""
-        state = [t.clone() for t in (self.seq_lens, self.hidden, self.codes_t, self.embeds, self.frame_idx, self.frames)]
+        state = [t.clone() for t in self._state()]
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             self._frame()                                    # warm-up: lazy handles, kernel attributes
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
+        for t, v in zip(self._state(), state):               # the captured pass must also see a valid state
+            t.copy_(v)
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self._frame()
         torch.cuda.synchronize()
-        for t, v in zip((self.seq_lens, self.hidden, self.codes_t, self.embeds, self.frame_idx, self.frames), state):
+        for t, v in zip(self._state(), state):
             t.copy_(v)
         return self
 
     def step(self):
         """One codec frame for every stream: a single graph launch."""
+        if self.frames_run >= self.max_frames:
+            raise RuntimeError(f"DeviceFrameLoop: frame budget of {self.max_frames} frames exhausted "
+                               "(frames buffer and block tables are sized for it)")
+        self.frames_run += 1
         if self.graph is None:
             with torch.inference_mode():
                 self._frame()
@@ -182,9 +273,18 @@ class DeviceFrameLoop:
             self.step()
 
     def result(self) -> torch.Tensor:
-        """[frames, streams, 16] int64 on the host (synchronises)."""
+        """[frames, streams, 16] int64 on the host (synchronises).  Rows of a stream beyond its ``frame_counts()``
+        entry (EOS) are padding."""
         n = int(self.frame_idx.item())
         return self.frames[:n].cpu()
+
+    def frame_counts(self) -> list[int]:
+        """Frames produced per stream (a stream stops at its codec EOS unless ``ignore_eos``)."""
+        return self.frames_done.tolist()
+
+    def result_per_stream(self) -> list[torch.Tensor]:
+        fr, counts = self.result(), self.frame_counts()
+        return [fr[:n, i] for i, n in enumerate(counts)]
 
 
 class StepApiFrameLoop:

@@ -180,11 +180,22 @@ class ModelRunner:
         has ``k_cache`` / ``v_cache``."""
         cfg, c = self.config, self.stack_config
         if cfg.num_kvcache_blocks <= 0:
+            # the reference's accounting (base.py:131-151, restated in engine/memory.py and pinned against the
+            # reference's own method): pages = (budget - used - peak + current) // page_bytes, at least 1
+            from ..memory import num_kv_blocks
             free, total = torch.cuda.mem_get_info(self.device)
-            frac = cfg.process_gpu_memory_fraction or cfg.gpu_memory_utilization
-            budget = min(free, int(total * frac)) - (2 << 30)              # headroom for activations/graphs
-            cfg.num_kvcache_blocks = max(1, min(budget // self.kv_block_bytes(),
-                                                self.max_bs * self.max_blocks))
+            stats = torch.cuda.memory_stats(self.device)
+            blocks, raw = num_kv_blocks(total, free, torch.cuda.memory_allocated(self.device),
+                                        stats.get("allocated_bytes.all.peak", 0), stats.get("allocated_bytes.all.current", 0),
+                                        cfg.gpu_memory_utilization, cfg.process_gpu_memory_fraction, self.kv_block_bytes())
+            if raw <= 0 and cfg.gpu_memory_utilization >= 0.05:                 # base.py:148-153
+                import warnings
+                warnings.warn(f"KV cache allocation would be 0 pages (gpu_memory_utilization="
+                              f"{cfg.gpu_memory_utilization}); using 1 page")
+            self.kv_blocks_uncapped = blocks
+            # deviation, on purpose: pages beyond what max_num_seqs sequences of max_model_len tokens can address
+            # are dead memory (the reference would torch.empty them anyway); the pool here is zero-filled
+            cfg.num_kvcache_blocks = max(1, min(blocks, self.max_bs * self.max_blocks))
         self.kv_cache = torch.zeros(2, c.num_hidden_layers, cfg.num_kvcache_blocks, self.block_size,
                                     c.num_key_value_heads, c.head_dim, dtype=BF16, device=self.device)
         ws_bytes = nat.paged_attn_decode_workspace_bytes(1, c.num_attention_heads, c.head_dim,

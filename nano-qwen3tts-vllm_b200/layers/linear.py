@@ -140,7 +140,8 @@ class LinearBase(nn.Module):
             self.register_parameter("bias", None)
 
     def weight_loader(self, param: nn.Parameter, loaded_weight: torch.Tensor):
-        param.data.copy_(loaded_weight)
+        with torch.no_grad():
+            param.copy_(loaded_weight)           # not param.data: bumps the version packed_weight() watches
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         return linear(x, self.weight, self.bias)
@@ -169,11 +170,12 @@ class MergedColumnParallelLinear(ColumnParallelLinear):
         super().__init__(input_size, sum(output_sizes), bias)
 
     def weight_loader(self, param: nn.Parameter, loaded_weight: torch.Tensor, loaded_shard_id: int = None):
-        if loaded_shard_id is None:
-            param.data.copy_(loaded_weight)
-            return
-        off = sum(self.output_sizes[:loaded_shard_id])
-        param.data.narrow(0, off, self.output_sizes[loaded_shard_id]).copy_(loaded_weight)
+        with torch.no_grad():
+            if loaded_shard_id is None:
+                param.copy_(loaded_weight)
+                return
+            off = sum(self.output_sizes[:loaded_shard_id])
+            param.narrow(0, off, self.output_sizes[loaded_shard_id]).copy_(loaded_weight)
 
 
 class QKVParallelLinear(MergedColumnParallelLinear):

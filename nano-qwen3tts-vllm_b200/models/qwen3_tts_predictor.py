@@ -50,16 +50,23 @@ class Qwen3TTSCodePredictorForCausalLM(nn.Module):
         sd = self.convert_state_dict(state_dict)
         if not sd:                                   # already converted
             sd = dict(state_dict)
-        rest = {}
-        for k, v in sd.items():
-            parts = k.split(".")
-            if k.startswith("model.codec_embedding.") and parts[2].isdigit():
-                self.model.codec_embedding.data[int(parts[2])].copy_(v)
-            elif k.startswith("lm_head.") and parts[1].isdigit():
-                self.lm_head.data[int(parts[1])].copy_(v)
-            else:
-                rest[k] = v
-        return load_reference_weights(self, rest, strict=strict)
+        rest, emb_seen, head_seen = {}, set(), set()
+        with torch.no_grad():
+            for k, v in sd.items():
+                parts = k.split(".")
+                if k.startswith("model.codec_embedding.") and parts[2].isdigit():
+                    self.model.codec_embedding[int(parts[2])].copy_(v)
+                    emb_seen.add(int(parts[2]))
+                elif k.startswith("lm_head.") and parts[1].isdigit():
+                    self.lm_head[int(parts[1])].copy_(v)
+                    head_seen.add(int(parts[1]))
+                else:
+                    rest[k] = v
+        n = self.lm_head.shape[0]
+        if strict and (len(emb_seen) != n or len(head_seen) != n):
+            raise KeyError(f"missing keys: codec_embedding {sorted(set(range(n)) - emb_seen)}, "
+                           f"lm_head {sorted(set(range(n)) - head_seen)}")
+        return load_reference_weights(self, rest, strict=strict, prefilled=("model.codec_embedding", "lm_head"))
 
     def get_input_embeddings(self, input_ids, input_embeds, generation_steps):
         """Prefill: the [hidden, embed(code0)] rows pass through.  Decode: row i is

@@ -241,11 +241,15 @@ _MERGED = {"q_proj": ("qkv_proj", 0), "k_proj": ("qkv_proj", 1), "v_proj": ("qkv
            "gate_proj": ("gate_up_proj", 0), "up_proj": ("gate_up_proj", 1)}
 
 
-def load_reference_weights(module: nn.Module, state_dict: dict, strict: bool = True) -> list[str]:
+def load_reference_weights(module: nn.Module, state_dict: dict, strict: bool = True,
+                           prefilled: tuple[str, ...] = ()) -> list[str]:
     """Load a state dict that uses the reference's (converted) key names into ``module``, merging
-    q/k/v and gate/up shards into the fused parameters.  Returns the keys that were not consumed."""
+    q/k/v and gate/up shards into the fused parameters.  Returns the keys that were not consumed.
+    ``strict``: unexpected keys AND parameters (or shards of merged parameters) left unfilled raise;
+    ``prefilled`` names parameters the caller has already loaded."""
     params = dict(module.named_parameters())
     unused = []
+    filled: dict[str, set] = {}
     for name, w in state_dict.items():
         target, shard = name, None
         for src, (dst, sid) in _MERGED.items():
@@ -257,14 +261,24 @@ def load_reference_weights(module: nn.Module, state_dict: dict, strict: bool = T
             unused.append(name)
             continue
         loader = getattr(p, "weight_loader", None)
+        filled.setdefault(target, set()).add(shard)
         if shard is not None:
             loader(p, w, shard)
         elif loader is not None:
             loader(p, w)
         else:
-            p.data.copy_(w)
+            with torch.no_grad():
+                p.copy_(w)
     if strict and unused:
         raise KeyError(f"unexpected keys: {unused[:8]}{'...' if len(unused) > 8 else ''}")
+    if strict:
+        missing = [n for n in params if n not in filled and n not in prefilled]
+        for n, shards in filled.items():
+            want = 3 if n.endswith("qkv_proj.weight") else 2 if n.endswith("gate_up_proj.weight") else 0
+            if want and None not in shards and len(shards) < want:
+                missing.append(f"{n} (shards {sorted(shards)} of {want})")
+        if missing:
+            raise KeyError(f"missing keys: {missing[:8]}{'...' if len(missing) > 8 else ''}")
     return unused
 
 

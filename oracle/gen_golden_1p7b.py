@@ -1,0 +1,121 @@
+"""Golden greedy codec frames + logits of the CPU oracle at the NAMED model size (Qwen3-TTS-12Hz-1.7B
+shapes), for the GPU parity tests of tests/test_gpu_parity_1p7b.py.
+
+TEST INFRASTRUCTURE ONLY - see ``oracle/__init__.py``.
+
+north_star: "greedy codec-token sequences are identical for the first 256 frames" (512 for BASELINE
+configs[1]); "attention outputs and logits match within 2e-2 relative in bf16".  The CPU oracle needs
+~0.5 s (1 stream) to ~3.6 s (64 streams) per frame at this size, so the expected frames are generated ONCE
+here, in the build container, and committed under tests/golden/:
+
+    python -m oracle.gen_golden_1p7b [--only b1,b8,b64] [--modes eager,fused]
+
+Per (streams, rounding mode) one file ``frames_1p7b_b{B}_{mode}.pt``:
+    frames      int16 [F, B, 16]    the oracle's greedy codes (top_k = 1, first maximum on exact ties)
+    top1, top2  bf16  [F, 16, B]    the two largest logits of the decision that produced frames[f, :, c]
+                                     (c = 0: talker - prefill for f = 0, decode step f otherwise; c >= 1: predictor)
+    rows        int64 [R]           the streams whose logits are kept (all of them up to 16 streams)
+    talker_logits     bf16 [4, R, 3072]   prefill + decode steps 1..3 (inputs = the oracle's own codes)
+    predictor_logits  bf16 [3, R, 2048]   frame 0, codebooks 1 (prefill pass), 2 (first decode pass), 15 (last)
+    meta        dict                dims, seeds, prompt spec
+
+Weights: ``oracle.model.synthetic_weights(seed=1234)`` (CPU generator, machine independent); prompts
+``N(0, 0.05^2)`` bf16 [64, H] from ``manual_seed(1000 + s)``; trailing-text term = one pad row, seed 999;
+EOS ignored.  ``mode`` = eager (the reference source op by op: what its CPU path
+computes) | fused (RMSNorm / SiLU*mul with inductor's single store rounding: what its GPU path computes).
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import model as OM      # noqa: E402
+from oracle import ops as O         # noqa: E402
+
+BF16 = torch.bfloat16
+PROMPT_LEN = 64
+CONFIGS = {"b1": (1, 512), "b8": (8, 256), "b64": (64, 256)}      # BASELINE configs[1], [2], [4]
+
+
+def dims_1p7b():
+    td = OM.StackDims(hidden_size=2048, intermediate_size=6144, num_hidden_layers=28, vocab_size=3072,
+                      rope_theta=1e6, mrope_section=[24, 20, 20], mrope_interleaved=True, page_size=256)
+    pd = OM.StackDims(hidden_size=1024, intermediate_size=3072, num_hidden_layers=5, vocab_size=2048,
+                      rope_theta=1e6, page_size=256)
+    return td, pd
+
+
+def prompts_for(b: int, hidden: int):
+    prompts = [(torch.randn(PROMPT_LEN, hidden, generator=torch.Generator().manual_seed(1000 + s)) * 0.05).to(BF16)
+               for s in range(b)]
+    pad = (torch.randn(1, hidden, generator=torch.Generator().manual_seed(999)) * 0.05).to(BF16)
+    return prompts, pad
+
+
+def kept_rows(b: int) -> torch.Tensor:
+    return torch.arange(b) if b <= 16 else torch.cat([torch.arange(8), torch.arange(b - 8, b)])
+
+
+def generate(b: int, nframes: int, fused: bool, tw, pw, td, pd, log=print):
+    prompts, pad = prompts_for(b, td.hidden_size)
+    pages = (PROMPT_LEN + nframes + 1 + td.page_size - 1) // td.page_size
+    talker = OM.Talker(td, tw, b * pages, fused_rounding=fused)
+    predictor = OM.Predictor(pd, pw, b, td.hidden_size, fused_rounding=fused)
+    rows = kept_rows(b)
+    top1, top2, t_logits, p_logits = [], [], [], []
+    calls = {"n": 0, "t0": time.time()}
+
+    def greedy(logits, temps):
+        n = calls["n"]
+        calls["n"] += 1
+        v = logits.float().topk(2, dim=-1).values
+        top1.append(v[:, 0].to(BF16)); top2.append(v[:, 1].to(BF16))
+        is_talker = logits.shape[-1] == td.vocab_size
+        if is_talker and len(t_logits) < 4:
+            t_logits.append(logits[rows].clone())
+        if not is_talker and n in (1, 2, 15):           # call 0 = talker prefill; 1..15 = frame 0's predictor passes
+            p_logits.append(logits[rows].clone())
+        if is_talker and (n // 16) % 16 == 0:
+            log(f"  b={b} fused={fused} frame {n // 16}/{nframes}  {time.time() - calls['t0']:.0f}s")
+        return O.topk_sample(logits, temps, torch.ones(logits.shape), top_k=1)
+
+    with torch.inference_mode():
+        res = OM.run_frames(talker, predictor, prompts, nframes, pad, greedy)
+    frames = torch.tensor(res.frames, dtype=torch.int16)                       # [F, B, 16]
+    # sampler calls: 0 = prefill (code0 of frame 0); per frame f: 15 predictor calls then the talker call that
+    # yields code0 of frame f + 1 (the last one belongs to the frame after the run: dropped)
+    t1, t2 = torch.stack(top1[:16 * nframes]), torch.stack(top2[:16 * nframes])   # [F*16, B]
+    return dict(frames=frames, top1=t1.view(nframes, 16, b), top2=t2.view(nframes, 16, b), rows=rows,
+                talker_logits=torch.stack(t_logits), predictor_logits=torch.stack(p_logits),
+                meta=dict(model="1.7B", streams=b, frames=nframes, prompt_len=PROMPT_LEN, weight_seed=1234,
+                          rounding="fused" if fused else "eager", torch=torch.__version__,
+                          generator="oracle/gen_golden_1p7b.py", seconds=round(time.time() - calls["t0"], 1)))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default="b1,b8,b64")
+    ap.add_argument("--modes", default="eager,fused")
+    ap.add_argument("--out", default=os.path.join(ROOT, "tests", "golden"))
+    a = ap.parse_args()
+    torch.set_num_threads(os.cpu_count() or 1)
+    td, pd = dims_1p7b()
+    tw, pw = OM.synthetic_weights(td, pd, seed=1234)
+    for name in a.only.split(","):
+        b, nframes = CONFIGS[name]
+        for mode in a.modes.split(","):
+            out = generate(b, nframes, mode == "fused", tw, pw, td, pd)
+            path = os.path.join(a.out, f"frames_1p7b_{name}_{mode}.pt")
+            torch.save(out, path)
+            print(f"wrote {path} ({os.path.getsize(path) / 1e6:.2f} MB, {out['meta']['seconds']} s)", flush=True)
+
+
+if __name__ == "__main__":
+    main()

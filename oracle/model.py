@@ -55,10 +55,15 @@ class AttnContext:
 class Stack:
     """A talker or predictor transformer stack on CPU."""
 
-    def __init__(self, dims: StackDims, weights: dict, num_blocks: int, silu_fused_rounding=False):
+    def __init__(self, dims: StackDims, weights: dict, num_blocks: int, silu_fused_rounding=False,
+                 fused_rounding=False):
+        """``fused_rounding``: RMSNorm (hidden and q/k head norms) and SiLU*mul with the single store
+        rounding inductor emits for the ``@torch.compile``d modules on a GPU (layernorm.py:17,29,
+        qwen3_tts_share.py:116); default = the source evaluated op by op (what runs on CPU)."""
         self.d = dims
         self.w = weights
-        self.silu_fused_rounding = silu_fused_rounding
+        self.fused = fused_rounding
+        self.silu_fused_rounding = silu_fused_rounding or fused_rounding
         self.inv_freq = ops.make_inv_freq(dims.head_dim, dims.rope_theta)
         self.dim_modality = ops.mrope_dim_modality(dims.head_dim, dims.mrope_section, dims.mrope_interleaved)
         # base.py:158: [2, L, blocks, page, kv_heads, hd]
@@ -73,7 +78,7 @@ class Stack:
         k = ops.linear(x, w[p + "k_proj.weight"]).view(-1, d.num_key_value_heads, d.head_dim)
         v = ops.linear(x, w[p + "v_proj.weight"]).view(-1, d.num_key_value_heads, d.head_dim)
         q, k = ops.qknorm_rope(q, k, w[p + "q_norm.weight"], w[p + "k_norm.weight"], d.rms_norm_eps,
-                               positions, self.inv_freq, 1.0, self.dim_modality)
+                               positions, self.inv_freq, 1.0, self.dim_modality, self.fused)
         k_cache, v_cache = self.kv_cache[0, li], self.kv_cache[1, li]
         if ctx.slot_mapping is not None and ctx.slot_mapping.numel():
             ops.store_kvcache(k, v, k_cache, v_cache, ctx.slot_mapping)        # attention.py:76-77
@@ -95,11 +100,11 @@ class Stack:
     def layer(self, li, positions, h, ctx):
         w, p = self.w, f"model.layers.{li}."
         res = h
-        h = ops.rmsnorm(h, w[p + "input_layernorm.weight"], self.d.rms_norm_eps)
+        h = ops.rmsnorm(h, w[p + "input_layernorm.weight"], self.d.rms_norm_eps, self.fused)
         h = self.attention(li, positions, h, ctx)
         h = res + h
         res = h
-        h = ops.rmsnorm(h, w[p + "post_attention_layernorm.weight"], self.d.rms_norm_eps)
+        h = ops.rmsnorm(h, w[p + "post_attention_layernorm.weight"], self.d.rms_norm_eps, self.fused)
         h = self.mlp(li, h)
         return res + h
 
@@ -107,7 +112,7 @@ class Stack:
         h = embeds
         for li in range(self.d.num_hidden_layers):
             h = self.layer(li, positions, h, ctx)
-        return ops.rmsnorm(h, self.w["model.norm.weight"], self.d.rms_norm_eps)
+        return ops.rmsnorm(h, self.w["model.norm.weight"], self.d.rms_norm_eps, self.fused)
 
 
 def prefill_layout(seq_lens, block_tables, page):
@@ -201,50 +206,78 @@ def next_talker_embed(talker_w, predictor_w, code0, codes, extra):
 class FrameLoopResult:
     frames: list = field(default_factory=list)       # per frame: list over streams of 16 ints
     first_logits: torch.Tensor | None = None
+    per_stream: list = field(default_factory=list)   # per stream: its frames (ragged once codec EOS is honoured)
 
 
 def run_frames(talker: Talker, predictor: Predictor, prompts, num_frames, tts_pad_embed,
-               sampler, talker_temp=1.0, predictor_temp=0.9):
-    """Greedy/sampled frame loop for ``len(prompts)`` streams stepping in lock-step.
+               sampler, talker_temp=1.0, predictor_temp=0.9, trailing=None, codec_eos=None):
+    """Greedy/sampled frame loop for ``len(prompts)`` streams stepping in lock-step
+    (interface.py:1207-1290 per stream).
 
     ``sampler(logits, temperatures) -> LongTensor[B]``.  Block tables are
     allocated contiguously per stream (stream s owns talker pages
     ``s*P .. s*P+P-1``); the predictor re-uses page ``s`` every frame, as the
-    block manager does after ``deallocate`` (scheduler.py:73-79)."""
+    block manager does after ``deallocate`` (scheduler.py:73-79).
+    ``trailing[s]`` = ``trailing_text_hiddens`` of stream s ``[T_s, H]`` (added at
+    generation step < T_s, ``tts_pad_embed`` after, interface.py:1282-1285);
+    ``codec_eos`` (2150) ends a stream before the frame whose code0 it is
+    (interface.py:1233-1239); ``None`` ignores EOS.  ``res.frames`` is filled while
+    every stream is alive, ``res.per_stream`` always."""
     page = talker.stack.d.page_size
     b = len(prompts)
     lens = [p.shape[0] for p in prompts]
     pages_per = (max(lens) + num_frames + 1 + page - 1) // page
     t_tables = [[s * pages_per + i for i in range(pages_per)] for s in range(b)]
-    p_tables = [[s] for s in range(b)]
     res = FrameLoopResult()
-    tt = torch.full((b,), talker_temp, dtype=torch.float32)
-    pt = torch.full((b,), predictor_temp, dtype=torch.float32)
+    res.per_stream = [[] for _ in range(b)]
 
     def table_for(n, tab):
         return tab[: (n + page - 1) // page]
 
+    def temps(t, n):
+        return torch.full((n,), t, dtype=torch.float32)
+
     logits, hidden = talker.prefill(prompts, [table_for(n, t) for n, t in zip(lens, t_tables)])
     res.first_logits = logits
-    code0 = sampler(logits, tt).tolist()
+    code0 = sampler(logits, temps(talker_temp, b)).tolist()
     lens = [n + 1 for n in lens]
-    for _ in range(num_frames):
+    alive = list(range(b))                       # stream ids; row r of hidden / code0 belongs to alive[r]
+    for step in range(num_frames):
+        if codec_eos is not None:
+            keep = [r for r in range(len(alive)) if code0[r] != codec_eos]
+            if len(keep) != len(alive):
+                hidden = hidden[keep]
+                code0 = [code0[r] for r in keep]
+                alive = [alive[r] for r in keep]
+        if not alive:
+            break
+        n = len(alive)
         emb0 = talker.w["model.codec_embedding.weight"][torch.tensor(code0)]          # interface.py:1242
-        pin = [torch.stack([hidden[s], emb0[s]], 0) for s in range(b)]                 # :1252
+        pin = [torch.stack([hidden[r], emb0[r]], 0) for r in range(n)]                 # :1252
+        p_tables = [[s] for s in alive]
         plogits = predictor.prefill(pin, p_tables)
-        codes = [sampler(plogits, pt).tolist()]
-        plens = [3] * b
+        codes = [sampler(plogits, temps(predictor_temp, n)).tolist()]
+        plens = [3] * n
         for g in range(1, 15):
-            plogits = predictor.decode(codes[-1], [g] * b, plens, p_tables)
-            codes.append(sampler(plogits, pt).tolist())
-            plens = [n + 1 for n in plens]
-        per_stream = [[code0[s]] + [codes[g][s] for g in range(15)] for s in range(b)]
-        res.frames.append(per_stream)
-        nxt = torch.cat([next_talker_embed(talker.w, predictor.w, per_stream[s][0], per_stream[s][1:], tts_pad_embed)
-                         for s in range(b)], 0)
-        logits, hidden = talker.decode(nxt, lens, [table_for(n, t) for n, t in zip(lens, t_tables)])
-        code0 = sampler(logits, tt).tolist()
-        lens = [n + 1 for n in lens]
+            plogits = predictor.decode(codes[-1], [g] * n, plens, p_tables)
+            codes.append(sampler(plogits, temps(predictor_temp, n)).tolist())
+            plens = [m + 1 for m in plens]
+        per_row = [[code0[r]] + [codes[g][r] for g in range(15)] for r in range(n)]
+        for r, s in enumerate(alive):
+            res.per_stream[s].append(per_row[r])
+        if n == b:
+            res.frames.append(per_row)
+        extras = []
+        for s in alive:
+            t = None if trailing is None else trailing[s]
+            extras.append(t[step:step + 1] if t is not None and step < t.shape[0] else tts_pad_embed)
+        nxt = torch.cat([next_talker_embed(talker.w, predictor.w, per_row[r][0], per_row[r][1:], extras[r])
+                         for r in range(n)], 0)
+        cur = [lens[s] for s in alive]
+        logits, hidden = talker.decode(nxt, cur, [table_for(lens[s], t_tables[s]) for s in alive])
+        code0 = sampler(logits, temps(talker_temp, n)).tolist()
+        for s in alive:
+            lens[s] += 1
     return res
 
 

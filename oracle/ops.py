@@ -10,7 +10,8 @@ linear, sampler, lm heads, decoder layer, talker / predictor stacks.
 PARITY UNPINNED by a reference run (CUDA-only in the reference): store_kvcache
 (Triton kernel) and the two flash-attn calls; restated from
 ``layers/attention.py:10-30,73-96`` and cross-checked against the flash-attn
-wheel on the GPU box (tests/test_gpu_reference_kernels.py).
+wheel and the reference's Triton kernel on the GPU box
+(tests/test_gpu_reference_kernels.py).
 """
 from __future__ import annotations
 
@@ -118,12 +119,16 @@ def varlen_attn_prefill(q, k, v, cu_seqlens_q, cu_seqlens_k, scale,
 # --------------------------------------------------------------------------
 # a4  RMSNorm                                           layers/layernorm.py:18-41
 # --------------------------------------------------------------------------
-def rmsnorm(x, weight, eps):
+def rmsnorm(x, weight, eps, fused_rounding=False):
     """layernorm.py:22-27 in eager mode: fp32 normalise, round to bf16, then a
-    bf16*bf16->bf16 multiply with the weight (a second rounding)."""
+    bf16*bf16->bf16 multiply with the weight (a second rounding).
+    ``fused_rounding``: the same source compiled by inductor on a GPU
+    (``@torch.compile``, layernorm.py:17) - fp32 through to the one store rounding."""
     xf = x.float()
     var = xf.pow(2).mean(dim=-1, keepdim=True)
     y = xf * torch.rsqrt(var + eps)
+    if fused_rounding:
+        return (y * weight.float()).to(x.dtype)
     return y.to(x.dtype) * weight
 
 
@@ -181,13 +186,14 @@ def rope_cos_sin(positions, inv_freq, dtype=BF16, attention_scaling=1.0, dim_mod
     if positions.dim() == 1:
         positions = positions.unsqueeze(0).expand(3, -1)
     pos = positions.float()                                      # [3,T]
+    inv_freq = inv_freq.to(positions.device)
     freqs = pos[:, :, None] * inv_freq.float()[None, None, :]    # [3,T,half]; K=1 matmul == product
     emb = torch.cat((freqs, freqs), dim=-1)                      # [3,T,hd]
     cos3 = (emb.cos() * attention_scaling).to(dtype)
     sin3 = (emb.sin() * attention_scaling).to(dtype)
     if dim_modality is None:
         dim_modality = [0] * hd
-    sel = torch.tensor(dim_modality, dtype=torch.long)
+    sel = torch.tensor(dim_modality, dtype=torch.long, device=positions.device)
     idx = sel.view(1, 1, hd).expand(1, cos3.shape[1], hd)
     cos = torch.gather(cos3, 0, idx)[0]
     sin = torch.gather(sin3, 0, idx)[0]
@@ -215,10 +221,10 @@ def rope(positions, query, key, inv_freq, attention_scaling=1.0, dim_modality=No
 
 
 def qknorm_rope(q, k, q_weight, k_weight, eps, positions, inv_freq,
-                attention_scaling=1.0, dim_modality=None):
+                attention_scaling=1.0, dim_modality=None, fused_rounding=False):
     """models/qwen3_tts_share.py:96-104: per-head RMSNorm on q and k, then RoPE."""
-    qn = rmsnorm(q, q_weight, eps)
-    kn = rmsnorm(k, k_weight, eps)
+    qn = rmsnorm(q, q_weight, eps, fused_rounding)
+    kn = rmsnorm(k, k_weight, eps, fused_rounding)
     return rope(positions, qn, kn, inv_freq, attention_scaling, dim_modality)
 
 

@@ -285,9 +285,121 @@ def pin_models():
     return out
 
 
+# ------------------------------------------------------------------ a11: KV-pool memory policy
+def pin_memory_policy():
+    """Run the reference's own memory-policy code on tables of inputs and assert that
+    nano_qwen3tts_vllm_b200.engine.memory reproduces every number exactly.
+
+    ``interface.py`` cannot be imported (qwen_tts / librosa / soundfile are absent), so the three pure
+    functions ``_estimate_model_params`` / ``_kv_block_bytes`` / ``_compute_memory_split``
+    (interface.py:57-197) are lifted from its source by ``ast`` and executed unmodified with a stand-in for
+    ``torch.cuda.get_device_properties``; ``ModelRunner.allocate_kv_cache`` (engine/model_runner/base.py:131-164)
+    is the reference's unbound method called on a stub runner whose ``torch`` exposes the allocator numbers of
+    the table row."""
+    import ast
+    import json
+    import logging
+    import tempfile
+
+    import nano_qwen3tts_vllm_b200.engine.memory as mem
+    from nano_qwen3tts_vllm_b200.config import ModelConfig, qwen3_tts_config
+    from nano_qwen3tts_vllm.config import Qwen3TTSConfig
+    import nano_qwen3tts_vllm.engine.model_runner.base as ref_base
+
+    src = open(os.path.join(REF_SRC, "interface.py")).read()
+    wanted = {"_estimate_model_params", "_kv_block_bytes", "_compute_memory_split"}
+    tree = ast.parse(src)
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in wanted]
+    assert {n.name for n in body} == wanted
+    vram = {"total": 0}
+    fake_torch = types.SimpleNamespace(cuda=types.SimpleNamespace(
+        get_device_properties=lambda i: types.SimpleNamespace(total_memory=vram["total"])))
+    ns = {"os": os, "json": json, "torch": fake_torch, "Qwen3TTSConfig": Qwen3TTSConfig,
+          "logger": logging.getLogger("ref.interface")}
+    exec(compile(ast.Module(body=body, type_ignores=[]), "interface.py[memory policy]", "exec"), ns)
+
+    rows = {"split": [], "blocks": []}
+    for size in ("1.7B", "0.6B"):
+        mc = qwen3_tts_config(size)
+        raw = mc.to_dict()
+        for stack in (raw["talker_config"], raw["talker_config"]["code_predictor_config"]):
+            stack.pop("text_vocab_size", None) if not stack.get("text_vocab_size") else None
+            stack.pop("text_hidden_size", None) if not stack.get("text_hidden_size") else None
+        with tempfile.TemporaryDirectory() as d:
+            with open(os.path.join(d, "config.json"), "w") as f:
+                json.dump(raw, f)
+            ref_cfg = Qwen3TTSConfig(**raw)
+            for cfg_ref, cfg_ours in ((ref_cfg.talker_config, mc.talker),
+                                      (ref_cfg.talker_config.code_predictor_config, mc.predictor)):
+                assert ns["_estimate_model_params"](cfg_ref) == mem.estimate_model_params(cfg_ours)
+                assert ns["_kv_block_bytes"](cfg_ref) == mem.kv_block_bytes(cfg_ours)
+            for total in (24 << 30, 80 << 30, 85_899_345_920, 191_514_542_080):
+                for util in (0.02, 0.05, 0.3, 0.5, 0.9, 0.95):
+                    vram["total"] = total
+                    want = ns["_compute_memory_split"](d, util)
+                    got = mem.compute_memory_split(mc, util, total)
+                    for k in ("talker_util", "pred_util", "process_gpu_memory_fraction"):
+                        assert got[k] == want[k], (size, total, util, k, got[k], want[k])
+                    rows["split"].append(dict(model=size, total_vram=total, gpu_memory_utilization=util,
+                                              talker_util=want["talker_util"], pred_util=want["pred_util"],
+                                              process_gpu_memory_fraction=want["process_gpu_memory_fraction"]))
+
+    # ---- allocate_kv_cache: the reference method on a stub runner
+    class _Empty:
+        def __init__(self, *shape):
+            self.shape = shape
+
+        def __getitem__(self, idx):
+            return self
+
+    real_torch = ref_base.torch
+    try:
+        for size in ("1.7B", "0.6B"):
+            mc = qwen3_tts_config(size)
+            for stack in (mc.talker, mc.predictor):
+                hf = types.SimpleNamespace(num_key_value_heads=stack.num_key_value_heads, head_dim=stack.head_dim,
+                                           hidden_size=stack.hidden_size, num_attention_heads=stack.num_attention_heads,
+                                           num_hidden_layers=stack.num_hidden_layers)
+                bb = mem.kv_block_bytes(stack)
+                for total, free, alloc, peak, cur, util, frac in (
+                        (191_514_542_080, 180 << 30, 4 << 30, 6 << 30, 4 << 30, 0.9, None),
+                        (191_514_542_080, 180 << 30, 4 << 30, 6 << 30, 4 << 30, 0.4278, 0.9),
+                        (191_514_542_080, 100 << 30, 9 << 30, 12 << 30, 9 << 30, 0.85, 0.5),
+                        (85_899_345_920, 70 << 30, 5 << 30, 5 << 30, 5 << 30, 0.3, None),
+                        (25_769_803_776, 2 << 30, 3 << 30, 4 << 30, 3 << 30, 0.9, None),       # nothing left: 1 page
+                        (25_769_803_776, 20 << 30, 3 << 30, 4 << 30, 3 << 30, 0.05, 0.3)):
+                    cfg = types.SimpleNamespace(gpu_memory_utilization=util, process_gpu_memory_fraction=frac,
+                                                num_kvcache_blocks=-1)
+                    ref_base.torch = types.SimpleNamespace(
+                        bfloat16=real_torch.bfloat16, empty=_Empty,
+                        cuda=types.SimpleNamespace(
+                            mem_get_info=lambda: (free, total), memory_allocated=lambda: alloc,
+                            memory_stats=lambda: {"allocated_bytes.all.peak": peak, "allocated_bytes.all.current": cur}))
+                    runner = types.SimpleNamespace(config=cfg, model_config=hf, world_size=1, block_size=256,
+                                                   model=types.SimpleNamespace(modules=lambda: []))
+                    import warnings
+                    with warnings.catch_warnings():
+                        warnings.simplefilter("ignore")
+                        ref_base.ModelRunner.allocate_kv_cache(runner)
+                    got, _ = mem.num_kv_blocks(total, free, alloc, peak, cur, util, frac, bb)
+                    assert got == cfg.num_kvcache_blocks, (size, total, free, util, frac, got, cfg.num_kvcache_blocks)
+                    rows["blocks"].append(dict(model=size, layers=stack.num_hidden_layers, total=total, free=free,
+                                               allocated=alloc, peak=peak, current=cur, gpu_memory_utilization=util,
+                                               process_gpu_memory_fraction=frac, block_bytes=bb,
+                                               num_kvcache_blocks=cfg.num_kvcache_blocks))
+    finally:
+        ref_base.torch = real_torch
+    return rows
+
+
 def main():
     import_reference()
     os.makedirs(GOLDEN, exist_ok=True)
+    import json
+    policy = pin_memory_policy()
+    with open(os.path.join(GOLDEN, "memory_policy.json"), "w") as f:
+        json.dump(policy, f, indent=1)
+    print(f"memory policy pinned: {len(policy['split'])} split rows, {len(policy['blocks'])} allocation rows")
     ops_vec = pin_ops()
     torch.save(ops_vec, os.path.join(GOLDEN, "ops.pt"))
     print("ops pinned:", ", ".join(ops_vec))

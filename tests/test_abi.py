@@ -15,7 +15,7 @@ def test_library_exports_every_declared_symbol(native):
     assert len(declared) >= 14
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/b200tts.h but not exported"
-    assert lib.b2tts_version() >= 1
+    assert lib.b2tts_version() >= 2
     assert lib.b2tts_last_error() is not None
 
 
@@ -45,6 +45,26 @@ def test_sass_uses_bulk_async_copy():
         pytest.skip("cuobjdump unavailable")
     assert "UBLKCP" in out.stdout
     assert "sm_100a" in subprocess.run(["cuobjdump", "-lelf", so], capture_output=True, text=True).stdout
+
+
+def test_sass_has_tcgen05_tmem_and_tma_per_kernel():
+    """SASS evidence per kernel (profiles/sass_counts.txt is the committed copy): the projection GEMM issues
+    tcgen05.mma (UTCHMMA) with TMEM accumulators read by tcgen05.ld (LDTM) and operands moved by the TMA unit
+    (UTMALDG tensor maps + UBLKCP bulk copies); the attention kernels stream K/V with UBLKCP; the tile prefill
+    attention runs QK^T and PV on tcgen05."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import sass_counts
+    try:
+        c = sass_counts.counts()
+    except (RuntimeError, OSError):
+        pytest.skip("cuobjdump unavailable")
+    gemm = [v for k, v in c.items() if k.startswith("b2::gemm_stream_kernel")]
+    assert gemm and all(v["UTCHMMA"] > 0 and v["LDTM"] > 0 and v["UTMALDG"] > 0 and v["UBLKCP"] > 0 for v in gemm)
+    for prefix in ("b2::paged_attn_kernel", "b2::fused_decode_attn_kernel"):
+        ks = [v for k, v in c.items() if k.startswith(prefix)]
+        assert ks and all(v["UBLKCP"] > 0 for v in ks), prefix
+    assert not any(v["HMMA"] for v in c.values()), "no legacy mma.sync tensor-core path in this library"
 
 
 def test_product_never_imports_oracle():

@@ -10,7 +10,7 @@ BF16 = torch.bfloat16
 H, KVH, HD, PAGE = 16, 8, 128, 256
 
 
-def _case(native, b, max_len, mrope, rounding, seed, pad_rows=0):
+def _case(native, b, max_len, mrope, rounding, seed, pad_rows=0, ws=None, max_ctx_override=None):
     g = torch.Generator(device="cuda").manual_seed(seed)
     dev = "cuda"
     lens = torch.randint(1, max_len + 1, (b,), generator=g, device=dev, dtype=torch.int32)
@@ -41,6 +41,9 @@ def _case(native, b, max_len, mrope, rounding, seed, pad_rows=0):
     else:
         pos, modality = (lens.long() - 1).clamp_min(0).contiguous(), None
     eps, scale, max_ctx = 1e-6, HD ** -0.5, width * PAGE
+    if max_ctx_override:                             # table capacity larger than the longest row: more KV splits
+        max_ctx = max_ctx_override
+        bt = torch.cat([bt, torch.full((b, max_ctx // PAGE - width), -1, dtype=torch.int32, device=dev)], 1).contiguous()
     # separate launches
     kc1, vc1 = kc.clone(), vc.clone()
     q_rot, _ = native.qknorm_rope_kvwrite(q, k, v, qw, kw, eps, pos, inv_freq, modality=modality, slot_mapping=slots,
@@ -48,7 +51,8 @@ def _case(native, b, max_len, mrope, rounding, seed, pad_rows=0):
     want = native.paged_attn_decode(q_rot, kc1, vc1, bt, lens, scale, max_ctx)
     # one launch
     kc2, vc2 = kc.clone(), vc.clone()
-    ws = native.fused_decode_attn_workspace(b, H, HD, max_ctx, dev)
+    if ws is None:
+        ws = native.fused_decode_attn_workspace(b, H, HD, max_ctx, dev)
     got = native.fused_decode_attn(q, k, v, qw, kw, eps, pos, inv_freq, slots, kc2, vc2, bt, lens, scale, max_ctx, ws,
                                    modality=modality, rounding=rounding)
     got2 = native.fused_decode_attn(q, k, v, qw, kw, eps, pos, inv_freq, slots, kc2, vc2, bt, lens, scale, max_ctx, ws,
@@ -73,3 +77,12 @@ def test_fused_decode_attention_matches_separate_launches(native, b, max_len, mr
 def test_fused_decode_attention_fused_rounding_and_padding_rows(native):
     _case(native, 16, 300, True, 1, seed=3, pad_rows=5)
     _case(native, 64, 64, False, 0, seed=4, pad_rows=1)
+
+
+def test_one_workspace_serves_every_batch_size(native):
+    """One zero-filled workspace sized for the largest batch, reused by launches of shrinking batch sizes with a
+    4096-token table capacity (the runner's layout, engine/model_runner/base.py): the split-KV tickets of one batch
+    size must not overlap the partial accumulators another batch size wrote (round-1 advisor finding)."""
+    ws = native.fused_decode_attn_workspace(16, H, HD, 4096, "cuda")
+    for i, b in enumerate((16, 8, 2, 1, 8, 16, 3)):
+        _case(native, b, 700, i % 2 == 0, 0, seed=50 + i, ws=ws, max_ctx_override=4096)

@@ -58,7 +58,7 @@ def pred_prefill():
 
 hid_p = pred_decode()
 def head_sample():
-    loop._sample(linear(hid_p, P.lm_head[5]), loop.p_temp, loop.codes_t[6])
+    loop._sample(linear(hid_p, P.lm_head[5]), loop.p_temp, 6)
 
 timed("whole frame", loop._frame)
 timed("talker decode pass (28 layers)", talker_pass)
