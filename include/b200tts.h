@@ -89,12 +89,15 @@ B2TTS_API int b2tts_paged_attn_decode(const void* q, int64_t q_row_stride,
  * strides in elements; cu_seqlens_* [num_seqs+1] int32.  Causal mask is bottom-right
  * aligned (query i of a sequence sees keys 0 .. len_k-len_q+i).  When block_table is
  * non-NULL (prefix-cache hit, attention.py:79-80) k,v are the paged caches
- * [num_pages, page_size, kv_heads, head_dim] and are read through block_table. */
+ * [num_pages, page_size, kv_heads, head_dim] and are read through block_table.
+ * total_k = rows of the packed k/v (ignored with a block table).  max_seqlen_q >= 128 (packed k/v) runs the
+ * tcgen05 tile kernel: 128-query x 128-key tiles, QK^T and PV on the tensor cores with TMEM accumulators, K/V by
+ * TMA, causal tile skipping; shorter prompts run one CTA per query token. */
 B2TTS_API int b2tts_varlen_attn_prefill(const void* q, int64_t q_row_stride,
                               const void* k, int64_t k_row_stride,
                               const void* v, int64_t v_row_stride,
                               const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
-                              void* out, int num_seqs, int total_q,
+                              void* out, int num_seqs, int total_q, int total_k,
                               int max_seqlen_q, int max_seqlen_k,
                               int num_heads, int num_kv_heads, int head_dim, float scale,
                               const int32_t* block_table, int bt_stride, int page_size,
@@ -161,6 +164,15 @@ B2TTS_API int b2tts_topk_sample(const void* logits, int64_t logits_row_stride, i
                       int64_t* out_index, float* probs_out,
                       int batch, int vocab, int top_k, float top_p, int apply_top_p,
                       void* stream);
+/* The same sampler followed, in the same launch, by the gather of the next predictor pass's input embedding:
+ * embed_out[i, :] = embed_table[out_index[i], :]   (bf16 rows of embed_cols)
+ * replaces Sampler.forward + codec_embedding[g-1](id)   layers/sampler.py:15-24, models/qwen3_tts_predictor.py:94-95
+ * vocab <= 4096 and a multiple of 8. */
+B2TTS_API int b2tts_topk_sample_embed(const void* logits, int64_t logits_row_stride, int logits_fp32,
+                            const float* temperatures, const float* noise,
+                            int64_t* out_index, int batch, int vocab, int top_k,
+                            const void* embed_table, int embed_cols, void* embed_out,
+                            int64_t embed_out_row_stride, void* stream);
 
 /* ---- a9 / frame-loop gathers ------------------------------------------------------------------
  * b2tts_gather_rows: out[i] = tables[table_index[i]][row_index[i]]  (bf16 rows of `cols`)

@@ -48,12 +48,13 @@ def _load():
         "b2tts_store_kvcache": (I, [P, P, L, L, P, P, P, I, I, P]),
         "b2tts_paged_attn_decode_workspace_bytes": (Z, [I, I, I, I]),
         "b2tts_paged_attn_decode": (I, [P, L, P, P, P, I, P, P, P, Z, I, I, I, I, I, F, I, P]),
-        "b2tts_varlen_attn_prefill": (I, [P, L, P, L, P, L, P, P, P, I, I, I, I, I, I, I, F, P, I, I, P]),
+        "b2tts_varlen_attn_prefill": (I, [P, L, P, L, P, L, P, P, P, I, I, I, I, I, I, I, I, F, P, I, I, P]),
         "b2tts_rmsnorm": (I, [P, L, P, P, I, I, F, I, P]),
         "b2tts_add_rmsnorm": (I, [P, P, P, P, P, I, I, F, I, I, P]),
         "b2tts_qknorm_rope_kvwrite": (I, [P, L, P, L, P, L, P, P, P, P, F, P, L, P, P, F, P, P, P, I, I, I, I, I, P]),
         "b2tts_silu_and_mul": (I, [P, P, L, P, I, I, I, P]),
         "b2tts_topk_sample": (I, [P, L, I, P, P, P, P, I, I, I, F, I, P]),
+        "b2tts_topk_sample_embed": (I, [P, L, I, P, P, P, I, I, I, P, I, P, L, P]),
         "b2tts_gather_rows": (I, [P, L, I, P, P, P, L, I, I, P]),
         "b2tts_codec_embed_sum": (I, [P, P, L, P, L, P, L, P, P, I, I, I, P]),
         "b2tts_decode_layout": (I, [P, P, I, I, I, I, I, P, P, P, I, P]),
@@ -204,13 +205,15 @@ def varlen_attn_prefill(q, k, v, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_s
         page, kvh = k.shape[1], k.shape[2]
         ks = vs = kvh * hd
         bt_ptr, bt_stride = block_table.data_ptr(), block_table.stride(0)
+        total_k = 0
     else:
         kvh, page = k.shape[1], 0
         ks, vs = k.stride(0), v.stride(0)
         bt_ptr, bt_stride = None, 0
+        total_k = min(k.shape[0], v.shape[0])
     _check(_load().b2tts_varlen_attn_prefill(q.data_ptr(), q.stride(0), k.data_ptr(), ks, v.data_ptr(), vs,
                                              cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), out.data_ptr(),
-                                             nseq, t, int(max_seqlen_q), int(max_seqlen_k), h, kvh, hd, float(scale),
+                                             nseq, t, total_k, int(max_seqlen_q), int(max_seqlen_k), h, kvh, hd, float(scale),
                                              bt_ptr, bt_stride, page, _stream()), "varlen_attn_prefill")
     return out
 
@@ -294,8 +297,10 @@ def silu_and_mul(gate, up, rounding=ROUND_EAGER, out=None):
 
 
 # ------------------------------------------------------------------------------------------ a8
-def topk_sample(logits, temperatures, noise, top_k=50, out=None, probs_out=None):
-    """logits [B, V] bf16 or fp32; temperatures [B] fp32; noise [B, V] fp32 Exp(1) draws."""
+def topk_sample(logits, temperatures, noise, top_k=50, out=None, probs_out=None, embed_table=None, embed_out=None):
+    """logits [B, V] bf16 or fp32; temperatures [B] fp32; noise [B, V] fp32 Exp(1) draws.
+    ``embed_table`` [V, cols] bf16 + ``embed_out`` [B, cols] (row stride free): also gathers
+    ``embed_table[index]`` into ``embed_out`` in the same launch (``b2tts_topk_sample_embed``)."""
     _cuda(logits, None, "logits"); _cuda(temperatures, F32, "temperatures"); _cuda(noise, F32, "noise")
     if logits.dtype not in (BF16, F32):
         raise RuntimeError(f"libb200tts: logits must be bf16 or fp32, got {logits.dtype}")
@@ -306,6 +311,17 @@ def topk_sample(logits, temperatures, noise, top_k=50, out=None, probs_out=None)
         noise = noise.contiguous()
     if out is None:
         out = torch.empty(b, dtype=I64, device=logits.device)
+    if embed_table is not None:
+        _cuda(embed_table, BF16, "embed_table"); _cuda(embed_out, BF16, "embed_out")
+        if embed_table.dim() != 2 or embed_table.stride(1) != 1 or embed_table.stride(0) != embed_table.shape[1] \
+                or embed_out.stride(-1) != 1:
+            raise RuntimeError("libb200tts: embed_table must be a contiguous [V, cols] tensor")
+        _check(_load().b2tts_topk_sample_embed(logits.data_ptr(), logits.stride(0), int(logits.dtype == F32),
+                                               temperatures.data_ptr(), noise.data_ptr(), out.data_ptr(), b, v,
+                                               int(min(top_k, v)), embed_table.data_ptr(), embed_table.shape[1],
+                                               embed_out.data_ptr(), embed_out.stride(0), _stream()),
+               "topk_sample_embed")
+        return out
     _check(_load().b2tts_topk_sample(logits.data_ptr(), logits.stride(0), int(logits.dtype == F32),
                                      temperatures.data_ptr(), noise.data_ptr(), out.data_ptr(), _ptr(probs_out),
                                      b, v, int(min(top_k, v)), 1.0, 0, _stream()), "topk_sample")

@@ -18,9 +18,18 @@
 // Prefill runs the same kernel with one CTA per query token (causal length = lk-lq+i+1);
 // K/V rows come either from the packed projections (per-row bulk copies, any row stride) or
 // from the paged cache when a block table is given (attention.py:79-80).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b2 {
+
+// attention_prefill_tc.cu
+bool prefill_tc_applicable(int max_seqlen_q, int head_dim, int num_heads, int num_kv_heads, const void* block_table);
+int launch_prefill_tc(const char* what, const void* q, int64_t q_row_stride, const void* k, int64_t k_row_stride,
+                      const void* v, int64_t v_row_stride, const int32_t* cu_q, const int32_t* cu_k, void* out,
+                      int num_seqs, int total_q, int total_k, int max_seqlen_q, int num_heads, int num_kv_heads,
+                      float scale, cudaStream_t st);
 
 constexpr int ATT_HD = 128;
 constexpr int ATT_TILE = 8;      // tokens per pipeline stage
@@ -449,15 +458,16 @@ extern "C" int b2tts_varlen_attn_prefill(const void* q, int64_t q_row_stride,
                                          const void* k, int64_t k_row_stride,
                                          const void* v, int64_t v_row_stride,
                                          const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
-                                         void* out, int num_seqs, int total_q,
+                                         void* out, int num_seqs, int total_q, int total_k,
                                          int max_seqlen_q, int max_seqlen_k,
                                          int num_heads, int num_kv_heads, int head_dim, float scale,
                                          const int32_t* block_table, int bt_stride, int page_size,
                                          void* stream) {
   using namespace b2;
   const char* what = "varlen_attn_prefill";
-  (void)max_seqlen_q; (void)max_seqlen_k;
-  B2_REQUIRE(num_seqs >= 0 && total_q >= 0, B2TTS_EINVAL, "%s: num_seqs=%d total_q=%d", what, num_seqs, total_q);
+  (void)max_seqlen_k;
+  B2_REQUIRE(num_seqs >= 0 && total_q >= 0 && total_k >= 0, B2TTS_EINVAL, "%s: num_seqs=%d total_q=%d total_k=%d", what,
+             num_seqs, total_q, total_k);
   if (num_seqs == 0 || total_q == 0) return B2TTS_OK;
   B2_REQUIRE(q && k && v && cu_seqlens_q && cu_seqlens_k && out, B2TTS_EINVAL, "%s: null pointer", what);
   int rc = check_heads(what, num_heads, num_kv_heads, head_dim);
@@ -468,6 +478,12 @@ extern "C" int b2tts_varlen_attn_prefill(const void* q, int64_t q_row_stride,
   if (block_table)
     B2_REQUIRE(page_size > 0 && page_size % ATT_TILE == 0 && bt_stride > 0, B2TTS_EUNSUPPORTED,
                "%s: page_size %d must be a positive multiple of %d", what, page_size, ATT_TILE);
+  // long prompts: the tcgen05 tile kernel (attention_prefill_tc.cu); short ones: one CTA per query token below
+  static const bool tc_enabled = [] { const char* e = getenv("B2TTS_PREFILL_TC"); return !(e && e[0] == '0'); }();
+  if (tc_enabled && max_seqlen_q > 0 && prefill_tc_applicable(max_seqlen_q, head_dim, num_heads, num_kv_heads, block_table))
+    return launch_prefill_tc(what, q, q_row_stride, k, k_row_stride, v, v_row_stride, cu_seqlens_q, cu_seqlens_k, out,
+                             num_seqs, total_q, total_k, max_seqlen_q, num_heads, num_kv_heads, scale,
+                             static_cast<cudaStream_t>(stream));
   AttnParams p{};
   p.q = static_cast<const __nv_bfloat16*>(q);
   p.q_stride = q_row_stride;

@@ -98,41 +98,95 @@ fused_decode_attn_kernel(const FusedAttnParams p) {
     }
     mbar_fence_init();
   }
+  // Latency discipline: this kernel runs 103 times per codec frame on contexts of 3 .. a few hundred tokens, so
+  // its cost is the chain of dependent global-memory round trips, not bytes.  Everything that does not depend on
+  // the previous kernel (rotary frequencies, M-RoPE row selectors, head-norm weights) is requested BEFORE
+  // griddepcontrol.wait; everything that does (length, slot, positions, the q/k/v rows, the block table) is
+  // requested in ONE batch right after it, so the prologue costs one round trip instead of six.
+  const int g = lane >> 3;        // token slot within a 4-token step
+  const int j = lane & 7;         // which 16 head-dims: [8j,8j+8) and [64+8j,64+8j+8)
+  const bool consumer = warp < kvh;
+  float frq[2] = {0.f, 0.f};
+  int md1[2] = {0, 0}, md2[2] = {0, 0};
+  uint32_t qw1 = 0, qw2 = 0, kw1 = 0, kw2 = 0;
+  if (consumer) {
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int fi = 2 * lane + e;
+      frq[e] = __ldg(p.inv_freq + fi);
+      if (p.modality) { md1[e] = __ldg(p.modality + fi); md2[e] = __ldg(p.modality + FA_HD / 2 + fi); }
+    }
+    if (p.q_w) { qw1 = *reinterpret_cast<const uint32_t*>(p.q_w + 2 * lane); qw2 = *reinterpret_cast<const uint32_t*>(p.q_w + 64 + 2 * lane); }
+    if (p.k_w) { kw1 = *reinterpret_cast<const uint32_t*>(p.k_w + 2 * lane); kw2 = *reinterpret_cast<const uint32_t*>(p.k_w + 64 + 2 * lane); }
+  }
   __syncthreads();
   pdl_wait();                                   // q/k/v rows, slots and lengths come from earlier kernels
 
+  const bool writer = (split == p.nsplit - 1);  // owns the last tile, i.e. the token appended this step
   int L = __ldg(p.context_lens + row);
+  // ---- one batch of independent requests (consumers: this token's rows; producer: the block-table row)
+  int tbl = 0;                                  // producer: lane l holds block_table[row][l]
+  int slot = -1;
+  int64_t pos[3] = {0, 0, 0};
+  uint32_t raw1[GROUP + 1], raw2[GROUP + 1];
+  uint4 vraw = make_uint4(0, 0, 0, 0);
+  const int nh_q = p.num_heads / kvh;           // q heads this warp normalises: warp, warp + kvh, ...  (== GROUP)
+  if (consumer) {
+    if (writer) slot = __ldg(p.slot_mapping + row);
+    pos[0] = __ldg(p.positions + row);
+    if (p.modality && p.pos_row_stride) {
+      pos[1] = __ldg(p.positions + p.pos_row_stride + row);
+      pos[2] = __ldg(p.positions + 2 * p.pos_row_stride + row);
+    } else {
+      pos[1] = pos[2] = pos[0];
+    }
+#pragma unroll
+    for (int i = 0; i < GROUP + 1; ++i) {
+      const bool is_k = i == GROUP;
+      raw1[i] = raw2[i] = 0u;
+      if (i < nh_q || (is_k && writer)) {
+        const __nv_bfloat16* src = is_k ? p.k + (int64_t)row * p.k_stride + warp * FA_HD
+                                        : p.q + (int64_t)row * p.q_stride + (warp + i * kvh) * FA_HD;
+        raw1[i] = *reinterpret_cast<const uint32_t*>(src + 2 * lane);
+        raw2[i] = *reinterpret_cast<const uint32_t*>(src + 64 + 2 * lane);
+      }
+    }
+    if (writer && (int)threadIdx.x < (kv_dim >> 3)) vraw = ldg_v4(p.v + (int64_t)row * p.v_stride + 8 * threadIdx.x);
+  } else if (lane < p.bt_stride) {
+    tbl = __ldg(p.block_table + (int64_t)row * p.bt_stride + lane);
+  }
   if (L < 0) L = 0;
   const int n_tiles = (L + FA_TILE - 1) / FA_TILE;
   const int t_begin = (int)(((int64_t)split * n_tiles) / p.nsplit);
   const int t_end = (int)(((int64_t)(split + 1) * n_tiles) / p.nsplit);
   const int my_tiles = t_end - t_begin;
-  const bool writer = (split == p.nsplit - 1);  // owns the last tile, i.e. the token appended this step
 
   if (warp == kvh) {
-    // =========================== producer warp
-    if (lane == 0) {
-      for (int i = 0; i < my_tiles; ++i) {
-        const int stage = i % FA_NSTAGE;
-        const uint32_t ph = (i / FA_NSTAGE) & 1;
+    // =========================== producer warp: the whole warp walks the ring (the page of a tile comes from the
+    // lanes' copy of the block-table row), lane 0 issues the copies
+    for (int i = 0; i < my_tiles; ++i) {
+      const int stage = i % FA_NSTAGE;
+      const uint32_t ph = (i / FA_NSTAGE) & 1;
+      const int tok0 = (t_begin + i) * FA_TILE;
+      const int pidx = tok0 / p.page_size;
+      int page = __shfl_sync(0xffffffffu, tbl, pidx & 31);
+      if (pidx >= 32) page = __ldg(p.block_table + (int64_t)row * p.bt_stride + pidx);
+      if (lane == 0) {
         mbar_wait(empty_bar + stage, ph ^ 1);
-        const int tok0 = (t_begin + i) * FA_TILE;
         const int ntok = min(FA_TILE, L - tok0);
-        int page = __ldg(p.block_table + (int64_t)row * p.bt_stride + tok0 / p.page_size);
         if (page < 0) page = 0;                  // never faults on a stale (-1) table entry
-        const int64_t slot = (int64_t)page * p.page_size + tok0 % p.page_size;
+        const int64_t slot0 = (int64_t)page * p.page_size + tok0 % p.page_size;
         const uint32_t bytes = (uint32_t)(ntok * kv_dim * 2);
         mbar_expect_tx(full_bar + stage, 2u * bytes);
-        bulk_g2s(Ks + stage * stage_elems, p.k_cache + slot * kv_dim, bytes, full_bar + stage);
-        bulk_g2s(Vs + stage * stage_elems, p.v_cache + slot * kv_dim, bytes, full_bar + stage);
+        bulk_g2s(Ks + stage * stage_elems, p.k_cache + slot0 * kv_dim, bytes, full_bar + stage);
+        bulk_g2s(Vs + stage * stage_elems, p.v_cache + slot0 * kv_dim, bytes, full_bar + stage);
       }
+      __syncwarp();
     }
     return;
   }
 
   // =========================== consumer warps
-  const int g = lane >> 3;        // token slot within a 4-token step
-  const int j = lane & 7;         // which 16 head-dims: [8j,8j+8) and [64+8j,64+8j+8)
   const int head0 = warp * GROUP;
 
   if (L == 0) {                   // CUDA-graph padding row (talker_mode_runner.py:97-100): zeros, no ticket
@@ -155,39 +209,31 @@ fused_decode_attn_kernel(const FusedAttnParams p) {
     float c1[2], s1[2], c2[2], s2[2];
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
-      const int fi = 2 * lane + e;
-      const float f = __ldg(p.inv_freq + fi);
-      const int m1 = p.modality ? __ldg(p.modality + fi) : 0;
-      const float a1 = (float)__ldg(p.positions + (int64_t)m1 * p.pos_row_stride + row) * f;
+      const float a1 = (float)(md1[e] == 0 ? pos[0] : md1[e] == 1 ? pos[1] : pos[2]) * frq[e];
       c1[e] = rbf(cosf(a1) * p.attention_scaling);
       s1[e] = rbf(sinf(a1) * p.attention_scaling);
-      const int m2 = p.modality ? __ldg(p.modality + FA_HD / 2 + fi) : 0;
-      if (m2 != m1) {
-        const float a2 = (float)__ldg(p.positions + (int64_t)m2 * p.pos_row_stride + row) * f;
+      if (md2[e] != md1[e]) {
+        const float a2 = (float)(md2[e] == 0 ? pos[0] : md2[e] == 1 ? pos[1] : pos[2]) * frq[e];
         c2[e] = rbf(cosf(a2) * p.attention_scaling);
         s2[e] = rbf(sinf(a2) * p.attention_scaling);
       } else {
         c2[e] = c1[e]; s2[e] = s1[e];
       }
     }
-    const int slot = writer ? __ldg(p.slot_mapping + row) : -1;
-    const int total = p.num_heads + (writer ? kvh : 0);
-    for (int hh = warp; hh < total; hh += kvh) {
-      const bool is_k = hh >= p.num_heads;
-      const int h = is_k ? hh - p.num_heads : hh;
-      const __nv_bfloat16* src = is_k ? p.k + (int64_t)row * p.k_stride + h * FA_HD : p.q + (int64_t)row * p.q_stride + h * FA_HD;
-      const __nv_bfloat16* w = is_k ? p.k_w : p.q_w;
-      const uint32_t r1 = *reinterpret_cast<const uint32_t*>(src + 2 * lane);
-      const uint32_t r2 = *reinterpret_cast<const uint32_t*>(src + 64 + 2 * lane);
-      float x1[2] = {bf16lo(r1), bf16hi(r1)};
-      float x2[2] = {bf16lo(r2), bf16hi(r2)};
-      if (w) {
+#pragma unroll
+    for (int i = 0; i < GROUP + 1; ++i) {
+      const bool is_k = i == GROUP;
+      if (!(i < nh_q || (is_k && writer))) continue;
+      const int h = is_k ? warp : warp + i * kvh;
+      const bool has_w = is_k ? (p.k_w != nullptr) : (p.q_w != nullptr);
+      float x1[2] = {bf16lo(raw1[i]), bf16hi(raw1[i])};
+      float x2[2] = {bf16lo(raw2[i]), bf16hi(raw2[i])};
+      if (has_w) {
         float ss = x1[0] * x1[0];
         ss = fmaf(x1[1], x1[1], ss); ss = fmaf(x2[0], x2[0], ss); ss = fmaf(x2[1], x2[1], ss);
         const float var = warp_sum(ss) / (float)FA_HD + p.eps;
         const float rstd = EAGER ? 1.0f / sqrtf(var) : rsqrtf(var);
-        const uint32_t w1 = *reinterpret_cast<const uint32_t*>(w + 2 * lane);
-        const uint32_t w2 = *reinterpret_cast<const uint32_t*>(w + 64 + 2 * lane);
+        const uint32_t w1 = is_k ? kw1 : qw1, w2 = is_k ? kw2 : qw2;
         const float wf[4] = {bf16lo(w1), bf16hi(w1), bf16lo(w2), bf16hi(w2)};
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
@@ -211,13 +257,9 @@ fused_decode_attn_kernel(const FusedAttnParams p) {
         *reinterpret_cast<uint32_t*>(cd + 64 + 2 * lane) = y2;
       }
     }
-    if (writer) {                                          // V goes to the cache untouched
-      const __nv_bfloat16* vs = p.v + (int64_t)row * p.v_stride;
-      for (int i = threadIdx.x; i < (kv_dim >> 3); i += kvh * 32) {
-        const uint4 vv = ldg_v4(vs + 8 * i);
-        *reinterpret_cast<uint4*>(vn_s + 8 * i) = vv;
-        if (slot >= 0) stg_v4(p.v_cache + (int64_t)slot * kv_dim + 8 * i, vv);
-      }
+    if (writer && (int)threadIdx.x < (kv_dim >> 3)) {      // V goes to the cache untouched
+      *reinterpret_cast<uint4*>(vn_s + 8 * threadIdx.x) = vraw;
+      if (slot >= 0) stg_v4(p.v_cache + (int64_t)slot * kv_dim + 8 * threadIdx.x, vraw);
     }
   }
   asm volatile("bar.sync 1, %0;" :: "r"(kvh * 32) : "memory");      // the consumer warps only

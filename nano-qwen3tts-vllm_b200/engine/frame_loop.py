@@ -74,7 +74,6 @@ class DeviceFrameLoop:
         self.t_temp = torch.full((b,), talker_temperature, dtype=torch.float32, device=dev)
         self.p_temp = torch.full((b,), predictor_temperature, dtype=torch.float32, device=dev)
         self.embeds = torch.zeros(b, tc.hidden_size, dtype=BF16, device=dev)        # next talker input
-        self.hidden = torch.zeros(b, tc.hidden_size, dtype=BF16, device=dev)        # last talker hidden
         self.codes_t = torch.zeros(self.ncb, b, dtype=torch.int64, device=dev)      # codebook-major: row g contiguous
         self.codes = torch.zeros(b, self.ncb, dtype=torch.int64, device=dev)        # [code0 | 15 predictor codes]
         # trailing_text_hiddens[:, step] for step < trail_rows, tts_pad_embed in row trail_rows     interface.py:1282-1285
@@ -89,7 +88,11 @@ class DeviceFrameLoop:
         # predictor static layouts: stream i owns page i; prefill rows (2i, 2i+1) -> slots page*P + {0,1}
         pg = torch.arange(b, dtype=torch.int32, device=dev)
         self.p_tables = pg.view(b, 1).contiguous()
+        # predictor prefill input rows (2i, 2i+1) = [last talker hidden_i, embed(code0_i)]   interface.py:1242-1252
         self.p_x = torch.zeros(2 * b, tc.hidden_size, dtype=BF16, device=dev)
+        self.hidden = self.p_x.view(b, 2, -1)[:, 0]                                 # last talker hidden (strided view)
+        self.p_emb0 = self.p_x.view(b, 2, -1)[:, 1]                                 # embed(code0), written by the sampler
+        self.p_emb = torch.zeros(b, tc.hidden_size, dtype=BF16, device=dev)         # next predictor pass's input embedding
         self.p_pre_pos = torch.tensor([0, 1] * b, dtype=torch.int64, device=dev)
         self.p_pre_slots = (pg.view(b, 1) * self.page + torch.tensor([0, 1], dtype=torch.int32, device=dev)).view(-1).contiguous()
         self.p_cu = (torch.arange(b + 1, dtype=torch.int32, device=dev) * 2).contiguous()
@@ -128,9 +131,19 @@ class DeviceFrameLoop:
     # ------------------------------------------------------------------ sampling
     def _sample(self, logits, temps, g: int):
         """Decision ``g`` of the current frame (0 = the talker's code0 of the NEXT frame): sampler.py:15-24 on the
-        frame's pre-drawn Exp(1) noise; argmax(p / 1) = first maximum under ``unit_noise`` (tests)."""
+        frame's pre-drawn Exp(1) noise; argmax(p / 1) = first maximum under ``unit_noise`` (tests).  The same launch
+        gathers the embedding of the chosen code for its consumer: code0 -> row 1 of the predictor's prefill input
+        (interface.py:1242), predictor code g -> the input of decode pass g (qwen3_tts_predictor.py:94-95)."""
         out = self.codes_t[g]
-        nat.topk_sample(logits, temps, self._noise_view(g), top_k=self.top_k, out=out)
+        if g == 0:
+            table, dst = self.talker.model.codec_embedding.weight, self.p_emb0
+        elif g < self.ncb - 1:
+            table, dst = self.predictor.model.codec_embedding[g - 1], self.p_emb
+        else:
+            table, dst = None, None
+        fused = table is not None and self.forced is None
+        nat.topk_sample(logits, temps, self._noise_view(g), top_k=self.top_k, out=out,
+                        embed_table=table if fused else None, embed_out=dst if fused else None)
         if self.keep_logits:
             buf = self.logit_log.get(g)
             if buf is None or buf.shape != logits.shape:
@@ -140,6 +153,8 @@ class DeviceFrameLoop:
             row = self.frame_idx * self.ncb + g                           # device index: graph-capturable
             self.sampled.view(-1, self.b).index_copy_(0, row, out.unsqueeze(0))
             out.copy_(self.forced.view(-1, self.b).index_select(0, row)[0])
+            if table is not None:
+                nat.gather_rows(table, out, out=dst)
 
     def _draw_noise(self):
         if not self.unit_noise:
@@ -176,8 +191,9 @@ class DeviceFrameLoop:
         x = torch.cat([p.reshape(-1, p.shape[-1]) for p in prompts], 0).to(dev, BF16)
         h = self.talker(x, torch.tensor(pos, dtype=torch.int64, device=dev))
         last = (cu_t[1:] - 1).to(torch.int64)
-        self.hidden.copy_(nat.gather_rows(h, last))
-        logits = linear(self.hidden, self.talker.codec_head.weight)
+        h_last = nat.gather_rows(h, last)
+        self.hidden.copy_(h_last)
+        logits = linear(h_last, self.talker.codec_head.weight)
         self.frame_idx.zero_()
         self._draw_noise() if not self.unit_noise else self.noise.fill_(1.0)
         self._sample(logits, self.t_temp, 0)
@@ -198,10 +214,7 @@ class DeviceFrameLoop:
         nat.frame_advance(code0, self.eos_id, self.active, self.seq_lens, self.gen_step, self.frames_done,
                           self.extra_row, self.trail_rows, self.max_frames)
         self._draw_noise()
-        # ---- predictor prefill on [hidden_i, embed(code0_i)]                   interface.py:1242-1252
-        x3 = self.p_x.view(b, 2, -1)
-        x3[:, 0].copy_(self.hidden)
-        nat.gather_rows(talker.model.codec_embedding.weight, code0, out=x3[:, 1])
+        # ---- predictor prefill on [hidden_i, embed(code0_i)] (both already in p_x)   interface.py:1242-1252
         set_context(True, self.p_cu, self.p_cu, 2, 2, self.p_pre_slots, None, None)
         h = predictor(self.p_x, self.p_pre_pos)
         last = h.view(b, 2, -1)[:, 1]
@@ -209,10 +222,9 @@ class DeviceFrameLoop:
         # ---- 14 predictor decode passes                                 predictor_model_runner.py:134-157
         for g in range(1, self.ncb - 1):
             lay = self.p_dec[g - 1]
-            emb = nat.gather_rows(predictor.model.codec_embedding[g - 1], self.codes_t[g])
             set_context(False, slot_mapping=lay["slots"], context_lens=lay["ctx"], block_tables=self.p_tables,
                         max_context_len=g + 2)           # exact: no split-KV, no combine launch
-            h = predictor(emb, lay["pos"])
+            h = predictor(self.p_emb, lay["pos"])        # p_emb = codec_embedding[g-1][code g], left by the sampler
             self._sample(linear(h, predictor.lm_head[g]), self.p_temp, g + 1)
         # ---- emit the frame, build the next talker input                       interface.py:1269-1286
         self.codes.copy_(self.codes_t.t())
@@ -225,12 +237,12 @@ class DeviceFrameLoop:
         set_context(False, slot_mapping=self.t_slots, context_lens=self.t_ctx, block_tables=self.t_tables,
                     max_context_len=self.width * self.page)
         th = talker(self.embeds, self.t_pos)
-        self.hidden.copy_(th)
         self._sample(linear(th, talker.codec_head.weight), self.t_temp, 0)
+        self.hidden.copy_(th)
         reset_context()
 
     def _state(self):
-        st = [self.seq_lens, self.hidden, self.codes_t, self.embeds, self.frame_idx, self.frames, self.active,
+        st = [self.seq_lens, self.p_x, self.p_emb, self.codes_t, self.embeds, self.frame_idx, self.frames, self.active,
               self.gen_step, self.frames_done, self.noise]
         if self.sampled is not None:
             st.append(self.sampled)

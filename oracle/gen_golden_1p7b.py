@@ -95,8 +95,44 @@ def generate(b: int, nframes: int, fused: bool, tw, pw, td, pd, log=print):
     return dict(frames=frames, top1=t1.view(nframes, 16, b), top2=t2.view(nframes, 16, b), rows=rows,
                 talker_logits=torch.stack(t_logits), predictor_logits=torch.stack(p_logits),
                 meta=dict(model="1.7B", streams=b, frames=nframes, prompt_len=PROMPT_LEN, weight_seed=1234,
-                          rounding="fused" if fused else "eager", torch=torch.__version__,
+                          rounding="fused" if fused else "eager", torch=str(torch.__version__),
                           generator="oracle/gen_golden_1p7b.py", seconds=round(time.time() - calls["t0"], 1)))
+
+
+def fp32_logits(b: int, gold: dict, tw, pw, td, pd, nframes: int = 4):
+    """The same model evaluated WITHOUT bf16 rounding points: weights upcast to fp32, every op in fp32, fed the
+    golden run's codes (teacher-forced), for the decisions whose bf16 logits the golden file keeps.  This is the
+    yardstick for "how far may two correct bf16 pipelines be from each other": the CPU oracle itself (= the
+    reference's own CPU path, bit for bit) sits ~4 % of max|logit| away from it after 28 layers, so the north-star
+    2e-2 bound holds per op / per layer (tests/test_gpu_ops.py, test_gpu_models.py) but cannot hold for whole-stack
+    logits, for ANY bf16 implementation including the reference's."""
+    old = OM.BF16, O.BF16
+    OM.BF16 = O.BF16 = torch.float32
+    try:
+        prompts, pad = prompts_for(b, td.hidden_size)
+        pages = (PROMPT_LEN + nframes + 1 + td.page_size - 1) // td.page_size
+        tw32 = {k: v.float() for k, v in tw.items()}
+        pw32 = {k: v.float() for k, v in pw.items()}
+        talker = OM.Talker(td, tw32, b * pages)
+        predictor = OM.Predictor(pd, pw32, b, td.hidden_size)
+        frames = gold["frames"].long()                               # [F, B, 16]
+        rows = gold["rows"]
+        t_logits, p_logits, calls = [], [], {"n": 0}
+
+        def forced(logits, temps):
+            n = calls["n"]
+            calls["n"] += 1
+            if logits.shape[-1] == td.vocab_size:
+                t_logits.append(logits[rows].clone())
+            elif n in (1, 2, 15):
+                p_logits.append(logits[rows].clone())
+            f, c = divmod(n, 16)
+            return frames[min(f, frames.shape[0] - 1), :, c].clone()
+        with torch.inference_mode():
+            OM.run_frames(talker, predictor, [p.float() for p in prompts], nframes - 1, pad.float(), forced)
+        return dict(talker_logits_fp32=torch.stack(t_logits[:4]), predictor_logits_fp32=torch.stack(p_logits))
+    finally:
+        OM.BF16, O.BF16 = old
 
 
 def main():
@@ -104,14 +140,28 @@ def main():
     ap.add_argument("--only", default="b1,b8,b64")
     ap.add_argument("--modes", default="eager,fused")
     ap.add_argument("--out", default=os.path.join(ROOT, "tests", "golden"))
+    ap.add_argument("--truth-only", action="store_true",
+                    help="add the fp32 logits to EXISTING golden files instead of regenerating the frames")
     a = ap.parse_args()
     torch.set_num_threads(os.cpu_count() or 1)
     td, pd = dims_1p7b()
     tw, pw = OM.synthetic_weights(td, pd, seed=1234)
+    if a.truth_only:
+        for name in a.only.split(","):
+            for mode in a.modes.split(","):
+                path = os.path.join(a.out, f"frames_1p7b_{name}_{mode}.pt")
+                gold = torch.load(path)
+                gold.update(fp32_logits(CONFIGS[name][0], gold, tw, pw, td, pd))
+                torch.save(gold, path)
+                e = (gold["talker_logits"].float() - gold["talker_logits_fp32"]).abs().amax((1, 2)) / \
+                    gold["talker_logits_fp32"].abs().amax((1, 2))
+                print(f"{path}: bf16 oracle vs fp32, talker logits rel err per step {[round(float(x), 4) for x in e]}", flush=True)
+        return
     for name in a.only.split(","):
         b, nframes = CONFIGS[name]
         for mode in a.modes.split(","):
             out = generate(b, nframes, mode == "fused", tw, pw, td, pd)
+            out.update(fp32_logits(b, out, tw, pw, td, pd))
             path = os.path.join(a.out, f"frames_1p7b_{name}_{mode}.pt")
             torch.save(out, path)
             print(f"wrote {path} ({os.path.getsize(path) / 1e6:.2f} MB, {out['meta']['seconds']} s)", flush=True)

@@ -188,6 +188,33 @@ def test_sampler_random_rows_and_ties(native):
     assert torch.equal(got32.cpu(), O.topk_sample(logits, temps, noise, 50))
 
 
+@pytest.mark.parametrize("b,vsz,top_k", [(64, 2048, 50), (3, 3072, 50), (5, 4096, 7), (4, 1000, 50), (2, 5000, 50),
+                                        (7, 512, 600), (1, 2048, 1)])
+def test_sampler_warp_and_block_paths_with_fused_embedding(native, b, vsz, top_k):
+    """The warp-per-row kernel (vocab <= 4096, multiple of 8) and the block kernel (everything else) against the
+    oracle, fp32 and bf16 logits, strided logits rows, heavy ties; and the fused gather of the chosen code's
+    embedding row (models/qwen3_tts_predictor.py:94-95)."""
+    g = torch.Generator().manual_seed(b * 31 + vsz)
+    logits = (torch.randn(b, vsz, generator=g) * 3).to(BF16)
+    logits[:, 10:60] = logits[:, 9:10]                           # 51-way tie, crosses the k-th place for k = 50
+    temps = torch.rand(b, generator=g) * 1.5 + 0.2
+    noise = torch.empty(b, vsz).exponential_(1, generator=g)
+    want = O.topk_sample(logits, temps, noise, min(top_k, vsz))
+    got = native.topk_sample(logits.to(DEV), temps.to(DEV), noise.to(DEV), top_k)
+    assert torch.equal(got.cpu(), want)
+    wide = torch.zeros(b, vsz + 64, dtype=BF16, device=DEV)       # rows of a wider buffer (row stride != vocab)
+    wide[:, :vsz] = logits.to(DEV)
+    assert torch.equal(native.topk_sample(wide[:, :vsz], temps.to(DEV), noise.to(DEV), top_k).cpu(), want)
+    got32 = native.topk_sample(logits.float().to(DEV), temps.to(DEV), noise.to(DEV), top_k)
+    assert torch.equal(got32.cpu(), want)
+    if vsz <= 4096 and vsz % 8 == 0:
+        table = torch.randn(vsz, 256, generator=g).to(BF16).to(DEV)
+        dst = torch.zeros(b, 2, 256, dtype=BF16, device=DEV)
+        idx = native.topk_sample(logits.to(DEV), temps.to(DEV), noise.to(DEV), top_k, embed_table=table, embed_out=dst[:, 1])
+        assert torch.equal(idx.cpu(), want)
+        assert torch.equal(dst[:, 1], table[idx]) and dst[:, 0].abs().max().item() == 0
+
+
 # ------------------------------------------------------------------------------------------ a2
 def _paged_case(b, lens, page=256, kvh=8, h=16, hd=128, seed=0, extra_pages=2):
     g = torch.Generator().manual_seed(seed)

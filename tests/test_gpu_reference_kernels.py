@@ -171,8 +171,10 @@ def test_rope_bit_exact_vs_reference_ops_on_cuda(native, mrope):
 def test_fused_qknorm_rope_kv_slots_vs_reference_ops_on_cuda(native, rounding):
     """q_norm / k_norm + RoPE + KV write (models/qwen3_tts_share.py:96-106) against the same ops in torch on CUDA.
     The rotation is bit-exact (test above); the head norm's mean over 128 values is summed in a different order than
-    torch's CUDA reduction, so rstd can differ in its last fp32 bit and a bf16 rounding can flip: at most 1 bf16 ulp
-    on a tiny share of the elements, everything else byte-identical."""
+    torch's CUDA reduction, so rstd can differ in its last fp32 bit and the bf16 rounding of a NORMALISED value can
+    flip by one ulp; the rotation then mixes that value into two outputs (x*cos + rotate_half(x)*sin), so an affected
+    output moves by at most ~2 ulp of the head's largest element.  A tiny share of the elements, everything else
+    byte-identical."""
     g = torch.Generator(device="cuda").manual_seed(12 + rounding)
     n = 200
     q = torch.randn(n, H, HD, device="cuda", generator=g).to(BF16)
@@ -195,6 +197,8 @@ def test_fused_qknorm_rope_kv_slots_vs_reference_ops_on_cuda(native, rounding):
         frac = ne.float().mean().item()
         assert frac <= 5e-3, f"{name}: {frac:.3%} of the elements differ"
         if ne.any():
-            ulp = torch.exp2(torch.floor(torch.log2(want.float().abs().clamp_min(1e-30))) - 7)
-            assert ((got.float() - want.float()).abs()[ne] <= 1.01 * ulp[ne]).all(), f"{name}: more than 1 bf16 ulp"
+            head_max = want.float().abs().amax(dim=-1, keepdim=True).expand_as(want)
+            ulp = torch.exp2(torch.floor(torch.log2(head_max.clamp_min(1e-30))) - 7)
+            worst = ((got.float() - want.float()).abs()[ne] / ulp[ne]).max().item()
+            assert worst <= 2.01, f"{name}: {worst:.2f} ulp of the head maximum"
     assert torch.equal(vc.view(-1, KVH, HD)[:n].view(torch.int16), v.view(torch.int16))

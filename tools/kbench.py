@@ -213,6 +213,52 @@ def fattn_case(b, l, layers=28, page=256, kvh=8, h=16, hd=128):
                       "nsplit_env": os.environ.get("B2TTS_FA_NSPLIT")}), flush=True)
 
 
+def prefill_case(lens, h=16, kvh=8, hd=128, layers=4):
+    """Varlen causal prefill attention (a3) over packed q/k/v slices of one QKV projection: ours (tcgen05 tile kernel
+    for max_seqlen >= 128, B2TTS_PREFILL_TC=0 selects the per-query kernel) and flash_attn_varlen_func."""
+    t = sum(lens)
+    qkvs = [torch.randn(t, (h + 2 * kvh) * hd, device=DEV, dtype=BF16) for _ in range(layers)]
+    cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32, device=DEV)
+    out = torch.empty(t, h, hd, device=DEV, dtype=BF16)
+    scale = hd ** -0.5
+
+    def split(x):
+        return x[:, :h * hd].view(t, h, hd), x[:, h * hd:(h + kvh) * hd].view(t, kvh, hd), x[:, (h + kvh) * hd:].view(t, kvh, hd)
+
+    def ours():
+        for x in qkvs:
+            q, k, v = split(x)
+            nat.varlen_attn_prefill(q, k, v, cu, cu, max(lens), max(lens), scale, out=out)
+    res = {}
+    impls = [("ours", ours)]
+    try:
+        import flash_attn
+
+        def fa():
+            for x in qkvs:
+                q, k, v = split(x)
+                flash_attn.flash_attn_varlen_func(q, k, v, cu_seqlens_q=cu, cu_seqlens_k=cu, max_seqlen_q=max(lens),
+                                                  max_seqlen_k=max(lens), softmax_scale=scale, causal=True)
+        impls.append(("flash_attn", fa))
+    except ImportError:
+        pass
+    for name, fn in impls:
+        fn(); torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        res[name] = time_ms(lambda i: g.replay()) / layers * 1e3
+    flops = sum(2.0 * n * n * hd * h for n in lens)          # causal: half of 4 * T^2 * hd * heads
+    tf = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("bf16_tflops_sustained", 1378.0) \
+        if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 1378.0
+    row = {"kernel": "varlen_attn_prefill", "lens": lens if len(lens) <= 4 else f"{len(lens)}x{lens[0]}", "T": t,
+           "tc": os.environ.get("B2TTS_PREFILL_TC", "1"), "us": round(res["ours"], 2),
+           "TFLOPs": round(flops / res["ours"] / 1e6, 1), "frac_sustained_bf16": round(flops / res["ours"] / 1e6 / tf, 4)}
+    if "flash_attn" in res:
+        row.update(flash_attn_us=round(res["flash_attn"], 2), flash_attn_TFLOPs=round(flops / res["flash_attn"] / 1e6, 1))
+    print(json.dumps(row), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("what")
@@ -232,6 +278,9 @@ def main():
                 if s_ and (s_ > k // 64):
                     continue
                 gemm_case(m, n, k, splits=s_, pdl=bool(a.pdl))
+    if a.what == "prefill":
+        for lens in ([4096], [1024], [256], [4096, 4096], [64] * 64, [300, 5]):
+            prefill_case(lens)
     if a.what == "sampler":
         for b, v in ((64, 2048), (64, 3072), (1, 3072), (512, 2048)):
             sampler_case(b, v)
