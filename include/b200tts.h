@@ -218,8 +218,8 @@ B2TTS_API int b2tts_frame_advance(const int64_t* code0, int eos_id, int32_t* act
  *   (q/k/v and gate/up as ONE GEMM each over a merged weight: models/qwen3_tts_share.py:85-87, 126-134),
  *   nn.Linear small_to_mtp_projection / lm_head[g]                 models/qwen3_tts_predictor.py:54-61,
  *   ParallelLMHead's F.linear                                      layers/embed_head.py:61
- * y[m, n] = x[m, k] @ W[n, k]^T, bf16 in/out, fp32 accumulate in TMEM, 1 <= m <= 128, n % 128 == 0,
- * k % 64 == 0.  W is passed PRE-PACKED: b2tts_gemm_pack_weight() re-tiles a row-major [n, k] weight
+ * y[m, n] = x[m, k] @ W[n, k]^T, bf16 in/out, fp32 accumulate in TMEM, m >= 1 (rows beyond 128 run as
+ * 128-row chunks inside the same launch), n % 128 == 0, k % 64 == 0.  W is passed PRE-PACKED: b2tts_gemm_pack_weight() re-tiles a row-major [n, k] weight
  * once at load time into [n/128][k/64] tiles of 16 KiB (the K-major SWIZZLE_128B shared-memory image
  * of a UMMA operand), b2tts_gemm_packed_bytes(n, k) bytes.  B2TTS_PACK_GATE_UP packs a merged
  * [gate; up] weight (n = 2 * intermediate) so that every 8 consecutive tile rows hold 4 gate features
@@ -267,6 +267,18 @@ B2TTS_API int    b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const
                                       int epilogue, int rounding, int splits, int pdl,
                                       const void* norm_weight, const float* ssq_in, int ssq_in_slots, float eps,
                                       float* ssq_out, void* stream);
+
+/* b2tts_gemm_norm_bf16 plus an L2 prefetch of the NEXT projection's packed weights (prefetch_next, prefetch_bytes =
+ * b2tts_gemm_packed_bytes of that weight, or NULL / 0): weights do not depend on activations, and a decode step is a
+ * chain of latency-bound launches during which HBM idles most of the time - every CTA pulls its slice of the next
+ * weight image into the 126 MB L2 (cp.async.bulk.prefetch.L2) so the next launch streams from L2 while HBM already
+ * fetches the launch after it.  Results are identical to b2tts_gemm_norm_bf16. */
+B2TTS_API int    b2tts_gemm_prefetch_bf16(const void* x, int64_t x_row_stride, const void* w_packed,
+                                          const void* bias, const void* residual, int64_t residual_row_stride,
+                                          void* out, int64_t out_row_stride, int m, int n, int k,
+                                          int epilogue, int rounding, int splits, int pdl,
+                                          const void* norm_weight, const float* ssq_in, int ssq_in_slots, float eps,
+                                          float* ssq_out, const void* prefetch_next, size_t prefetch_bytes, void* stream);
 
 /* ---- a7 x 4 in one launch: the persistent GEMM chain of the decoder layer ------------------------------------
  * replaces the four dependent projections between two attention calls

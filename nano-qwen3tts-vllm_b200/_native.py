@@ -68,6 +68,7 @@ def _load():
         "b2tts_fused_decode_attn": (I, [P, L, P, L, P, L, P, P, F, P, L, P, P, F, P, P, P, P, I, P, P, P, Z,
                                         I, I, I, I, I, F, I, I, I, P]),
         "b2tts_gemm_norm_bf16": (I, [P, L, P, P, P, L, P, L, I, I, I, I, I, I, I, P, P, I, F, P, P]),
+        "b2tts_gemm_prefetch_bf16": (I, [P, L, P, P, P, L, P, L, I, I, I, I, I, I, I, P, P, I, F, P, P, Z, P]),
         "b2tts_gemm_chain_ssq_slots": (I, [I]),
         "b2tts_gemm_chain_workspace_bytes": (Z, [I, P, P, I]),
         "b2tts_gemm_chain": (I, [P, I, I, F, I, P, Z, I, P]),
@@ -394,7 +395,8 @@ def frame_advance(code0, eos_id, active, seq_lens, gen_step, frames_done, extra_
 # ------------------------------------------------------------------------------------------ a7
 GEMM_BIAS, GEMM_RESIDUAL, GEMM_SILU_MUL = 0, 1, 2
 PACK_PLAIN, PACK_GATE_UP = 0, 1
-GEMM_MAX_M = 128
+GEMM_MAX_M = 1 << 16        # any batch: rows beyond 128 run as 128-row chunks of the same kernel (gemm.cu)
+GEMM_CHAIN_MAX_M = 128
 
 
 def launch_count() -> int:
@@ -434,11 +436,12 @@ def gemm_ssq_slots(m: int, n: int, k: int, splits: int = 0) -> int:
 
 
 def gemm_bf16(x, packed, n, bias=None, residual=None, epilogue=GEMM_BIAS, rounding=ROUND_EAGER, out=None,
-              splits=0, pdl=False, norm_weight=None, ssq_in=None, eps=1e-6, ssq_out=None):
+              splits=0, pdl=False, norm_weight=None, ssq_in=None, eps=1e-6, ssq_out=None, prefetch=None):
     """y = epilogue(x[M,K] @ W[N,K]^T) with W pre-packed by ``gemm_pack_weight``; bf16 in/out, fp32
     accumulation in TMEM.  GEMM_SILU_MUL returns [M, N/2]; GEMM_RESIDUAL may write in place (out=residual).
     ``norm_weight`` + ``ssq_in`` [M, slots] fp32: x is normalised (RMSNorm) while it is staged.
-    ``ssq_out`` [M, gemm_ssq_slots(n, k, splits)] fp32 receives the row sums of squares of the output."""
+    ``ssq_out`` [M, gemm_ssq_slots(n, k, splits)] fp32 receives the row sums of squares of the output.
+    ``prefetch``: the packed image of the NEXT projection's weight - pulled into L2 while this GEMM runs."""
     _cuda(x, BF16, "x")
     m, k = x.shape
     if x.stride(1) != 1:
@@ -449,7 +452,7 @@ def gemm_bf16(x, packed, n, bias=None, residual=None, epilogue=GEMM_BIAS, roundi
     if residual is not None:
         _cuda(residual, BF16, "residual")
     res_stride = residual.stride(0) if residual is not None else 0
-    if norm_weight is None and ssq_out is None:
+    if norm_weight is None and ssq_out is None and prefetch is None:
         _check(_load().b2tts_gemm_bf16(x.data_ptr(), x.stride(0), packed.data_ptr(), _ptr(bias), _ptr(residual),
                                        res_stride, out.data_ptr(), out.stride(0),
                                        m, n, k, int(epilogue), int(rounding), int(splits), int(bool(pdl)), _stream()),
@@ -466,6 +469,13 @@ def gemm_bf16(x, packed, n, bias=None, residual=None, epilogue=GEMM_BIAS, roundi
         need = gemm_ssq_slots(m, n, k, splits)
         if ssq_out.dim() != 2 or ssq_out.shape[0] < m or ssq_out.shape[1] != need or not ssq_out.is_contiguous():
             raise ValueError(f"ssq_out must be a contiguous [>=M, {need}] fp32 tensor")
+    if prefetch is not None:
+        _check(_load().b2tts_gemm_prefetch_bf16(
+            x.data_ptr(), x.stride(0), packed.data_ptr(), _ptr(bias), _ptr(residual), res_stride, out.data_ptr(),
+            out.stride(0), m, n, k, int(epilogue), int(rounding), int(splits), int(bool(pdl)), _ptr(norm_weight),
+            _ptr(ssq_in), slots_in, float(eps), _ptr(ssq_out), prefetch.data_ptr(),
+            prefetch.numel() * prefetch.element_size(), _stream()), "gemm_prefetch_bf16")
+        return out
     _check(_load().b2tts_gemm_norm_bf16(x.data_ptr(), x.stride(0), packed.data_ptr(), _ptr(bias), _ptr(residual),
                                         res_stride, out.data_ptr(), out.stride(0), m, n, k, int(epilogue),
                                         int(rounding), int(splits), int(bool(pdl)), _ptr(norm_weight), _ptr(ssq_in),

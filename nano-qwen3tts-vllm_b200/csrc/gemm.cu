@@ -39,7 +39,8 @@ constexpr int G_STAGES = 4;                    // ring depth the split heuristic
 constexpr int G_MAX_STAGES = 12;
 constexpr int G_THREADS = 192;                  // warp 0: W producer, warp 1: MMA issuer + TMEM owner, warps 2-5: x producers + epilogue
 constexpr int G_WTILE_BYTES = G_BN * G_BK * 2;  // 16 KiB
-constexpr int G_MAX_M = 128;
+constexpr int G_MAX_M = 128;                    // batch rows per CTA (UMMA N); larger batches are cut into row chunks
+constexpr int G_MAX_ROWS = 1 << 16;
 
 struct GemmParams {
   const __nv_bfloat16* x;
@@ -67,6 +68,15 @@ struct GemmParams {
   float* ssq_out;
   unsigned long long* trace;    // debug: 8 globaltimer stamps per CTA (null = off)
   int ssq_lanes;                // lanes per row when summing ssq_in (power of two, divides ssq_in_slots)
+  // L2 prefetch of the NEXT GEMM's packed weights (or null): weights never depend on activations, and a decode
+  // step is a chain of latency-bound launches during which HBM idles ~75 % of the time; every CTA asks the TMA
+  // unit to pull its slice of the next weight image into L2 (cp.async.bulk.prefetch.L2) once its own stream is fully
+  // requested, so the next launch streams from L2.
+  const uint8_t* pf_ptr;
+  unsigned long long pf_bytes;
+  int nchunks;                  // M > 128: the batch is cut into ceil(M / 128) row chunks, one CTA (cluster) per
+                                // (feature tile, chunk); blockIdx.y = tile * nchunks + chunk so that the chunks of one
+                                // weight tile are launched next to each other and share it through L2
 };
 
 // ---------------------------------------------------------------- tcgen05 / cluster PTX
@@ -219,7 +229,9 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   const int lane = threadIdx.x & 31;
   const int S = p.splits;
   const int rank = blockIdx.x;                  // gridDim.x == S == cluster size: rank in cluster
-  const int tile = blockIdx.y;
+  const int tile = blockIdx.y / p.nchunks;
+  const int row0 = (blockIdx.y % p.nchunks) * G_MAX_M;          // first batch row of this CTA's chunk
+  const int m_loc = min(p.m - row0, G_MAX_M);                   // rows of the chunk (the last one may be short)
   const int kb_begin = (int)(((int64_t)rank * p.kblocks) / S);
   const int kb_end = (int)(((int64_t)(rank + 1) * p.kblocks) / S);
   const int nkb = kb_end - kb_begin;
@@ -268,7 +280,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       if (elect_one()) {
         for (int i = 0; i < first; ++i) {
           mbar_expect_tx(raw_bar + i, xbytes);
-          tma_load_2d(smem + i * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, 0, raw_bar + i);
+          tma_load_2d(smem + i * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, row0, raw_bar + i);
         }
       }
       __syncwarp();
@@ -280,10 +292,19 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
           mbar_expect_tx(full_bar + stage, G_WTILE_BYTES);
           bulk_g2s(smem + stage * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + stage);
           mbar_expect_tx(raw_bar + stage, xbytes);
-          tma_load_2d(smem + stage * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, 0, raw_bar + stage);
+          tma_load_2d(smem + stage * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, row0, raw_bar + stage);
         }
         __syncwarp();
         if (++stage == NS) { stage = 0; ph ^= 1; }
+      }
+      // my own stream is fully requested: from here to the next launch's first copy HBM would idle (MMA tail, split-K
+      // exchange, epilogue, kernel boundary), so this is when the next weight image is pulled towards L2
+      if (p.pf_ptr && elect_one()) {
+        const unsigned long long ncta = (unsigned long long)gridDim.x * gridDim.y;
+        const unsigned long long me = (unsigned long long)blockIdx.y * gridDim.x + blockIdx.x;
+        const unsigned long long pieces = p.pf_bytes / G_WTILE_BYTES;
+        for (unsigned long long t = me; t < pieces; t += ncta)
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p.pf_ptr + t * G_WTILE_BYTES), "r"(G_WTILE_BYTES) : "memory");
       }
     }
     __syncwarp();
@@ -328,8 +349,8 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       for (int r0 = 0; r0 < mpad; r0 += rows_per_pass) {
         const int r = r0 + tp / G;
         float sum = 0.f;
-        if (r < p.m) {
-          const float* src = p.ssq_in + (int64_t)r * p.ssq_in_slots + gl * chunk;
+        if (r < m_loc) {
+          const float* src = p.ssq_in + (int64_t)(row0 + r) * p.ssq_in_slots + gl * chunk;
           if ((chunk & 3) == 0) {
             for (int i = 0; i < chunk; i += 4) {
               const float4 v = *reinterpret_cast<const float4*>(src + i);
@@ -363,7 +384,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
         for (int j = 0; j < NCH; ++j) {
           const int idx = tp + 128 * j;
           const int r = idx >> 3, c = idx & 7;
-          if (r < p.m) {
+          if (r < m_loc) {
             uint4* cell = reinterpret_cast<uint4*>(xs + r * 128 + ((c ^ (r & 7)) << 4));
             *cell = norm8(*cell, wv, rstd_s[r], eager);
           }
@@ -472,7 +493,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
         }
         uint2 w;
         w.x = pack_bf16(o[0], o[1]); w.y = pack_bf16(o[2], o[3]);
-        stg_v2(p.out + (int64_t)m * p.out_stride + (n >> 1), w);
+        stg_v2(p.out + (int64_t)(row0 + m) * p.out_stride + (n >> 1), w);
         return 0.f;
       }
       if (p.epilogue == B2TTS_GEMM_BIAS && p.bias) {
@@ -481,7 +502,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
         acc[4] += bf16lo(bw.z); acc[5] += bf16hi(bw.z); acc[6] += bf16lo(bw.w); acc[7] += bf16hi(bw.w);
       } else if (p.epilogue == B2TTS_GEMM_RESIDUAL) {
         // bf16(residual + bf16(x W^T)): the projection output is rounded before the add
-        const uint4 rw = ldg_v4(p.res + (int64_t)m * p.res_stride + n);
+        const uint4 rw = ldg_v4(p.res + (int64_t)(row0 + m) * p.res_stride + n);
         acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
         acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
         acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
@@ -490,7 +511,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       uint4 w;
       w.x = pack_bf16(acc[0], acc[1]); w.y = pack_bf16(acc[2], acc[3]);
       w.z = pack_bf16(acc[4], acc[5]); w.w = pack_bf16(acc[6], acc[7]);
-      stg_v4(p.out + (int64_t)m * p.out_stride + n, w);
+      stg_v4(p.out + (int64_t)(row0 + m) * p.out_stride + n, w);
       float q = 0.f;
       q = fmaf(bf16lo(w.x), bf16lo(w.x), q); q = fmaf(bf16hi(w.x), bf16hi(w.x), q);
       q = fmaf(bf16lo(w.y), bf16lo(w.y), q); q = fmaf(bf16hi(w.y), bf16hi(w.y), q);
@@ -502,16 +523,16 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       // one thread per batch row walks this CTA's feature groups in order: a deterministic partial
       // sum of squares of the stored row slice, slot = (tile, rank)
       const int slots = (p.n / G_BN) * S;
-      for (int m = threadIdx.x; m < p.m; m += G_THREADS) {
+      for (int m = threadIdx.x; m < m_loc; m += G_THREADS) {
         float q = 0.f;
         for (int g8 = 0; g8 < groups; ++g8) q += item(m, g8);
-        p.ssq_out[(int64_t)m * slots + tile * S + rank] = q;
+        p.ssq_out[(int64_t)(row0 + m) * slots + tile * S + rank] = q;
       }
     } else {
-      const int items = p.m * groups;
+      const int items = m_loc * groups;
       for (int it = threadIdx.x; it < items; it += G_THREADS) {
-        const int g8 = it / p.m;                   // lanes along m: conflict-free reads of red
-        item(it - g8 * p.m, g8);
+        const int g8 = it / m_loc;                 // lanes along m: conflict-free reads of red
+        item(it - g8 * m_loc, g8);
       }
     }
   }
@@ -592,7 +613,7 @@ static int launch_gemm(const GemmParams& p, const CUtensorMap& tmap, cudaStream_
     configured = true;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(p.splits, p.n / G_BN, 1);
+  cfg.gridDim = dim3(p.splits, (p.n / G_BN) * p.nchunks, 1);
   cfg.blockDim = dim3(G_THREADS, 1, 1);
   cfg.dynamicSmemBytes = gemm_smem_bytes(p.mpad, p.stages, p.splits);
   cfg.stream = st;
@@ -621,7 +642,8 @@ static int launch_gemm(const GemmParams& p, const CUtensorMap& tmap, cudaStream_
 }  // namespace b2
 
 extern "C" int b2tts_gemm_bf16_supported(int m, int n, int k) {
-  return m >= 1 && m <= b2::G_MAX_M && n >= b2::G_BN && n % b2::G_BN == 0 && k >= b2::G_BK && k % b2::G_BK == 0;
+  return m >= 1 && m <= b2::G_MAX_ROWS && n >= b2::G_BN && n % b2::G_BN == 0 && k >= b2::G_BK && k % b2::G_BK == 0 &&
+         (int64_t)(n / b2::G_BN) * ((m + b2::G_MAX_M - 1) / b2::G_MAX_M) <= 65535;
 }
 
 extern "C" size_t b2tts_gemm_packed_bytes(int n, int k) {
@@ -686,11 +708,13 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
                      void* out, int64_t out_row_stride, int m, int n, int k,
                      int epilogue, int rounding, int splits, int pdl,
                      const void* norm_weight, const float* ssq_in, int ssq_in_slots, float eps, float* ssq_out,
-                     void* stream) {
+                     const void* prefetch_next, size_t prefetch_bytes, void* stream) {
   B2_REQUIRE(m >= 0 && n > 0 && k > 0, B2TTS_EINVAL, "%s: m=%d n=%d k=%d", what, m, n, k);
+  B2_REQUIRE(!prefetch_next || (aligned16(prefetch_next) && prefetch_bytes % G_WTILE_BYTES == 0), B2TTS_EALIGN,
+             "%s: prefetch_next must be a packed weight image (16-byte aligned, a multiple of %d bytes)", what, G_WTILE_BYTES);
   if (m == 0) return B2TTS_OK;
   B2_REQUIRE(b2tts_gemm_bf16_supported(m, n, k), B2TTS_EUNSUPPORTED,
-             "%s: m=%d (1..%d), n=%d (multiple of %d), k=%d (multiple of %d)", what, m, G_MAX_M, n, G_BN, k, G_BK);
+             "%s: m=%d (1..%d), n=%d (multiple of %d), k=%d (multiple of %d)", what, m, G_MAX_ROWS, n, G_BN, k, G_BK);
   B2_REQUIRE(x && w_packed && out, B2TTS_EINVAL, "%s: null pointer", what);
   B2_REQUIRE(epilogue == B2TTS_GEMM_BIAS || epilogue == B2TTS_GEMM_RESIDUAL || epilogue == B2TTS_GEMM_SILU_MUL,
              B2TTS_EINVAL, "%s: epilogue %d", what, epilogue);
@@ -712,11 +736,12 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
   p.out = static_cast<__nv_bfloat16*>(out);
   p.out_stride = out_row_stride;
   p.m = m; p.n = n; p.k = k;
-  p.mpad = (m + 15) & ~15;
+  p.nchunks = (m + G_MAX_M - 1) / G_MAX_M;
+  p.mpad = p.nchunks > 1 ? G_MAX_M : (m + 15) & ~15;
   p.kblocks = k / G_BK;
   p.epilogue = epilogue;
   p.rounding = rounding;
-  int s = splits > 0 ? splits : choose_splits(n / G_BN, p.kblocks, p.mpad);
+  int s = splits > 0 ? splits : choose_splits((n / G_BN) * p.nchunks, p.kblocks, p.mpad);
   B2_REQUIRE((s == 1 || s == 2 || s == 4 || s == 8 || s == 16) && s <= p.kblocks, B2TTS_EINVAL,
              "%s: splits %d must be 1,2,4,8,16 and <= k/64", what, s);
   p.splits = s;
@@ -730,6 +755,8 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
   p.eps = eps;
   p.ssq_out = ssq_out;
   p.ssq_lanes = 1;
+  p.pf_ptr = prefetch_bytes ? static_cast<const uint8_t*>(prefetch_next) : nullptr;
+  p.pf_bytes = prefetch_bytes;
   p.trace = nullptr;
   if (g_trace_base && g_trace_next < g_trace_slots) p.trace = g_trace_base + (g_trace_next++) * 4096 * 8;
   if (norm_weight) {
@@ -759,12 +786,14 @@ extern "C" int b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void* 
                                void* out, int64_t out_row_stride, int m, int n, int k,
                                int epilogue, int rounding, int splits, int pdl, void* stream) {
   return b2::gemm_impl("gemm_bf16", x, x_row_stride, w_packed, bias, residual, residual_row_stride, out, out_row_stride,
-                       m, n, k, epilogue, rounding, splits, pdl, nullptr, nullptr, 0, 0.f, nullptr, stream);
+                       m, n, k, epilogue, rounding, splits, pdl, nullptr, nullptr, 0, 0.f, nullptr, nullptr, 0, stream);
 }
 
 extern "C" int b2tts_gemm_ssq_slots(int m, int n, int k, int splits) {
   if (n <= 0 || k <= 0 || n % b2::G_BN || k % b2::G_BK) return 0;
-  const int s = splits > 0 ? splits : b2::choose_splits(n / b2::G_BN, k / b2::G_BK, (m + 15) & ~15);
+  const int nchunks = (m + b2::G_MAX_M - 1) / b2::G_MAX_M;
+  const int mpad = nchunks > 1 ? b2::G_MAX_M : (m + 15) & ~15;
+  const int s = splits > 0 ? splits : b2::choose_splits((n / b2::G_BN) * nchunks, k / b2::G_BK, mpad);
   return (n / b2::G_BN) * s;
 }
 
@@ -776,7 +805,18 @@ extern "C" int b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const v
                                     float* ssq_out, void* stream) {
   return b2::gemm_impl("gemm_norm_bf16", x, x_row_stride, w_packed, bias, residual, residual_row_stride, out,
                        out_row_stride, m, n, k, epilogue, rounding, splits, pdl, norm_weight, ssq_in, ssq_in_slots, eps,
-                       ssq_out, stream);
+                       ssq_out, nullptr, 0, stream);
+}
+
+extern "C" int b2tts_gemm_prefetch_bf16(const void* x, int64_t x_row_stride, const void* w_packed,
+                                        const void* bias, const void* residual, int64_t residual_row_stride,
+                                        void* out, int64_t out_row_stride, int m, int n, int k,
+                                        int epilogue, int rounding, int splits, int pdl,
+                                        const void* norm_weight, const float* ssq_in, int ssq_in_slots, float eps,
+                                        float* ssq_out, const void* prefetch_next, size_t prefetch_bytes, void* stream) {
+  return b2::gemm_impl("gemm_prefetch_bf16", x, x_row_stride, w_packed, bias, residual, residual_row_stride, out,
+                       out_row_stride, m, n, k, epilogue, rounding, splits, pdl, norm_weight, ssq_in, ssq_in_slots, eps,
+                       ssq_out, prefetch_next, prefetch_bytes, stream);
 }
 
 // =====================================================================================================

@@ -216,16 +216,18 @@ class DeviceFrameLoop:
         self._draw_noise()
         # ---- predictor prefill on [hidden_i, embed(code0_i)] (both already in p_x)   interface.py:1242-1252
         set_context(True, self.p_cu, self.p_cu, 2, 2, self.p_pre_slots, None, None)
-        h = predictor(self.p_x, self.p_pre_pos)
+        qkv0 = predictor.model.layers[0].self_attn.qkv_proj.weight      # what streams after every predictor head
+        h = predictor(self.p_x, self.p_pre_pos, head=0)
         last = h.view(b, 2, -1)[:, 1]
-        self._sample(linear(last, predictor.lm_head[0]), self.p_temp, 1)
+        self._sample(linear(last, predictor.lm_head[0], nxt=qkv0), self.p_temp, 1)
         # ---- 14 predictor decode passes                                 predictor_model_runner.py:134-157
         for g in range(1, self.ncb - 1):
             lay = self.p_dec[g - 1]
             set_context(False, slot_mapping=lay["slots"], context_lens=lay["ctx"], block_tables=self.p_tables,
                         max_context_len=g + 2)           # exact: no split-KV, no combine launch
-            h = predictor(self.p_emb, lay["pos"])        # p_emb = codec_embedding[g-1][code g], left by the sampler
-            self._sample(linear(h, predictor.lm_head[g]), self.p_temp, g + 1)
+            h = predictor(self.p_emb, lay["pos"], head=g)   # p_emb = codec_embedding[g-1][code g], left by the sampler
+            nxt = qkv0 if g + 1 < self.ncb - 1 else talker.model.layers[0].self_attn.qkv_proj.weight
+            self._sample(linear(h, predictor.lm_head[g], nxt=nxt), self.p_temp, g + 1)
         # ---- emit the frame, build the next talker input                       interface.py:1269-1286
         self.codes.copy_(self.codes_t.t())
         self.frames.index_copy_(0, self.frame_idx, self.codes.unsqueeze(0))
@@ -237,7 +239,8 @@ class DeviceFrameLoop:
         set_context(False, slot_mapping=self.t_slots, context_lens=self.t_ctx, block_tables=self.t_tables,
                     max_context_len=self.width * self.page)
         th = talker(self.embeds, self.t_pos)
-        self._sample(linear(th, talker.codec_head.weight), self.t_temp, 0)
+        proj = predictor.small_to_mtp_projection
+        self._sample(linear(th, talker.codec_head.weight, nxt=proj.weight if proj is not None else qkv0), self.t_temp, 0)
         self.hidden.copy_(th)
         reset_context()
 

@@ -3,18 +3,29 @@ attributes (layers/linear.py:12-153).  Replicas only (tp_size == 1): no process 
 and no collective follows any GEMM.
 
 ``linear()`` is the one GEMM entry of the hot path: y[M,N] = x[M,K] @ W[N,K]^T (+ b).  In decode
-M is the number of streams, so the GEMM streams W once from HBM; the hand-written sm_100a kernel
+M is the number of streams, so the GEMM streams W once from HBM: the hand-written sm_100a kernel
 (``b2tts_gemm_bf16``: weights as the 128-row tcgen05 operand, the batch as the N tile, accumulators
-in TMEM) serves M <= GEMM_NATIVE_MAX_M, and cuBLASLt (through torch) serves the large-M prefill
-contractions - a plain library GEMM."""
+in TMEM).  Larger row counts (decode batches above 128 streams, the predictor's 2-token prefill) run the
+same kernel over 128-row chunks of x with the same fused epilogues; the chunks of one weight tile are
+launched next to each other and share it through L2.  Beyond ``GEMM_NATIVE_MAX_M`` rows (long prompt
+prefills) the product is compute-bound and goes to the plain library GEMM
+(``torch.nn.functional.linear`` = cuBLAS), as it does for shapes the kernel cannot tile
+(n % 128 != 0 or k % 64 != 0), which no shipped model has."""
+import os
+
 import torch
 from torch import nn
 
 from .. import _native as nat
 
-GEMM_NATIVE_MAX_M = nat.GEMM_MAX_M
-import os
+# rows up to which the projections run on the weight-streaming kernel; beyond it (long prefills) the GEMM is
+# compute-bound and the plain library GEMM (cuBLAS, 1.43 PFLOP/s at M = 4096 against our 0.93) takes over
+GEMM_NATIVE_MAX_M = int(os.environ.get("B2TTS_GEMM_NATIVE_MAX_M", "512"))
 PDL = os.environ.get("B2TTS_PDL_GEMM", "1") != "0"     # programmatic dependent launch of the native GEMM (weight stream starts early)
+# each GEMM pulls the NEXT projection's weights into L2 (b2tts_gemm_prefetch_bf16).  Off by default: measured at 64
+# streams it does not shorten the frame (5873 us against 5885 us; talker pass 2052 against 2018) - the launches are
+# bound by their dependent latencies, not by the weight stream (DESIGN.md section 8).
+PREFETCH = os.environ.get("B2TTS_GEMM_PREFETCH", "0") != "0"
 _packed: dict = {}
 
 
@@ -70,17 +81,29 @@ def _ssq_buffer(m, n, k, device):
     return torch.empty(m, nat.gemm_ssq_slots(m, n, k), dtype=torch.float32, device=device)
 
 
+def _pf(nxt):
+    """``nxt`` = the weight the NEXT GEMM of the chain will stream (a tensor, or (tensor, pack mode)) -> its packed
+    image, for the L2 prefetch."""
+    if nxt is None or not PREFETCH:
+        return None
+    if isinstance(nxt, tuple):
+        return packed_weight(nxt[0], nxt[1])
+    return packed_weight(nxt)
+
+
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = None,
-           out: torch.Tensor | None = None, norm: RowNorm | None = None, want_ssq: bool = False):
+           out: torch.Tensor | None = None, norm: RowNorm | None = None, want_ssq: bool = False, nxt=None):
     """y = x W^T (+ b).  ``norm``: x is un-normalised and the GEMM applies the RMSNorm on the fly (native
-    path only).  ``want_ssq``: also return the [M, slots] partial row sums of squares of y."""
+    path only).  ``want_ssq``: also return the [M, slots] partial row sums of squares of y.  ``nxt``: the weight
+    of the next GEMM on the stream (prefetched into L2 meanwhile)."""
     if not x.is_cuda:
         raise RuntimeError("libb200tts: linear() needs CUDA tensors (there is no CPU path)")
     x2 = x.reshape(-1, x.shape[-1])
     m, n = x2.shape[0], weight.shape[0]
     if native_ok(m, n, x2.shape[1]):
         ssq = _ssq_buffer(m, n, x2.shape[1], x.device) if want_ssq else None
-        y = nat.gemm_bf16(x2, packed_weight(weight), n, bias=bias, out=out, pdl=PDL, ssq_out=ssq, **_norm_kw(norm))
+        y = nat.gemm_bf16(x2, packed_weight(weight), n, bias=bias, out=out, pdl=PDL, ssq_out=ssq, prefetch=_pf(nxt),
+                          **_norm_kw(norm))
         y = y.view(*x.shape[:-1], n)
         return (y, ssq) if want_ssq else y
     if norm is not None or want_ssq:
@@ -93,7 +116,7 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = No
 
 
 def linear_residual(x: torch.Tensor, weight: torch.Tensor, residual: torch.Tensor,
-                    out: torch.Tensor | None = None, want_ssq: bool = False):
+                    out: torch.Tensor | None = None, want_ssq: bool = False, nxt=None):
     """bf16(residual + bf16(x W^T)) - the projection followed by the decoder layer's residual add
     (models/qwen3_tts_share.py:171,175 of the reference) in the GEMM epilogue.  ``out`` may be ``residual``.
     ``want_ssq`` also returns the partial row sums of squares of the result (for the next fused norm)."""
@@ -101,7 +124,7 @@ def linear_residual(x: torch.Tensor, weight: torch.Tensor, residual: torch.Tenso
     if native_ok(m, n, x.shape[1]):
         ssq = _ssq_buffer(m, n, x.shape[1], x.device) if want_ssq else None
         y = nat.gemm_bf16(x, packed_weight(weight), n, residual=residual, epilogue=nat.GEMM_RESIDUAL, out=out, pdl=PDL,
-                          ssq_out=ssq)
+                          ssq_out=ssq, prefetch=_pf(nxt))
         return (y, ssq) if want_ssq else y
     if want_ssq:
         raise RuntimeError(f"libb200tts: ssq epilogue unsupported for m={m} n={n} k={x.shape[1]}")
@@ -112,7 +135,7 @@ def linear_residual(x: torch.Tensor, weight: torch.Tensor, residual: torch.Tenso
 
 
 def linear_silu_mul(x: torch.Tensor, gate_up_weight: torch.Tensor, rounding: int = nat.ROUND_EAGER,
-                    norm: RowNorm | None = None) -> torch.Tensor:
+                    norm: RowNorm | None = None, nxt=None) -> torch.Tensor:
     """silu(x Wg^T) * (x Wu^T) over the merged [gate; up] weight (qwen3_tts_share.py:131-135) with the
     activation in the GEMM epilogue: the [M, 2I] intermediate never reaches HBM."""
     m, n = x.shape[0], gate_up_weight.shape[0]
@@ -120,7 +143,7 @@ def linear_silu_mul(x: torch.Tensor, gate_up_weight: torch.Tensor, rounding: int
         kw = _norm_kw(norm)
         kw.setdefault("rounding", rounding)
         return nat.gemm_bf16(x, packed_weight(gate_up_weight, nat.PACK_GATE_UP), n, epilogue=nat.GEMM_SILU_MUL,
-                             pdl=PDL, **kw)
+                             pdl=PDL, prefetch=_pf(nxt), **kw)
     if norm is not None:
         raise RuntimeError(f"libb200tts: fused-norm GEMM unsupported for m={m} n={n} k={x.shape[1]}")
     gu = torch.nn.functional.linear(x, gate_up_weight)

@@ -24,8 +24,8 @@ class Qwen3TTSCodePredictorModel(DecoderStack):
         self.codec_embedding = nn.Parameter(torch.empty(n, config.vocab_size, talker_config.hidden_size),
                                             requires_grad=False)
 
-    def forward(self, input_embeds: torch.Tensor, positions: torch.Tensor, input_ssq=None) -> torch.Tensor:
-        return self.run_layers(input_embeds, positions, input_ssq)
+    def forward(self, input_embeds: torch.Tensor, positions: torch.Tensor, input_ssq=None, tail_weight=None) -> torch.Tensor:
+        return self.run_layers(input_embeds, positions, input_ssq, tail_weight)
 
 
 class Qwen3TTSCodePredictorForCausalLM(nn.Module):
@@ -77,16 +77,19 @@ class Qwen3TTSCodePredictorForCausalLM(nn.Module):
             torch.tensor(generation_steps, dtype=torch.int32, device=input_ids.device)
         return nat.gather_rows(self.model.codec_embedding, input_ids.view(-1), (steps - 1).to(torch.int32))
 
-    def forward(self, inputs_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
+    def forward(self, inputs_embeds: torch.Tensor, positions: torch.Tensor, head: int | None = None) -> torch.Tensor:
+        """``head``: the LM head the caller applies next (its weights are pulled into L2 by the last layer)."""
         proj, ssq = self.small_to_mtp_projection, None
+        tail = self.lm_head[head] if head is not None else None
         if proj is not None:
             x2 = inputs_embeds.reshape(-1, inputs_embeds.shape[-1])
             if native_ok(x2.shape[0], proj.weight.shape[0], x2.shape[1]):
                 # the projection's epilogue leaves the row sums of squares the first layer's norm needs
-                inputs_embeds, ssq = linear(x2, proj.weight, proj.bias, want_ssq=True)
+                inputs_embeds, ssq = linear(x2, proj.weight, proj.bias, want_ssq=True,
+                                            nxt=self.model.layers[0].self_attn.qkv_proj.weight)
             else:
                 inputs_embeds = proj(inputs_embeds)
-        return self.model(inputs_embeds, positions, ssq)
+        return self.model(inputs_embeds, positions, ssq, tail)
 
     def compute_logits(self, hidden_states: torch.Tensor, generation_steps: list[int]) -> torch.Tensor:
         """hidden_states [num_seqs * len, H] -> logits of the LAST position of every sequence through

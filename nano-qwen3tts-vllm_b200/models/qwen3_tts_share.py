@@ -61,7 +61,7 @@ class Qwen3TTSAttention(nn.Module):
     def attend(self, positions: torch.Tensor, hidden_states: torch.Tensor, norm: RowNorm | None = None) -> torch.Tensor:
         """Everything up to (not including) o_proj: [n, heads * head_dim].  With ``norm`` the input is the
         un-normalised residual stream and the QKV GEMM applies the input RMSNorm while staging it."""
-        return self.attend_qkv(positions, linear(hidden_states, self.qkv_proj.weight, norm=norm))
+        return self.attend_qkv(positions, linear(hidden_states, self.qkv_proj.weight, norm=norm, nxt=self.o_proj.weight))
 
     def attend_qkv(self, positions: torch.Tensor, qkv: torch.Tensor) -> torch.Tensor:
         """``attend`` from the rows of the QKV projection (the GEMM chain of the previous layer produced them)."""
@@ -129,15 +129,17 @@ class Qwen3TTSDecoderLayer(nn.Module):
         hidden_states = self.mlp(hidden_states)
         return hidden_states, residual
 
-    def forward_decode(self, positions: torch.Tensor, residual: torch.Tensor, ssq: torch.Tensor | None, in_place: bool):
-        """The same layer on the residual stream alone, for n <= GEMM_NATIVE_MAX_M rows, 5 launches:
+    def forward_decode(self, positions: torch.Tensor, residual: torch.Tensor, ssq: torch.Tensor | None, in_place: bool,
+                       nxt=None):
+        """The same layer on the residual stream alone (decode and prefill, any row count), 5 launches:
         QKV GEMM (input RMSNorm applied while x is staged), q/k-norm + RoPE + KV write, attention,
         o_proj GEMM (+ residual add, row sums of squares out), gate_up GEMM (post-attention RMSNorm in,
         SiLU*mul out), down GEMM (+ residual add, row sums of squares out).  ``ssq`` = partial row sums of
         squares of ``residual`` from the GEMM that produced it (None: a separate RMSNorm launch).
         Rounding points are unchanged: bf16(residual + bf16(x W^T)), then the norm of the rounded sum.
         ``in_place`` False keeps the caller's tensor (the first layer's input embeddings) intact.
-        Returns (residual, ssq)."""
+        ``nxt``: the weight the GEMM after this layer streams (the next layer's qkv_proj, or the LM head): every GEMM
+        here pulls its successor's weights into L2 while it runs.  Returns (residual, ssq)."""
         if ssq is None:
             h = nat.rmsnorm(residual, self.input_layernorm.weight, self.eps, self.rounding)
             o = self.self_attn.attend(positions, h)
@@ -145,10 +147,11 @@ class Qwen3TTSDecoderLayer(nn.Module):
             o = self.self_attn.attend(positions, residual,
                                       RowNorm(self.input_layernorm.weight, ssq, self.eps, self.rounding))
         residual, ssq = linear_residual(o, self.self_attn.o_proj.weight, residual, out=residual if in_place else None,
-                                        want_ssq=True)
+                                        want_ssq=True, nxt=(self.mlp.gate_up_proj.weight, nat.PACK_GATE_UP))
         act = linear_silu_mul(residual, self.mlp.gate_up_proj.weight, self.rounding,
-                              norm=RowNorm(self.post_attention_layernorm.weight, ssq, self.eps, self.rounding))
-        return linear_residual(act, self.mlp.down_proj.weight, residual, out=residual, want_ssq=True)
+                              norm=RowNorm(self.post_attention_layernorm.weight, ssq, self.eps, self.rounding),
+                              nxt=self.mlp.down_proj.weight)
+        return linear_residual(act, self.mlp.down_proj.weight, residual, out=residual, want_ssq=True, nxt=nxt)
 
 
 class DecoderStack(nn.Module):
@@ -170,13 +173,23 @@ class DecoderStack(nn.Module):
                 (c.hidden_size, c.intermediate_size), (c.q_size + 2 * c.kv_size, c.hidden_size)))
         return ok
 
+    def _native_gemm_shapes(self) -> bool:
+        """All four projections have n % 128 == 0 and k % 64 == 0 (true for every shipped model size)."""
+        ok = getattr(self, "_native_ok", None)
+        if ok is None:
+            c = self.config
+            ok = self._native_ok = all(nat.gemm_supported(1, n, k) for n, k in (
+                (c.hidden_size, c.q_size), (2 * c.intermediate_size, c.hidden_size),
+                (c.hidden_size, c.intermediate_size), (c.q_size + 2 * c.kv_size, c.hidden_size)))
+        return ok
+
     def _chain_workspace(self, device) -> torch.Tensor:
         ws = getattr(self, "_chain_ws", None)
         if ws is None or ws.device != torch.device(device):
             c = self.config
             shapes = [(c.hidden_size, c.q_size), (2 * c.intermediate_size, c.hidden_size),
                       (c.hidden_size, c.intermediate_size), (c.q_size + 2 * c.kv_size, c.hidden_size)]
-            ws = self._chain_ws = nat.gemm_chain_workspace(GEMM_NATIVE_MAX_M, shapes, device)
+            ws = self._chain_ws = nat.gemm_chain_workspace(nat.GEMM_CHAIN_MAX_M, shapes, device)
         return ws
 
     def run_layers_chained(self, input_embeds: torch.Tensor, positions: torch.Tensor,
@@ -221,13 +234,17 @@ class DecoderStack(nn.Module):
         return nat.rmsnorm(residual, self.norm.weight, eps, rnd)
 
     def run_layers(self, input_embeds: torch.Tensor, positions: torch.Tensor,
-                   input_ssq: torch.Tensor | None = None) -> torch.Tensor:
-        if GEMM_CHAIN and 1 <= input_embeds.shape[0] <= GEMM_NATIVE_MAX_M and self._chain_supported():
+                   input_ssq: torch.Tensor | None = None, tail_weight=None) -> torch.Tensor:
+        """``tail_weight``: the weight streamed right after the stack (the LM head), prefetched by the last layer."""
+        if GEMM_CHAIN and 1 <= input_embeds.shape[0] <= nat.GEMM_CHAIN_MAX_M and self._chain_supported():
             return self.run_layers_chained(input_embeds, positions, input_ssq)
-        if input_embeds.shape[0] <= GEMM_NATIVE_MAX_M:
+        if 1 <= input_embeds.shape[0] <= GEMM_NATIVE_MAX_M and self._native_gemm_shapes():
+            # decode and short prefills (<= GEMM_NATIVE_MAX_M rows): 5 launches per layer, norms / residual adds / SiLU*mul inside the GEMMs
             residual, ssq = input_embeds, input_ssq
+            nl = len(self.layers)
             for i, layer in enumerate(self.layers):
-                residual, ssq = layer.forward_decode(positions, residual, ssq, in_place=i > 0)
+                nxt = self.layers[i + 1].self_attn.qkv_proj.weight if i + 1 < nl else tail_weight
+                residual, ssq = layer.forward_decode(positions, residual, ssq, in_place=i > 0, nxt=nxt)
             return nat.rmsnorm(residual, self.norm.weight, self.config.rms_norm_eps, self.rounding)
         hidden_states, residual = input_embeds, None
         for layer in self.layers:

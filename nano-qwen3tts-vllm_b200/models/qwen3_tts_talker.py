@@ -38,8 +38,8 @@ class Qwen3TTSTalkerModel(DecoderStack):
     def get_text_embeddings(self):
         return self.text_embedding
 
-    def forward(self, input_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
-        return self.run_layers(input_embeds, positions)
+    def forward(self, input_embeds: torch.Tensor, positions: torch.Tensor, tail_weight=None) -> torch.Tensor:
+        return self.run_layers(input_embeds, positions, None, tail_weight)
 
 
 class Qwen3TTSTalkerForCausalLM(nn.Module):
@@ -73,7 +73,7 @@ class Qwen3TTSTalkerForCausalLM(nn.Module):
         return self.model.get_text_embeddings()
 
     def forward(self, input_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
-        return self.model(input_embeds, positions)
+        return self.model(input_embeds, positions, self.codec_head.weight)
 
     def compute_logits(self, hidden_states: torch.Tensor) -> torch.Tensor:
         return self.codec_head(hidden_states)

@@ -141,7 +141,8 @@ def test_gemm_linearity_at_full_size(native):
 def test_gemm_argument_errors(native):
     x = torch.zeros(4, 100, device="cuda", dtype=BF16)
     assert not native.gemm_supported(4, 128, 100)
-    assert not native.gemm_supported(300, 128, 64)
+    assert native.gemm_supported(300, 128, 64)              # rows beyond 128 run as 128-row chunks of the grid
+    assert not native.gemm_supported((1 << 16) + 1, 128, 64)
     with pytest.raises(RuntimeError):
         native.gemm_pack_weight(torch.zeros(100, 64, device="cuda", dtype=BF16))
     w = native.gemm_pack_weight(torch.zeros(128, 128, device="cuda", dtype=BF16))
@@ -208,3 +209,67 @@ def test_gemm_bias_epilogue_ssq_out(native):
     y = native.gemm_bf16(x, native.gemm_pack_weight(w), n, bias=b, ssq_out=ssq)
     assert torch.equal(y, native.gemm_bf16(x, native.gemm_pack_weight(w), n, bias=b))
     torch.testing.assert_close(ssq.sum(1), y.float().pow(2).sum(1), rtol=1e-5, atol=1e-5)
+
+
+# ------------------------------------------------------------------ more than 128 rows: grid chunks of 128 rows
+@pytest.mark.parametrize("m", [129, 256, 300, 1000, 4096])
+def test_gemm_row_chunks(native, m):
+    """Prefill-sized M (SURVEY.md section 8a row a7 "lift G_MAX_M"): every 128-row chunk is its own set of CTAs,
+    the last one ragged.  Same bound as the single-chunk case, every epilogue."""
+    n, k = 2048, 1024
+    g = torch.Generator(device="cuda").manual_seed(m)
+    x = torch.randn(m, k, device="cuda", generator=g).to(BF16)
+    w = (torch.randn(n, k, device="cuda", generator=g) * 0.05).to(BF16)
+    b = torch.randn(n, device="cuda", generator=g).to(BF16)
+    res = torch.randn(m, n, device="cuda", generator=g).to(BF16)
+    pk = native.gemm_pack_weight(w)
+    _check(native.gemm_bf16(x, pk, n, bias=b), _ref_linear(x, w, b), f"chunked gemm+bias m={m}")
+    y = native.gemm_bf16(x, pk, n, residual=res, epilogue=native.GEMM_RESIDUAL)
+    want = res.float() + (x.double() @ w.double().t()).to(BF16).float()
+    assert (y.float() - want).abs().max().item() <= 2e-2 * want.abs().max().item()
+    # rows are independent: chunked result == the same rows computed 128 at a time (same K split => same fp32 order)
+    full = native.gemm_bf16(x, pk, n, bias=b, splits=2)
+    for lo in (0, 128 * ((m - 1) // 128)):
+        hi = min(m, lo + 128)
+        assert torch.equal(native.gemm_bf16(x[lo:hi], pk, n, bias=b, splits=2), full[lo:hi])
+
+
+@pytest.mark.parametrize("m", [200, 512])
+@pytest.mark.parametrize("rounding", [0, 1])
+def test_gemm_row_chunks_fused_norm_ssq_silu(native, m, rounding):
+    h, inter, eps = 1024, 3072, 1e-6
+    g = torch.Generator(device="cuda").manual_seed(m + rounding)
+    act = torch.randn(m, inter, device="cuda", generator=g).to(BF16)
+    res = torch.randn(m, h, device="cuda", generator=g).to(BF16)
+    w_down = (torch.randn(h, inter, device="cuda", generator=g) * 0.03).to(BF16)
+    w_gu = (torch.randn(2 * inter, h, device="cuda", generator=g) * 0.03).to(BF16)
+    nw = (1 + 0.1 * torch.randn(h, device="cuda", generator=g)).to(BF16)
+    pd, pg = native.gemm_pack_weight(w_down), native.gemm_pack_weight(w_gu, native.PACK_GATE_UP)
+    ssq = torch.full((m, native.gemm_ssq_slots(m, h, inter)), float("nan"), device="cuda")
+    new_res = native.gemm_bf16(act, pd, h, residual=res, epilogue=native.GEMM_RESIDUAL, ssq_out=ssq)
+    assert torch.equal(new_res, native.gemm_bf16(act, pd, h, residual=res, epilogue=native.GEMM_RESIDUAL))
+    torch.testing.assert_close(ssq.sum(1), new_res.float().pow(2).sum(1), rtol=1e-5, atol=1e-5)
+    y = native.gemm_bf16(new_res, pg, 2 * inter, epilogue=native.GEMM_SILU_MUL, rounding=rounding, norm_weight=nw,
+                         ssq_in=ssq, eps=eps)
+    want = native.gemm_bf16(native.rmsnorm(new_res, nw, eps, rounding), pg, 2 * inter, epilogue=native.GEMM_SILU_MUL,
+                            rounding=rounding)
+    assert y.shape == (m, inter)
+    diff = (y.float() - want.float()).abs()
+    assert diff.max().item() <= 2e-2 * want.float().abs().max().item()
+    assert (diff > 0).float().mean().item() < 0.02
+
+
+def test_gemm_prefetch_next_weights_changes_nothing(native):
+    """b2tts_gemm_prefetch_bf16: the L2 prefetch of the next projection's packed weights is a hint only."""
+    m, n, k = 64, 1024, 2048
+    g = torch.Generator(device="cuda").manual_seed(77)
+    x = torch.randn(m, k, device="cuda", generator=g).to(BF16)
+    w = (torch.randn(n, k, device="cuda", generator=g) * 0.05).to(BF16)
+    nxt = native.gemm_pack_weight((torch.randn(4096, n, device="cuda", generator=g) * 0.05).to(BF16))
+    pk = native.gemm_pack_weight(w)
+    ssq = torch.zeros(m, native.gemm_ssq_slots(m, n, k), device="cuda")
+    y = native.gemm_bf16(x, pk, n, ssq_out=ssq, prefetch=nxt)
+    assert torch.equal(y, native.gemm_bf16(x, pk, n))
+    assert torch.equal(native.gemm_bf16(x, pk, n, prefetch=nxt), y)
+    with pytest.raises(RuntimeError):
+        native.gemm_bf16(x, pk, n, prefetch=nxt.view(-1)[8:8 + 16384])        # not 16-byte aligned
