@@ -11,7 +11,9 @@ synthetic streams with a 64-token prompt, top-k 50 sampling at T=1.0/0.9, EOS ig
   value     frames/s with everything resident in HBM: one CUDA-graph launch per frame (DeviceFrameLoop)
   e2e       frames/s through the reference-facing step API (TalkerLLM / PredictorLLM add_request/step)
             with HOST buffers crossing both ways every frame (StepApiFrameLoop)
-  roofline  paged decode attention kernel at this workload's context lengths (CUDA events, per launch)
+  roofline  the dominant kernel (weight-streaming tcgen05 GEMM) + roofline_kernels for every other kernel of the path
+  reference_kernels   cuBLAS / flash-attn / Triton on the same shapes, timed the same way (bench_kernels.py)
+  other_workloads     1 / 8 / 128 / 256 / 512 streams;  icl_workload = BASELINE configs[3] (4k-token prompts)
   cpu_baseline   the CPU oracle (port of the reference's torch path) on the host cores, bounded sample
 
 N > 1: independent per-GPU replicas (no collective on the data path); barrier + max-over-ranks timing.
@@ -47,7 +49,10 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-streams", type=int, default=0, help="streams of the CPU legs (0 = the same as --streams)")
-    ap.add_argument("--also-streams", default="1,8", help="extra stream counts reported under other_workloads")
+    ap.add_argument("--also-streams", default="1,8,128,256,512",
+                    help="extra stream counts reported under other_workloads (BASELINE configs[1], [2], [4])")
+    ap.add_argument("--no-icl", action="store_true", help="skip the BASELINE configs[3] leg (4k-token prompts, 8 streams)")
+    ap.add_argument("--no-reference-kernels", action="store_true")
     return ap.parse_args()
 
 
@@ -58,6 +63,19 @@ def peaks():
         return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def tensor_peak():
+    """Dense bf16 TFLOP/s: the sustained figure (kernels timed back to back inside a graph)."""
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        for key in ("bf16_tflops_sustained", "bf16_sustained_tflops", "bf16_tflops"):
+            if key in p:
+                return float(p[key]), f"measured (MEASURED_PEAKS.json {key})"
+        raise KeyError
+    except Exception:
+        return 1400.0, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler:
@@ -109,12 +127,12 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
-def build_engines(model_size: str, streams: int, max_frames: int, device: str):
+def build_engines(model_size: str, streams: int, max_frames: int, device: str, prompt_len: int = PROMPT_LEN):
     from nano_qwen3tts_vllm_b200.config import qwen3_tts_config
     from nano_qwen3tts_vllm_b200.llm import PredictorLLM, TalkerLLM
     mc = qwen3_tts_config(model_size)
     page = 256
-    width = (PROMPT_LEN + max_frames + 2 + page - 1) // page
+    width = (prompt_len + max_frames + 2 + page - 1) // page
     max_len = width * page
     common = dict(max_num_seqs=max(streams, 2), max_model_len=max_len, max_num_batched_tokens=max(16384, max_len),
                   device=device, graph_batch_sizes=[streams])
@@ -146,43 +164,6 @@ def frame_bytes(mc, lens_sum: float) -> float:
                  + (t.hidden_size * p.hidden_size if t.hidden_size != p.hidden_size else 0)) * 2
     kv = t.num_hidden_layers * 2 * t.kv_size * 2 * lens_sum
     return talker_w + (p.num_code_groups - 1) * pred_pass + kv
-
-
-def time_attention_kernel(talker_runner, loop, iters: int = 3):
-    """Average duration of ONE paged decode attention launch at the loop's current context lengths:
-    CUDA events on the launching stream around one launch per talker layer (each layer has its own
-    K/V pages, together far larger than L2, so every launch reads cold data)."""
-    import torch
-    import nano_qwen3tts_vllm_b200._native as nat
-    r = talker_runner
-    c = r.stack_config
-    b = loop.b
-    q = torch.randn(b, c.num_attention_heads, c.head_dim, device=r.device, dtype=torch.bfloat16)
-    out = torch.empty_like(q)
-    ctx = (loop.seq_lens - 1).clamp_min(1).to(torch.int32).contiguous()
-    max_ctx = loop.width * loop.page
-    L = c.num_hidden_layers
-    def launches():
-        for l in range(L):
-            nat.paged_attn_decode(q, r.kv_cache[0, l], r.kv_cache[1, l], loop.t_tables, ctx, c.head_dim ** -0.5,
-                                  max_ctx, out=out, workspace=r.attn_workspace)
-    launches()
-    torch.cuda.synchronize()
-    g = torch.cuda.CUDAGraph()                  # no host launch gaps between the L launches
-    with torch.cuda.graph(g):
-        launches()
-    best = []
-    for it in range(iters + 1):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        g.replay()
-        e1.record()
-        torch.cuda.synchronize()
-        if it:
-            best.append(e0.elapsed_time(e1) / L)
-    ms = sorted(best)[len(best) // 2]
-    alg = float((4096.0 * ctx.float() + 8192.0).sum())
-    return ms, alg, float(ctx.float().mean())
 
 
 def ncu_traffic() -> dict:
@@ -217,42 +198,6 @@ def _graph_ms(fn, launches: int, iters: int = 3):
     return sorted(times)[len(times) // 2]
 
 
-def time_gemm_kernel(talker_runner, streams: int):
-    """The weight-streaming GEMM (gemm_stream_kernel) as the talker runs it: the 4 projections of every layer at
-    M = streams, over the model's own packed weights (2.8 GB, far larger than L2), with the production epilogues
-    and programmatic dependent launch.  Returns (ms per launch, algorithmic bytes per launch, launches)."""
-    import torch
-    import nano_qwen3tts_vllm_b200._native as nat
-    from nano_qwen3tts_vllm_b200.layers.linear import RowNorm, linear, linear_residual, linear_silu_mul
-    r = talker_runner
-    c = r.stack_config
-    dev = r.device
-    layers = r.model.model.layers if hasattr(r.model, "model") and hasattr(r.model.model, "layers") else None
-    if layers is None:
-        layers = [m for m in r.model.modules() if m.__class__.__name__ == "Qwen3TTSDecoderLayer"]
-    m = streams
-    resid = (torch.randn(m, c.hidden_size, device=dev) * 0.5).to(torch.bfloat16)
-    attn = (torch.randn(m, c.q_size, device=dev) * 0.5).to(torch.bfloat16)
-    eps, rnd = c.rms_norm_eps, nat.ROUND_EAGER
-
-    def launches():
-        x = resid.clone()
-        _, ssq = linear_residual(attn, layers[0].self_attn.o_proj.weight, x, out=x, want_ssq=True)
-        for layer in layers:
-            linear(x, layer.self_attn.qkv_proj.weight, norm=RowNorm(layer.input_layernorm.weight, ssq, eps, rnd))
-            _, ssq = linear_residual(attn, layer.self_attn.o_proj.weight, x, out=x, want_ssq=True)
-            act = linear_silu_mul(x, layer.mlp.gate_up_proj.weight, rnd,
-                                  norm=RowNorm(layer.post_attention_layernorm.weight, ssq, eps, rnd))
-            _, ssq = linear_residual(act, layer.mlp.down_proj.weight, x, out=x, want_ssq=True)
-    n = 4 * len(layers) + 1
-    ms = _graph_ms(launches, n)
-    w_bytes = 2.0 * (c.hidden_size * (c.q_size + 2 * c.kv_size) + c.q_size * c.hidden_size + 3 * c.hidden_size * c.intermediate_size)
-    io_bytes = 2.0 * m * (c.hidden_size + (c.q_size + 2 * c.kv_size) + c.q_size + c.hidden_size + c.hidden_size
-                          + c.intermediate_size + c.intermediate_size + c.hidden_size)
-    alg = (w_bytes + io_bytes) / 4.0                     # average over the 4 projections of a layer
-    return ms, alg, n
-
-
 def time_attention_long(device, streams: int = 64, ctx_len: int = 4096, layers: int = 3):
     """paged_attn_kernel at the north-star shape (BASELINE configs[3]: ~4k-token KV): `streams` sequences of `ctx_len`
     cached tokens, scattered pages, `layers` launches over different caches (each 2 x streams x ctx_len x 2 KiB)."""
@@ -277,14 +222,24 @@ def time_attention_long(device, streams: int = 64, ctx_len: int = 4096, layers: 
     return ms, float(streams * (4096.0 * ctx_len + 8192.0))
 
 
-def run_device_loop(talker, predictor, mc, streams, steps, warmup, sampler: ClockSampler | None, dist_barrier=None):
+def run_device_loop(talker, predictor, mc, streams, steps, warmup, sampler: ClockSampler | None, dist_barrier=None,
+                    prompt_len: int = PROMPT_LEN, prefill_ms: list | None = None):
     import torch
     import nano_qwen3tts_vllm_b200._native as nat
     from nano_qwen3tts_vllm_b200.engine.frame_loop import DeviceFrameLoop
     dev = talker.model_runner.device
-    loop = DeviceFrameLoop(talker.model_runner, predictor.model_runner, streams, steps + warmup + 4, PROMPT_LEN)
-    prompts, pad = synthetic_prompts(streams, mc.talker.hidden_size, pinned=False)
-    loop.start([p[0].to(dev) for p in prompts], pad.to(dev))
+    loop = DeviceFrameLoop(talker.model_runner, predictor.model_runner, streams, steps + warmup + 4, prompt_len)
+    prompts, pad = synthetic_prompts(streams, mc.talker.hidden_size, pinned=False, prompt_len=prompt_len)
+    prompts_dev, pad_dev = [p[0].to(dev) for p in prompts], pad.to(dev)
+    loop.start(prompts_dev, pad_dev)
+    if prefill_ms is not None:                 # the packed varlen prefill of all streams, timed warm (second run)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        loop.start(prompts_dev, pad_dev)
+        e1.record()
+        torch.cuda.synchronize()
+        prefill_ms.append(e0.elapsed_time(e1))
     n0 = nat.launch_count()
     loop.capture()
     # capture() runs one warm-up frame eagerly and records one: half of the delta is one frame
@@ -474,34 +429,107 @@ def main():
 
     line = None
     if rank == 0:
+        import bench_kernels as BK
         peak, peak_src = peaks()
-        att_ms, att_alg, mean_ctx = time_attention_kernel(talker.model_runner, loop)
-        gemm_ms, gemm_alg, gemm_n = time_gemm_kernel(talker.model_runner, a.streams)
+        tpeak, tpeak_src = tensor_peak()
+        ctx_now = loop.seq_lens.to(torch.int32)                   # context lengths at the end of the timed run
+        mean_ctx = float(ctx_now.float().mean())
+        gemm_ms, gemm_alg, gemm_n = BK.gemm_stack(talker.model_runner, a.streams)
+        pg_ms, pg_alg, pg_n = BK.gemm_stack(predictor.model_runner, a.streams)
+        pg2_ms, pg2_alg, _ = BK.gemm_stack(predictor.model_runner, 2 * a.streams)
+        att_ms, att_alg = BK.decode_attention(a.streams, ctx_now, device, layers=8)
+        a512_ms, a512_alg = BK.decode_attention(64, 512, device, layers=6)
+        a4k_ms, a4k_alg = BK.decode_attention(64, 4096, device, layers=3)
         long_ms, long_alg = time_attention_long(device)
+        pf_ms, pf_flops = BK.prefill_attention([4096], device)
+        st_ms, st_alg = BK.kv_store(4096, device)
+        sm_ms, sm_alg = BK.sampler(a.streams, mc.predictor.vocab_size, device)
         lens_sum = float((loop.seq_lens - 1).sum())
         step_bytes = frame_bytes(mc, lens_sum)
         traffic = ncu_traffic()
-        att_gbs, gemm_gbs, long_gbs = att_alg / att_ms / 1e6, gemm_alg / gemm_ms / 1e6, long_alg / long_ms / 1e6
-        # the dominant kernel of the frame by time share (profiles/*_launches_summary.txt): the weight-streaming GEMM
-        roofline = {"kernel": "gemm_stream_kernel (qkv / o / gate_up / down projections, tcgen05 + TMEM)", "bound": "hbm",
-                    "achieved": round(gemm_gbs, 1), "peak": peak, "unit": "GB/s", "frac": round(gemm_gbs / peak, 4),
-                    "traffic": traffic.get("gemm_stream_kernel"), "traffic_note": traffic.get("_gemm_stream_kernel"),
-                    "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": gemm_alg, "launch_ms": round(gemm_ms, 5), "launches_timed": gemm_n,
-                    "how": f"CUDA events around one graph of the talker's {gemm_n} projection launches at M={a.streams} over the "
-                           "model's own weights (2.8 GB >> L2), production epilogues + PDL; bytes = 2*(K*N + M*K + M*N) "
-                           "averaged over the 4 projections of a layer"}
+
+        def hbm(kernel, ms_, alg_, how, **extra):
+            g = alg_ / ms_ / 1e6
+            d = {"kernel": kernel, "bound": "hbm", "achieved": round(g, 1), "peak": peak, "unit": "GB/s",
+                 "frac": round(g / peak, 4), "traffic": None, "algorithmic_bytes_per_launch": alg_,
+                 "launch_ms": round(ms_, 5), "how": how}
+            d.update(extra)
+            return d
+        # the dominant kernel of the frame by time share (profiles/*_launches_summary.txt, tools/pass_ablation.py:
+        # ~82 % of the frame): the weight-streaming GEMM
+        roofline = hbm("gemm_stream_kernel (qkv / o / gate_up / down projections of the talker, tcgen05 + TMEM)", gemm_ms, gemm_alg,
+                       f"CUDA events around one graph of the talker's {gemm_n} projection launches at M={a.streams} over the "
+                       "model's own weights (2.8 GB >> L2), production epilogues + PDL; bytes = 2*(K*N + M*K + M*N) "
+                       "averaged over the 4 projections of a layer",
+                       traffic=traffic.get("gemm_stream_kernel"), traffic_note=traffic.get("_gemm_stream_kernel"),
+                       peak_source=peak_src, launches_timed=gemm_n)
         roofline_kernels = [
-            {"kernel": "paged_attn_kernel<2,false> (+ attn_combine_kernel when split-KV), bench contexts", "bound": "hbm",
-             "achieved": round(att_gbs, 1), "peak": peak, "unit": "GB/s", "frac": round(att_gbs / peak, 4),
-             "traffic": None, "algorithmic_bytes_per_launch": att_alg, "launch_ms": round(att_ms, 5),
-             "mean_context": round(mean_ctx, 1),
-             "how": "graph of 28 per-layer launches at the bench's end-of-run context lengths; bytes = sum_b(4096*L_b + 8192)"},
-            {"kernel": "paged_attn_kernel<2,false>, 64 sequences x 4096 cached tokens (BASELINE configs[3] KV length)",
-             "bound": "hbm", "achieved": round(long_gbs, 1), "peak": peak, "unit": "GB/s", "frac": round(long_gbs / peak, 4),
-             "traffic": traffic.get("paged_attn_kernel"), "traffic_note": traffic.get("_paged_attn_kernel"),
-             "algorithmic_bytes_per_launch": long_alg,
-             "launch_ms": round(long_ms, 5), "how": "graph of 3 launches over different 1 GiB caches, scattered pages"}]
+            hbm("gemm_stream_kernel, code-predictor shapes (H 1024, I 3072), decode pass", pg_ms, pg_alg,
+                f"graph of the predictor's {pg_n} projection launches at M={a.streams} (5 layers x 4; 31 MB of weights per "
+                "layer: latency-bound launches)"),
+            hbm("gemm_stream_kernel, code-predictor shapes, 2-token prefill pass", pg2_ms, pg2_alg,
+                f"same at M={2 * a.streams} rows"),
+            hbm("fused_decode_attn_kernel (qk-norm + M-RoPE + KV write + paged GQA attention + combine), bench contexts",
+                att_ms, att_alg, "graph of 8 launches over different caches at the run's end-of-run context lengths; "
+                "bytes = sum_b(4096*L_b + 8192)", mean_context=round(mean_ctx, 1)),
+            hbm("fused_decode_attn_kernel, 64 sequences x 512 cached tokens", a512_ms, a512_alg, "graph of 6 launches, cold caches",
+                traffic=traffic.get("fused_decode_attn_kernel"), traffic_note=traffic.get("_fused_decode_attn_kernel")),
+            hbm("fused_decode_attn_kernel, 64 sequences x 4096 cached tokens (BASELINE configs[3] KV length)", a4k_ms, a4k_alg,
+                "graph of 3 launches over different 1 GiB caches, scattered pages"),
+            hbm("paged_attn_kernel<2,false> (stand-alone a2 entry point), 64 sequences x 4096 cached tokens", long_ms, long_alg,
+                "graph of 3 launches over different 1 GiB caches, scattered pages",
+                traffic=traffic.get("paged_attn_kernel"), traffic_note=traffic.get("_paged_attn_kernel")),
+            hbm("store_kvcache_kernel (stand-alone a1 entry point), 4096 tokens", st_ms, st_alg,
+                "graph of 8 launches; bytes = tokens * 1024 * 2 B * 2 (K, V) * 2 (read + write)"),
+            hbm(f"topk_sample_row_kernel, [{a.streams}, {mc.predictor.vocab_size}] bf16 logits, top-k 50", sm_ms, sm_alg,
+                "graph of 16 launches; bytes = the logits (latency-bound: one CTA per row)"),
+            {"kernel": "prefill_attn_tc_kernel (tcgen05 128x128 tiles, TMEM), one 4096-token sequence (BASELINE configs[3])",
+             "bound": "tensor", "achieved": round(pf_flops / pf_ms / 1e9, 1), "peak": tpeak, "unit": "TFLOP/s",
+             "frac": round(pf_flops / pf_ms / 1e9 / tpeak, 4), "traffic": None, "flops_per_launch": pf_flops,
+             "launch_ms": round(pf_ms, 5), "peak_source": tpeak_src,
+             "how": "graph of 4 launches over different QKV buffers; flops = 4*heads*hd*n(n+1)/2 (causal half)"}]
+        ref_kernels = None
+        if not a.no_reference_kernels:
+            ref_kernels = {"about": "the kernels the reference runs for the same ops, timed the same way on this GPU "
+                                    "(bench_kernels.py); library code, measured only"}
+
+            def leg(name, fn):
+                try:
+                    ref_kernels[name] = fn()
+                except Exception as e:                                   # a missing library must not void the bench line
+                    ref_kernels[name] = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+
+            def cublas(runner, m, ours_ms):
+                ms_, alg_, n_ = BK.gemm_stack(runner, m, impl="cublas")
+                return {"library": "cuBLAS via F.linear (layers/linear.py:72-73)", "launch_ms": round(ms_, 5),
+                        "GBps": round(alg_ / ms_ / 1e6, 1), "ours_launch_ms": round(ours_ms, 5), "speedup": round(ms_ / ours_ms, 3),
+                        "note": "plain products only: the reference's separate RMSNorm / residual / SiLU*mul launches are fused "
+                                "into ours and not counted on the library side"}
+
+            def flash_dec(b_, ctx_, layers_, ours_ms):
+                ms_, alg_ = BK.decode_attention(b_, ctx_, device, layers=layers_, impl="flash")
+                return {"library": "flash_attn_with_kvcache (layers/attention.py:92-95)", "launch_ms": round(ms_, 5),
+                        "GBps": round(alg_ / ms_ / 1e6, 1), "ours_launch_ms": round(ours_ms, 5), "speedup": round(ms_ / ours_ms, 3),
+                        "note": "attention only: the reference's separate q/k norm, RoPE and Triton KV store launches are "
+                                "inside ours and not counted on the library side"}
+
+            def flash_pre():
+                ms_, fl_ = BK.prefill_attention([4096], device, impl="flash")
+                return {"library": "flash_attn_varlen_func (layers/attention.py:78-91)", "launch_ms": round(ms_, 5),
+                        "TFLOPs": round(fl_ / ms_ / 1e9, 1), "ours_launch_ms": round(pf_ms, 5), "speedup": round(ms_ / pf_ms, 3)}
+
+            def triton_store():
+                ms_, alg_ = BK.kv_store(4096, device, impl="triton")
+                return {"library": "Triton store_kvcache restated (layers/attention.py:10-41)", "launch_ms": round(ms_, 5),
+                        "GBps": round(alg_ / ms_ / 1e6, 1), "ours_launch_ms": round(st_ms, 5), "speedup": round(ms_ / st_ms, 3)}
+            leg(f"gemm_talker_M{a.streams}", lambda: cublas(talker.model_runner, a.streams, gemm_ms))
+            leg(f"gemm_predictor_M{a.streams}", lambda: cublas(predictor.model_runner, a.streams, pg_ms))
+            leg(f"gemm_predictor_M{2 * a.streams}", lambda: cublas(predictor.model_runner, 2 * a.streams, pg2_ms))
+            leg("decode_attention_bench_contexts", lambda: flash_dec(a.streams, ctx_now, 8, att_ms))
+            leg("decode_attention_64x512", lambda: flash_dec(64, 512, 6, a512_ms))
+            leg("decode_attention_64x4096", lambda: flash_dec(64, 4096, 3, a4k_ms))
+            leg("prefill_attention_4096", flash_pre)
+            leg("kv_store_4096", triton_store)
         step_roof = {"bound": "hbm", "achieved": round(step_bytes / (ms_per_step / 1e3) / 1e9, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(step_bytes / (ms_per_step / 1e3) / 1e9 / peak, 4), "algorithmic_bytes_per_step": step_bytes,
                      "note": "whole frame: weights streamed once per pass (talker + 15 predictor passes) + talker KV"}
@@ -510,9 +538,13 @@ def main():
                 "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                 "config": workload_config(a, a.streams), "clocks": clocks,
                 "rtf_per_stream": round(ms_per_step / 1e3 * FRAME_HZ, 5),
+                "rounding": "eager (the reference source op by op: what its CPU path computes; ROUND_FUSED = its inductor GPU "
+                            "path is the other mode, same kernels and launch count)",
                 "roofline": roofline, "roofline_kernels": roofline_kernels, "step_roofline": step_roof,
                 "gpu_launches": int(lib_per_frame * a.steps),
                 "launches_per_step": {"libb200tts": int(lib_per_frame), "note": "includes the tcgen05 GEMMs; exponential_ noise and small torch copies are extra"}}
+        if ref_kernels is not None:
+            line["reference_kernels"] = ref_kernels
     # ---- end to end through the step API with host buffers
     if not a.no_e2e:
         e2e_fps, h2d, d2h, _ = run_e2e(talker, predictor, mc, a.streams, a.e2e_steps)
@@ -524,7 +556,7 @@ def main():
             line["e2e"] = {"value": round(e2e_fps, 1), "unit": "frames/s", "h2d_bytes_per_step": int(h2d),
                            "d2h_bytes_per_step": int(d2h), "steps": a.e2e_steps,
                            "api": "TalkerLLM.add_request/step_with_outputs + PredictorLLM.add_request/step, pinned host tensors"}
-    # ---- other stream counts (BASELINE configs[1], [2]) on rank 0, short runs
+    # ---- other stream counts (BASELINE configs[1], [2], [4]) on rank 0, short runs
     if rank == 0 and world == 1 and a.also_streams:
         others = {}
         for b in [int(x) for x in a.also_streams.split(",") if x]:
@@ -533,11 +565,42 @@ def main():
             talker.exit(); predictor.exit()
             del loop, talker, predictor
             torch.cuda.empty_cache()
-            mc, talker, predictor = build_engines(a.model, b, total_frames, device)
-            loop, ms_b, _, _ = run_device_loop(talker, predictor, mc, b, a.steps, a.warmup, None)
-            others[str(b)] = {"frames_per_s": round(b * a.steps / (ms_b / 1e3), 1), "ms_per_step": round(ms_b / a.steps, 4),
-                              "rtf_per_stream": round(ms_b / a.steps / 1e3 * FRAME_HZ, 5)}
+            steps_b = a.steps if b <= 64 else max(16, a.steps // 2)
+            try:
+                mc, talker, predictor = build_engines(a.model, b, steps_b + a.warmup + 8, device)
+                loop, ms_b, _, _ = run_device_loop(talker, predictor, mc, b, steps_b, a.warmup, None)
+                others[str(b)] = {"frames_per_s": round(b * steps_b / (ms_b / 1e3), 1), "ms_per_step": round(ms_b / steps_b, 4),
+                                  "rtf_per_stream": round(ms_b / steps_b / 1e3 * FRAME_HZ, 5), "steps": steps_b}
+            except Exception as e:
+                others[str(b)] = {"failed": f"{type(e).__name__}: {e}"[:300]}
+                mc, talker, predictor = build_engines(a.model, 1, 16, device)
+                loop = None
         line["other_workloads"] = others
+    # ---- BASELINE configs[3]: voice-clone ICL, ~4k-token prompts (varlen prefill + decode), 8 streams
+    if rank == 0 and world == 1 and not a.no_icl:
+        talker.exit(); predictor.exit()
+        del loop, talker, predictor
+        torch.cuda.empty_cache()
+        try:
+            b, plen, frames = 8, 4096, 256
+            mc, talker, predictor = build_engines(a.model, b, frames + 16, device, prompt_len=plen)
+            pre = []
+            loop, ms_b, _, _ = run_device_loop(talker, predictor, mc, b, frames, 4, None, prompt_len=plen, prefill_ms=pre)
+            t = mc.talker
+            lin = 2.0 * b * plen * t.num_hidden_layers * (t.hidden_size * (t.q_size + 2 * t.kv_size) + t.q_size * t.hidden_size
+                                                          + 3 * t.hidden_size * t.intermediate_size)
+            att = b * t.num_hidden_layers * 4.0 * t.num_attention_heads * t.head_dim * plen * (plen + 1) / 2
+            line["icl_workload"] = {
+                "workload": f"BASELINE configs[3]: {b} streams x {plen}-token prompt (packed varlen prefill: tcgen05 prefill "
+                            f"attention + cuBLAS projections above {os.environ.get('B2TTS_GEMM_NATIVE_MAX_M', '512')} rows), "
+                            f"then {frames} frames of decode at ~{plen + frames // 2}-token contexts",
+                "prefill_ms": round(pre[0], 3), "prefill_tokens_per_s": round(b * plen / (pre[0] / 1e3), 1),
+                "prefill_TFLOPs": round((lin + att) / (pre[0] / 1e3) / 1e12, 1),
+                "decode_frames_per_s": round(b * frames / (ms_b / 1e3), 1), "decode_ms_per_step": round(ms_b / frames, 4),
+                "rtf_per_stream": round(ms_b / frames / 1e3 * FRAME_HZ, 5)}
+        except Exception as e:
+            line["icl_workload"] = {"failed": f"{type(e).__name__}: {e}"[:300]}
+            mc, talker, predictor = None, None, None
     if rank == 0 and not a.no_cpu_baseline and world == 1:
         fps, cores, what, dt = cpu_oracle_frames(a.model, a.cpu_streams or a.streams, 2, 1, budget_s=25.0)
         line["cpu_baseline"] = {"value": round(fps, 3), "unit": "frames/s", "cores": cores, "kind": "port", "sample": what}

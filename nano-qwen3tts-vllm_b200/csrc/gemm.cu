@@ -410,11 +410,23 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   // the reduce reads it conflict-free with lanes along m).  Feature rows of one owner are contiguous,
   // so ONE bulk async copy per peer (shared::cta -> shared::cluster through the TMA unit) moves the
   // slice into the owner's receive buffer recv[src][row][mpad+4] and completes on the OWNER's
-  // mbarrier: no cluster barrier on the critical path, no per-thread remote stores.
+  // mbarrier: no cluster barrier on the critical path, no per-thread remote stores.  (Tried and removed:
+  // st.async straight from the TMEM registers into the peers' buffers - no staging, no proxy fence, no closing
+  // cluster barrier, yet 1.2 us slower per launch: 2048 16-byte remote stores per CTA cost more than 8 bulk copies.)
   const int rows_own = G_BN / S;
   const int rstride = mpad + 4;
   float* stg = reinterpret_cast<float*>(smem);
   const float* red = (S > 1) ? recv : stg;
+  // the first epilogue item of every thread reads a residual / bias vector: request it before the exchange wait
+  const int groups = rows_own >> 3;
+  const int n0 = tile * G_BN + rank * rows_own;
+  const int items = m_loc * groups;
+  uint4 pre = make_uint4(0, 0, 0, 0);
+  if ((int)threadIdx.x < items) {
+    const int g8 = threadIdx.x / m_loc, m = threadIdx.x - g8 * m_loc;
+    if (p.epilogue == B2TTS_GEMM_RESIDUAL) pre = ldg_v4(p.res + (int64_t)(row0 + m) * p.res_stride + n0 + g8 * 8);
+    else if (p.epilogue == B2TTS_GEMM_BIAS && p.bias) pre = ldg_v4(p.bias + n0 + g8 * 8);
+  }
   if (warp >= 2) {
     const int q = warp & 3;                     // TMEM lane quarter this warp may read
     const int f = q * 32 + lane;                // feature row of the tile held by this thread
@@ -444,7 +456,6 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     if (S > 1) {
       fence_proxy_async();                      // generic-proxy stores -> visible to the bulk copies
       bar_sync_producers();
-      if (threadIdx.x == 64) G_TRACE(5);
       if (threadIdx.x == 64) {
         const uint32_t chunk = (uint32_t)(rows_own * rstride * 4);
         const uint32_t recv_local = smem_u32(recv) + (uint32_t)rank * chunk;
@@ -456,6 +467,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
         }
       }
     }
+    if (threadIdx.x == 64) G_TRACE(5);
   }
   tc_fence_before();
   if (S > 1) {
@@ -470,9 +482,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   // One item = (batch row m, 8 consecutive features of this CTA's slice); returns the sum of squares
   // of the 8 bf16 values it stored.
   {
-    const int groups = rows_own >> 3;
-    const int n0 = tile * G_BN + rank * rows_own;
-    auto item = [&](int m, int g8) -> float {
+    auto item = [&](int m, int g8, bool have_pre) -> float {
       float acc[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[j] = 0.f;
@@ -497,12 +507,12 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
         return 0.f;
       }
       if (p.epilogue == B2TTS_GEMM_BIAS && p.bias) {
-        const uint4 bw = ldg_v4(p.bias + n);
+        const uint4 bw = have_pre ? pre : ldg_v4(p.bias + n);
         acc[0] += bf16lo(bw.x); acc[1] += bf16hi(bw.x); acc[2] += bf16lo(bw.y); acc[3] += bf16hi(bw.y);
         acc[4] += bf16lo(bw.z); acc[5] += bf16hi(bw.z); acc[6] += bf16lo(bw.w); acc[7] += bf16hi(bw.w);
       } else if (p.epilogue == B2TTS_GEMM_RESIDUAL) {
         // bf16(residual + bf16(x W^T)): the projection output is rounded before the add
-        const uint4 rw = ldg_v4(p.res + (int64_t)(row0 + m) * p.res_stride + n);
+        const uint4 rw = have_pre ? pre : ldg_v4(p.res + (int64_t)(row0 + m) * p.res_stride + n);
         acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
         acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
         acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
@@ -525,14 +535,14 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       const int slots = (p.n / G_BN) * S;
       for (int m = threadIdx.x; m < m_loc; m += G_THREADS) {
         float q = 0.f;
-        for (int g8 = 0; g8 < groups; ++g8) q += item(m, g8);
+        for (int g8 = 0; g8 < groups; ++g8) q += item(m, g8, g8 == 0);
         p.ssq_out[(int64_t)(row0 + m) * slots + tile * S + rank] = q;
       }
     } else {
-      const int items = m_loc * groups;
+      // item it = (feature group g8 = it / m_loc, batch row m = it % m_loc): lanes along m read red conflict-free
       for (int it = threadIdx.x; it < items; it += G_THREADS) {
-        const int g8 = it / m_loc;                 // lanes along m: conflict-free reads of red
-        item(it - g8 * m_loc, g8);
+        const int g8 = it / m_loc;
+        item(it - g8 * m_loc, g8, it == (int)threadIdx.x);
       }
     }
   }

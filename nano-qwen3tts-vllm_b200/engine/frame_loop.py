@@ -311,7 +311,11 @@ class StepApiFrameLoop:
     process, as in the reference (interface.py:1276-1286)."""
 
     def __init__(self, talker_llm, predictor_llm, tts_pad_embed: torch.Tensor, ignore_eos: bool = True,
-                 codec_eos: int = 2150):
+                 codec_eos: int = 2150, batched: bool = True):
+        """``batched``: feed each engine with ONE ``add_requests`` call per frame (one pinned buffer, one host->device
+        copy) and read the talker's hidden states as one tensor; False = one ``add_request`` per stream, exactly the
+        reference's call pattern.  Same bytes across PCIe, same results."""
+        self.batched = batched
         self.talker, self.predictor = talker_llm, predictor_llm
         self.tmodel = talker_llm.model_runner.model
         self.pmodel = predictor_llm.model_runner.model
@@ -324,6 +328,30 @@ class StepApiFrameLoop:
         self.d2h_bytes = 0
         self.active: list[str] = []
         self.frames: dict[str, list[list[int]]] = {}
+        self._pins: dict[str, torch.Tensor] = {}
+        self.timing: dict[str, float] | None = None       # set to {} to accumulate wall time per phase (tools/e2e_profile.py)
+
+    def _mark(self, name: str, t0: float) -> float:
+        import time
+        t1 = time.perf_counter()
+        if self.timing is not None:
+            self.timing[name] = self.timing.get(name, 0.0) + (t1 - t0)
+        return t1
+
+    def _pinned(self, name: str, shape, dtype) -> torch.Tensor:
+        """A reusable pinned host buffer (``pin_memory()`` per frame would page-lock fresh memory every time)."""
+        n = 1
+        for d in shape:
+            n *= d
+        buf = self._pins.get(name)
+        if buf is None or buf.numel() < n or buf.dtype != dtype:
+            buf = self._pins[name] = torch.empty(max(n, 1), dtype=dtype).pin_memory()
+        return buf[:n].view(*shape)
+
+    def _to_host(self, name: str, t: torch.Tensor) -> torch.Tensor:
+        out = self._pinned(name, t.shape, t.dtype)
+        out.copy_(t, non_blocking=True)
+        return out
 
     def add_streams(self, prompts: list[torch.Tensor]):
         """prompts: host bf16 [1, T, H] each.  Queues the prefill; ``step_frame`` runs it."""
@@ -337,6 +365,8 @@ class StepApiFrameLoop:
     def step_frame(self) -> int:
         """One talker step for every active stream + the predictor burst + next-input assembly.
         Returns the number of frames completed."""
+        import time
+        t = time.perf_counter()
         outs = []
         while len(outs) < len(self.active):
             _, _, outs_all = self.talker.step_with_outputs()
@@ -345,9 +375,13 @@ class StepApiFrameLoop:
             outs += outs_all
         if not outs:
             return 0
+        t = self._mark("talker.step_with_outputs", t)
         rids = [o[0] for o in outs]
         code0 = [o[2][-1] for o in outs]
-        hidden_host = torch.stack([o[3] for o in outs], 0).float().cpu()       # protocol.py:78-91 (fp32 numpy)
+        last = getattr(self.talker, "last_step", None)
+        whole = self.batched and last is not None and len(last[0]) == len(outs) and last[2].shape[0] == len(outs)
+        hidden_dev = last[2] if whole else torch.stack([o[3] for o in outs], 0)
+        hidden_host = self._to_host("hidden", hidden_dev.float())               # protocol.py:78-91 (fp32 numpy)
         self.d2h_bytes += hidden_host.numel() * 4 + 8 * len(outs)
         live = [i for i, c in enumerate(code0) if self.ignore_eos or c != self.codec_eos]
         for i, rid in enumerate(rids):
@@ -359,29 +393,46 @@ class StepApiFrameLoop:
             return 0
         # predictor input = [hidden, embed(code0)] per stream                   interface.py:1242-1252
         c0 = torch.tensor([code0[i] for i in live], dtype=torch.int64)
-        emb0 = nat.gather_rows(self.tmodel.model.codec_embedding.weight, c0.to(self.dev))
-        pin_host = torch.stack([hidden_host[live].to(BF16), emb0.cpu()], 1).pin_memory()       # [n, 2, H]
+        emb0 = nat.gather_rows(self.tmodel.model.codec_embedding.weight, c0.to(self.dev, non_blocking=True))
+        emb0_host = self._to_host("emb0", emb0)
+        torch.cuda.current_stream().synchronize()                               # hidden + embed(code0) are on the host
+        pin_host = self._pinned("pred_in", (len(live), 2, hidden_host.shape[-1]), BF16)        # [n, 2, H]
+        pin_host[:, 0].copy_(hidden_host if len(live) == len(outs) else hidden_host[live])
+        pin_host[:, 1].copy_(emb0_host)
         self.d2h_bytes += emb0.numel() * 2
-        for j, i in enumerate(live):
-            self.h2d_bytes += pin_host[j].numel() * 2
-            self.predictor.add_request([pin_host[j:j + 1]], self.p_sp, request_id=rids[i])
+        self.h2d_bytes += pin_host.numel() * 2
+        t = self._mark("hidden + embed(code0) to host, pack", t)
+        if self.batched:
+            self.predictor.add_requests(pin_host, self.p_sp, [rids[i] for i in live])
+        else:
+            for j, i in enumerate(live):
+                self.predictor.add_request([pin_host[j:j + 1]], self.p_sp, request_id=rids[i])
+        t = self._mark("predictor.add_requests", t)
         done: dict[str, list[int]] = {}
         while len(done) < len(live):
             fin, _ = self.predictor.step()
             for rid, _, codes in fin:
                 done[rid] = codes
+        t = self._mark("predictor.step (burst)", t)
         self.d2h_bytes += 8 * 15 * len(live)
-        codes16 = torch.tensor([[code0[i]] + done[rids[i]] for i in live], dtype=torch.int64)
-        for row, i in zip(codes16.tolist(), live):
-            self.frames[rids[i]].append(row)
+        rows = [[code0[i]] + done[rids[i]] for i in live]
+        codes16 = torch.tensor(rows, dtype=torch.int64)
         # next talker input                                                      interface.py:1276-1290
         nxt = nat.codec_embed_sum(self.tmodel.model.codec_embedding.weight, self.pmodel.model.codec_embedding,
-                                  codes16.to(self.dev), extra=self.extra)
-        nxt_host = nxt.cpu().pin_memory()
+                                  codes16.to(self.dev, non_blocking=True), extra=self.extra)
+        nxt_host = self._to_host("next_in", nxt)
+        for row, i in zip(rows, live):                                          # while the sum is on its way back
+            self.frames[rids[i]].append(row)
+        torch.cuda.current_stream().synchronize()
         self.h2d_bytes += codes16.numel() * 8 + nxt_host.numel() * 2
         self.d2h_bytes += nxt_host.numel() * 2
-        for j, i in enumerate(live):
-            self.talker.add_request([nxt_host[j:j + 1].unsqueeze(0)], self.t_sp, request_id=rids[i])
+        t = self._mark("frames bookkeeping + embed sum to host", t)
+        if self.batched:
+            self.talker.add_requests(nxt_host.unsqueeze(1), self.t_sp, [rids[i] for i in live])
+        else:
+            for j, i in enumerate(live):
+                self.talker.add_request([nxt_host[j:j + 1].unsqueeze(0)], self.t_sp, request_id=rids[i])
+        self._mark("talker.add_requests", t)
         return len(live)
 
     def close(self):

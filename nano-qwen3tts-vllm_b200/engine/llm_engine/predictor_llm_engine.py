@@ -25,6 +25,34 @@ class PredictorLLMEngine(LLMEngine):
                 self.scheduler.request_id_to_seq[request_id] = seq
             self.scheduler.add(seq)
 
+    def add_requests(self, inputs_embeds: torch.Tensor, sampling_params: SamplingParams, request_ids: list[str | None]):
+        """Batched ``add_request``: ``inputs_embeds`` [n, 2, H] (host, ideally pinned) crosses PCIe as ONE copy; request
+        i gets row i.  Same queueing as n single calls."""
+        dev = self._to_device(inputs_embeds)
+        for i, rid in enumerate(request_ids):
+            seq = PredictorSequence([], input_embeds=dev[i:i + 1], sampling_params=sampling_params, generation_steps=0,
+                                    request_id=rid)
+            seq.batch_src = (dev, i)
+            if rid is not None:
+                self.scheduler.request_id_to_seq[rid] = seq
+            self.scheduler.add(seq)
+
+    burst = True          # whole-request graphs (PredictorModelRunner.run_burst); False = step by step as the reference
+
+    def _step_burst(self, seqs):
+        """Every scheduled sequence is a fresh 2-row request: one graph replay yields all of its codes."""
+        n_codes = self.model_runner.burst_codes()
+        codes = self.model_runner.call("run_burst", seqs)                    # replay queued; the GPU is busy from here
+        for s in seqs:                                                       # bookkeeping that needs no code values
+            s.num_tokens += n_codes
+            s.generation_steps += n_codes
+            self.scheduler._finish(s)
+        toks = codes.tolist()                                                # the one synchronisation of the burst
+        for s, row in zip(seqs, toks):
+            s.token_ids.extend(row)
+            s.last_token = row[-1]
+        return [(s.request_id, s.seq_id, s.completion_token_ids) for s in seqs], sum(2 for _ in seqs)
+
     # The predictor never stops on an EOS id (config.eos stays -1: no tokenizer, predictor_llm_engine.py:33-66 of the
     # reference finishes on max_tokens), so the sampled codes are only needed on the host when a sequence finishes.
     # With ``defer_tokens`` the per-step ``.tolist()`` of the reference (one PCIe round trip and one stream
@@ -84,6 +112,8 @@ class PredictorLLMEngine(LLMEngine):
         seqs, is_prefill = self.scheduler.schedule()
         if not seqs:
             return [], 0
+        if is_prefill and self.burst and self.scheduler.eos < 0 and self.model_runner.burst_ok(seqs):
+            return self._step_burst(seqs)
         if self.defer_tokens and self.scheduler.eos < 0 and all(not s.token_ids or hasattr(s, "_deferred") for s in seqs):
             self._step_deferred(seqs, is_prefill)
             for s in seqs:

@@ -23,11 +23,29 @@ class TalkerLLMEngine(LLMEngine):
         for emb, sp in zip(inputs_embeds, sampling_params):
             emb = self._to_device(emb)
             if request_id is not None and request_id in self.scheduler.request_id_to_seq:
-                self.scheduler.request_id_to_seq[request_id].decode_input_embeds = emb
+                seq = self.scheduler.request_id_to_seq[request_id]
+                seq.decode_input_embeds = emb
+                seq.batch_src = None
                 return
             seq = Sequence([], input_embeds=emb, sampling_params=sp, request_id=request_id)
             if request_id is not None:
                 self.scheduler.request_id_to_seq[request_id] = seq
+            self.scheduler.add(seq)
+
+    def add_requests(self, inputs_embeds: torch.Tensor, sampling_params: SamplingParams, request_ids: list[str | None]):
+        """Batched ``add_request`` for decode inputs (and equal-length prompts): ``inputs_embeds`` [n, T, H] (host,
+        ideally pinned) crosses PCIe as ONE copy; row i belongs to ``request_ids[i]``."""
+        dev = self._to_device(inputs_embeds)
+        known = self.scheduler.request_id_to_seq
+        for i, rid in enumerate(request_ids):
+            seq = known.get(rid) if rid is not None else None
+            if seq is not None:
+                seq.decode_input_embeds = dev[i]
+                seq.batch_src = (dev, i)
+                continue
+            seq = Sequence([], input_embeds=dev[i:i + 1], sampling_params=sampling_params, request_id=rid)
+            if rid is not None:
+                known[rid] = seq
             self.scheduler.add(seq)
 
     def _step(self):
@@ -36,6 +54,7 @@ class TalkerLLMEngine(LLMEngine):
             return None, 0, []
         token_ids, hidden = self.model_runner.call("run", seqs, is_prefill)
         self.scheduler.postprocess(seqs, token_ids, hidden)
+        self.last_step = (seqs, token_ids, hidden)      # the step's batch as a whole: hidden [n, H] on the device
         return seqs, (sum(len(s) for s in seqs) if is_prefill else -len(seqs)), seqs
 
     def step(self):

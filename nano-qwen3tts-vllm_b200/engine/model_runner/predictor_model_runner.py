@@ -6,8 +6,10 @@ from __future__ import annotations
 
 import torch
 
+from ... import _native as nat
+from ...layers.linear import linear
 from ...models.qwen3_tts_predictor import Qwen3TTSCodePredictorForCausalLM
-from ...utils.context import reset_context
+from ...utils.context import reset_context, set_context
 from ..sequence import PredictorSequence, Sequence  # noqa: F401  (re-exported like the reference)
 from .base import ModelRunner
 
@@ -32,6 +34,105 @@ class PredictorModelRunner(ModelRunner):
         d = self.layout.d
         emb = self.model.get_input_embeddings(d["last_tokens"][:rows], None, d["gen_steps"][:rows])
         return self.model(emb, d["positions"][:rows])
+
+    # ------------------------------------------------------------------ the whole burst as one graph (a13)
+    # A predictor request is always the same program: prefill of the 2 rows [talker hidden, embed(code0)], then one
+    # decode step per remaining codebook (interface.py:1242-1268 drives it step by step).  Nothing in it depends on
+    # the host, so prefill + 14 decode passes + the 15 samplers are captured ONCE per batch size and a request
+    # batch that fits the pattern costs one replay and one device->host read of its [n, 15] codes.
+    def capture_cudagraph(self):
+        super().capture_cudagraph()
+        self.capture_burst()
+
+    def burst_codes(self) -> int:
+        return self.stack_config.num_code_groups - 1
+
+    def burst_ok(self, seqs: list[Sequence]) -> bool:
+        if self.enforce_eager or not getattr(self, "burst_graphs", None) or len(seqs) > self.graph_bs[-1]:
+            return False
+        if self.top_k != self.burst_top_k:                                   # the sampler's k is baked into the graphs
+            self.capture_burst()
+        want = 2 + self.burst_codes()
+        return all(s.num_tokens == 2 and s.num_cached_tokens == 0 and s.generation_steps == 0 and not s.token_ids
+                   and s.max_tokens == want and len(s.block_table) == 1 for s in seqs)
+
+    def burst_body(self, bs: int) -> torch.Tensor:
+        """Static inputs: ``burst_x[:2 bs]`` (rows 2i, 2i+1 of sequence i), ``layout.d['block_tables'][:bs, 0]`` (the
+        sequence's KV page, -1 = padding row), ``layout.d['temperatures'][:bs]``.  Returns codes [15, bs]."""
+        model, d, page, n = self.model, self.layout.d, self.block_size, self.burst_codes()
+        vocab = self.stack_config.vocab_size
+        tables = d["block_tables"][:bs]
+        pg = tables[:, 0]
+        live = pg >= 0
+        base = pg * page
+        noise = self.burst_noise[:n * bs * vocab].view(n, bs, vocab)
+        noise.exponential_(1)
+        codes = self.burst_out[bs]
+        temps = d["temperatures"][:bs]
+        slots = torch.where(live.view(bs, 1), base.view(bs, 1) + self.burst_two, -1).view(-1).to(torch.int32)
+        set_context(True, self.burst_cu[:bs + 1], self.burst_cu[:bs + 1], 2, 2, slots, None, None)
+        qkv0 = model.model.layers[0].self_attn.qkv_proj.weight
+        h = model(self.burst_x[:2 * bs], self.burst_pos2[:2 * bs], head=0)
+        last = h.view(bs, 2, -1)[:, 1]
+        nat.topk_sample(linear(last, model.lm_head[0], nxt=qkv0), temps, noise[0], top_k=self.top_k, out=codes[0],
+                        embed_table=model.model.codec_embedding[0], embed_out=self.burst_emb[:bs])
+        for g in range(1, n):
+            set_context(False, slot_mapping=torch.where(live, base + (g + 1), -1).to(torch.int32),
+                        context_lens=torch.where(live, g + 2, 0).to(torch.int32), block_tables=tables,
+                        max_context_len=g + 2)
+            h = model(self.burst_emb[:bs], self.burst_posg[g][:bs], head=g)
+            last_pass = g == n - 1
+            nat.topk_sample(linear(h, model.lm_head[g], nxt=None if last_pass else qkv0), temps, noise[g], top_k=self.top_k,
+                            out=codes[g], embed_table=None if last_pass else model.model.codec_embedding[g],
+                            embed_out=None if last_pass else self.burst_emb[:bs])
+        reset_context()
+        return codes
+
+    @torch.inference_mode()
+    def capture_burst(self):
+        dev, n, mb = self.device, self.burst_codes(), self.graph_bs[-1]
+        ht = self.talker_config.hidden_size
+        self.burst_x = torch.zeros(2 * mb, ht, dtype=torch.bfloat16, device=dev)
+        self.burst_emb = torch.zeros(mb, ht, dtype=torch.bfloat16, device=dev)
+        self.burst_noise = torch.ones(n * mb * self.stack_config.vocab_size, dtype=torch.float32, device=dev)
+        self.burst_two = torch.tensor([0, 1], dtype=torch.int32, device=dev).view(1, 2)
+        self.burst_pos2 = torch.tensor([0, 1] * mb, dtype=torch.int64, device=dev)
+        self.burst_cu = (torch.arange(mb + 1, dtype=torch.int32, device=dev) * 2).contiguous()
+        self.burst_posg = [None] + [torch.full((mb,), g + 1, dtype=torch.int64, device=dev) for g in range(1, n)]
+        self.burst_out = {bs: torch.zeros(n, bs, dtype=torch.int64, device=dev) for bs in self.graph_bs}
+        self.burst_graphs: dict[int, torch.cuda.CUDAGraph] = {}
+        self.burst_top_k = self.top_k
+        h = self.layout.begin()
+        h["block_tables"][:] = -1
+        self.layout.upload()
+        for bs in reversed(self.graph_bs):
+            self.burst_body(bs)                                             # warm-up (packs lm_head images, lazy handles)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, self.graph_pool):
+                self.burst_body(bs)
+            self.burst_graphs[bs] = g
+        torch.cuda.synchronize()
+
+    @torch.inference_mode()
+    def run_burst(self, seqs: list[Sequence]) -> torch.Tensor:
+        """All codes of ``seqs`` (fresh 2-row requests, see ``burst_ok``): device tensor [n, 15]."""
+        n = len(seqs)
+        bs = self.pick_graph(n)
+        h = self.layout.begin()
+        h["block_tables"][:n, 0] = [s.block_table[0] for s in seqs]
+        h["block_tables"][n:bs, 0] = -1
+        h["temperatures"][:n] = [s.temperature for s in seqs]
+        h["temperatures"][n:bs] = 1.0
+        self.layout.upload()
+        src = getattr(seqs[0], "batch_src", None)
+        if src is not None and all(getattr(s, "batch_src", None) is not None and s.batch_src[0] is src[0]
+                                   and s.batch_src[1] == i for i, s in enumerate(seqs)):
+            self.burst_x[:2 * n].copy_(src[0][:n].reshape(2 * n, -1))        # one batched upload: already contiguous
+        else:
+            self.burst_x[:2 * n].copy_(torch.cat([s.input_embeds.reshape(2, -1) for s in seqs], 0))
+        self.burst_graphs[bs].replay()
+        return self.burst_out[bs][:, :n].t()
 
     @torch.inference_mode()
     def run_model(self, seqs: list[Sequence], is_prefill: bool, prev_tokens: torch.Tensor | None = None):

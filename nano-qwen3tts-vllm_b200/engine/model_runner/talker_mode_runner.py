@@ -51,7 +51,12 @@ class TalkerModeModelRunner(ModelRunner):
         gb = self.pick_graph(n)
         rows = gb or n
         self.fill_decode_layout(seqs, rows)
-        emb = torch.cat([s.decode_input_embeds.reshape(1, -1) for s in seqs], 0)
+        src = getattr(seqs[0], "batch_src", None)
+        if src is not None and all(getattr(s, "batch_src", None) is not None and s.batch_src[0] is src[0]
+                                   and s.batch_src[1] == i for i, s in enumerate(seqs)):
+            emb = src[0][:n].reshape(n, -1)                                   # fed by one add_requests call, in order
+        else:
+            emb = torch.cat([s.decode_input_embeds.reshape(1, -1) for s in seqs], 0)
         self.static_embeds[:n].copy_(emb, non_blocking=True)
         self.set_decode_context(rows)
         if gb is None:

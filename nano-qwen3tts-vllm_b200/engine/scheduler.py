@@ -118,6 +118,7 @@ class TalkerScheduler(Scheduler):
         for i, (seq, tok) in enumerate(zip(seqs, token_ids)):
             seq.append_token(tok, hidden_states[i])
             seq.decode_input_embeds = None
+            seq.batch_src = None
             hit_eos = not seq.ignore_eos and tok == self.eos
             # requests driven by the interface stop on the codec EOS there, not here
             # (talker_llm_engine.py:74-77)

@@ -197,20 +197,32 @@ def test_graph_replay_equals_eager_frames(setup):
     assert torch.equal(outs[0], outs[1])
 
 
-def test_step_api_frame_loop_greedy_vs_oracle(setup):
-    """The reference's per-frame protocol with host buffers (StepApiFrameLoop) gives the oracle's frames."""
+@pytest.mark.parametrize("batched", [True, False])
+def test_step_api_frame_loop_greedy_vs_oracle(setup, batched):
+    """The reference's per-frame protocol with host buffers (StepApiFrameLoop) gives the oracle's frames: one
+    add_request per stream and one engine step per codebook (the reference's call pattern), and the batched form
+    (one add_requests per engine per frame, the predictor's whole burst as one captured graph)."""
     from nano_qwen3tts_vllm_b200.engine.frame_loop import StepApiFrameLoop
     talker, predictor = setup["talker"], setup["predictor"]
+    if batched:                 # graphs on: decode graphs + the predictor's burst graphs (the fixture's engines are eager)
+        from nano_qwen3tts_vllm_b200.llm import PredictorLLM, TalkerLLM
+        _, _, tw, pw = small_weights()
+        kw = dict(num_kvcache_blocks=4 * B, max_num_seqs=max(B, 2), max_model_len=512, graph_batch_sizes=[B])
+        talker, predictor = TalkerLLM(small_model_config(), state_dict=tw, **kw), PredictorLLM(small_model_config(), state_dict=pw, **kw)
     talker.model_runner.kv_cache.zero_(); predictor.model_runner.kv_cache.zero_()
-    old = talker.model_runner.top_k, predictor.model_runner.top_k
+    old = talker.model_runner.top_k, predictor.model_runner.top_k, predictor.burst
     talker.model_runner.top_k = predictor.model_runner.top_k = 1
+    predictor.burst = batched
     try:
-        api = StepApiFrameLoop(talker, predictor, setup["pad"])
+        api = StepApiFrameLoop(talker, predictor, setup["pad"], batched=batched)
         api.add_streams([x.unsqueeze(0).pin_memory() for x in setup["prompts"]])
         for _ in range(NFRAMES):
             api.step_frame()
         got = torch.tensor([api.frames[f"s{i}"] for i in range(B)]).permute(1, 0, 2)
         api.close()
     finally:
-        talker.model_runner.top_k, predictor.model_runner.top_k = old
+        talker.model_runner.top_k, predictor.model_runner.top_k, predictor.burst = old
+    if batched:
+        assert predictor.model_runner.burst_top_k == 1           # the burst graphs were re-captured for greedy and used
+        talker.exit(); predictor.exit()
     _check_against_oracle(got, setup["want"], setup["margins"])
