@@ -330,6 +330,42 @@ B2TTS_API int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, const
                             int batch, int num_heads, int num_kv_heads, int head_dim, int page_size,
                             float scale, int max_ctx, int rounding, int pdl, void* stream);
 
+/* ---- a10 in one launch: the decode pass of a whole (small) decoder stack ----------------------------------------
+ * replaces, for one decode step of up to 64 sequences, the layer loop of Qwen3TTSCodePredictorModel.forward /
+ * Qwen3TTSTalkerModel.forward                          models/qwen3_tts_predictor.py:30-44, qwen3_tts_talker.py:53-62
+ * over Qwen3TTSDecoderLayer.forward                    models/qwen3_tts_share.py:163-176 (and :79-113, :131-135)
+ * i.e. per layer: input RMSNorm, QKV projection, q/k head norm + RoPE + paged KV write + paged GQA attention,
+ * o projection + residual add, post-attention RMSNorm, gate_up projection + SiLU*mul, down projection + residual
+ * add; then the final RMSNorm.  ONE persistent dataflow kernel (one CTA per SM): every CTA owns one (projection,
+ * 128-feature tile, K split) job in every layer and prefetches its packed weights ahead of the activations; phases
+ * are linked by arrival counters in the workspace instead of kernel boundaries (csrc/decoder_stack.cu).  Same packed
+ * weights (b2tts_gemm_pack_weight; gate_up in B2TTS_PACK_GATE_UP mode), rounding points and summation orders as
+ * b2tts_rmsnorm -> b2tts_gemm_bf16 -> b2tts_fused_decode_attn -> b2tts_gemm_bf16(RESIDUAL, splits = o_splits) ->
+ * b2tts_rmsnorm -> b2tts_gemm_bf16(SILU_MUL) -> b2tts_gemm_bf16(RESIDUAL, splits = down_splits): bit-identical.
+ * x [m, hidden] is the residual stream entering layer 0 (left intact), out [m, hidden] the normalised final hidden
+ * states.  positions [m] int64 (1-D RoPE), slot_mapping / block_table / context_lens as b2tts_fused_decode_attn.
+ * 1 <= m <= 64, 1 <= num_layers <= 8, head_dim 128, num_heads == 2 * num_kv_heads, hidden <= 2048, and the jobs must
+ * fit one per SM (b2tts_decoder_stack_plan returns 0 otherwise).  workspace: b2tts_decoder_stack_workspace_bytes(...)
+ * bytes, 256-byte aligned, ZERO-FILLED once by the caller; one workspace must not be used by two launches that can
+ * run concurrently, and the grid needs every SM of the device.  A dependency that fails to resolve within 4 s traps
+ * (CUDA launch failure) rather than hanging the device. */
+typedef struct b2tts_stack_layer {
+  const void *qkv_w, *o_w, *gate_up_w, *down_w;                      /* packed weights */
+  const void *input_norm_w, *post_norm_w, *q_norm_w, *k_norm_w;       /* bf16 norm weights [hidden] / [128] */
+  void *k_cache, *v_cache;                                            /* [pages, page, kv_heads, 128] bf16 */
+} b2tts_stack_layer;
+B2TTS_API int    b2tts_decoder_stack_plan(int hidden, int q_size, int kv_size, int intermediate,
+                                          int* o_splits, int* down_splits);
+B2TTS_API size_t b2tts_decoder_stack_workspace_bytes(int hidden, int q_size, int kv_size, int intermediate);
+B2TTS_API int    b2tts_decoder_stack_decode(const void* x, int64_t x_row_stride, void* out, int64_t out_row_stride,
+                                            const b2tts_stack_layer* layers, int num_layers, const void* final_norm_weight,
+                                            int m, int hidden, int num_heads, int num_kv_heads, int head_dim,
+                                            int intermediate, float eps, int rounding,
+                                            const int64_t* positions, const float* inv_freq, float attention_scaling,
+                                            const int32_t* slot_mapping, const int32_t* block_table, int bt_stride,
+                                            const int32_t* context_lens, int page_size, float scale,
+                                            void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
