@@ -72,6 +72,9 @@ def _load():
         "b2tts_gemm_chain_ssq_slots": (I, [I]),
         "b2tts_gemm_chain_workspace_bytes": (Z, [I, P, P, I]),
         "b2tts_gemm_chain": (I, [P, I, I, F, I, P, Z, I, P]),
+        "b2tts_decoder_stack_plan": (I, [I, I, I, I, P, P]),
+        "b2tts_decoder_stack_workspace_bytes": (Z, [I, I, I, I]),
+        "b2tts_decoder_stack_decode": (I, [P, L, P, L, P, I, P, I, I, I, I, I, I, F, I, P, P, F, P, P, I, P, I, F, P, Z, P]),
     }
     for name, (res, args) in sig.items():
         if not hasattr(lib, name):
@@ -548,3 +551,68 @@ def gemm_chain(ops: list[dict], m: int, workspace: torch.Tensor, eps: float = 1e
     _check(_load().b2tts_gemm_chain(ctypes.byref(arr), len(ops), int(m), float(eps), int(rounding),
                                     workspace.data_ptr(), workspace.numel() * workspace.element_size(),
                                     int(bool(pdl)), _stream()), "gemm_chain")
+
+
+# ------------------------------------------------------------------------------------------ a10 in one launch
+class StackLayer(ctypes.Structure):
+    """``b2tts_stack_layer`` (include/b200tts.h)."""
+    _fields_ = [("qkv_w", c_void_p), ("o_w", c_void_p), ("gate_up_w", c_void_p), ("down_w", c_void_p),
+                ("input_norm_w", c_void_p), ("post_norm_w", c_void_p), ("q_norm_w", c_void_p), ("k_norm_w", c_void_p),
+                ("k_cache", c_void_p), ("v_cache", c_void_p)]
+
+
+DECODER_STACK_MAX_M = 64
+DECODER_STACK_MAX_LAYERS = 8
+
+
+def decoder_stack_plan(hidden: int, q_size: int, kv_size: int, intermediate: int):
+    """(o_splits, down_splits) of the persistent decoder-stack kernel for these widths, or None when the stack
+    does not fit one job per SM (``b2tts_decoder_stack_plan``)."""
+    so, sd = c_int(), c_int()
+    ok = _load().b2tts_decoder_stack_plan(int(hidden), int(q_size), int(kv_size), int(intermediate),
+                                          ctypes.byref(so), ctypes.byref(sd))
+    return (so.value, sd.value) if ok else None
+
+
+def decoder_stack_workspace(hidden: int, q_size: int, kv_size: int, intermediate: int, device) -> torch.Tensor:
+    """Zero-filled, 256-byte aligned workspace of ``decoder_stack_decode``."""
+    n = int(_load().b2tts_decoder_stack_workspace_bytes(int(hidden), int(q_size), int(kv_size), int(intermediate)))
+    if n == 0:
+        raise RuntimeError("libb200tts decoder_stack_workspace: unsupported widths")
+    buf = torch.zeros(n + 256, dtype=torch.uint8, device=device)
+    off = (-buf.data_ptr()) % 256
+    return buf[off:off + n]
+
+
+def decoder_stack_decode(x, layers: list[dict], final_norm_weight, positions, inv_freq, slot_mapping, block_table,
+                         context_lens, *, num_heads, num_kv_heads, head_dim, intermediate, eps, scale, workspace,
+                         attention_scaling=1.0, rounding=ROUND_EAGER, out=None, layer_array=None):
+    """One decode step of a whole decoder stack in one persistent launch (``b2tts_decoder_stack_decode``).
+    ``layers``: per layer a dict of tensors ``qkv_w, o_w, gate_up_w, down_w`` (packed images),
+    ``input_norm_w, post_norm_w, q_norm_w, k_norm_w``, ``k_cache, v_cache``; ``layer_array`` a prebuilt
+    ``StackLayer`` array (skips the per-call marshalling).  x [m, hidden] -> normalised hidden states [m, hidden]."""
+    _cuda(x, BF16, "x"); _cuda(positions, I64, "positions"); _cuda(inv_freq, F32, "inv_freq")
+    _cuda(slot_mapping, I32, "slot_mapping"); _cuda(block_table, I32, "block_table"); _cuda(context_lens, I32, "context_lens")
+    m, hidden = x.shape
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    if out is None:
+        out = torch.empty(m, hidden, dtype=BF16, device=x.device)
+    arr = layer_array if layer_array is not None else stack_layer_array(layers)
+    kc = layers[0]["k_cache"]
+    _check(_load().b2tts_decoder_stack_decode(
+        x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), ctypes.byref(arr), len(layers),
+        final_norm_weight.data_ptr(), m, hidden, int(num_heads), int(num_kv_heads), int(head_dim), int(intermediate),
+        float(eps), int(rounding), positions.data_ptr(), inv_freq.data_ptr(), float(attention_scaling),
+        slot_mapping.data_ptr(), block_table.data_ptr(), block_table.stride(0), context_lens.data_ptr(),
+        int(kc.shape[1]), float(scale), workspace.data_ptr(), workspace.numel() * workspace.element_size(), _stream()),
+        "decoder_stack_decode")
+    return out
+
+
+def stack_layer_array(layers: list[dict]):
+    arr = (StackLayer * len(layers))()
+    for a, d in zip(arr, layers):
+        for name, _ in StackLayer._fields_:
+            setattr(a, name, d[name].data_ptr())
+    return arr

@@ -17,6 +17,8 @@ reference (``self_attn.{q,k,v,o}_proj.weight`` ...) are accepted by ``load_refer
 merged at load time."""
 from __future__ import annotations
 
+import os
+
 import torch
 from torch import nn
 
@@ -33,6 +35,8 @@ from ..utils.context import get_context
 
 FUSED_DECODE_ATTENTION = True     # False: separate qknorm_rope_kvwrite + paged_attn_decode launches
 GEMM_CHAIN = False                # decode: the 4 projections between two attention calls as ONE persistent launch
+# decode of a small stack (the code predictor) as ONE persistent dataflow launch (csrc/decoder_stack.cu)
+DATAFLOW_STACK = os.environ.get("B2TTS_DATAFLOW_STACK", "1") != "0"
 
 
 class Qwen3TTSAttention(nn.Module):
@@ -233,9 +237,52 @@ class DecoderStack(nn.Module):
             residual = out
         return nat.rmsnorm(residual, self.norm.weight, eps, rnd)
 
+    def dataflow_plan(self):
+        """(o_splits, down_splits) when this stack can run its decode pass as one persistent dataflow launch
+        (every (projection, tile, split) job on its own SM, 1-D RoPE, <= 8 layers), else None."""
+        plan = getattr(self, "_df_plan", False)
+        if plan is False:
+            c = self.config
+            rope = self.layers[0].self_attn.rotary_emb
+            plan = None
+            if (len(self.layers) <= nat.DECODER_STACK_MAX_LAYERS and rope.modality is None and c.head_dim == 128
+                    and c.num_attention_heads == 2 * c.num_key_value_heads):
+                plan = nat.decoder_stack_plan(c.hidden_size, c.q_size, c.kv_size, c.intermediate_size)
+            self._df_plan = plan
+        return plan
+
+    def run_layers_dataflow(self, input_embeds: torch.Tensor, positions: torch.Tensor) -> torch.Tensor:
+        """The whole decode pass (all layers + final norm, attention and KV write included) in one launch."""
+        c, ctx = self.config, get_context()
+        dev = input_embeds.device
+        st = getattr(self, "_df_state", None)
+        if st is None or st[0] != dev or st[1] != self.layers[0].self_attn.attn.k_cache.data_ptr():
+            layers = []
+            for layer in self.layers:
+                a, m = layer.self_attn, layer.mlp
+                layers.append(dict(
+                    qkv_w=packed_weight(a.qkv_proj.weight), o_w=packed_weight(a.o_proj.weight),
+                    gate_up_w=packed_weight(m.gate_up_proj.weight, nat.PACK_GATE_UP), down_w=packed_weight(m.down_proj.weight),
+                    input_norm_w=layer.input_layernorm.weight, post_norm_w=layer.post_attention_layernorm.weight,
+                    q_norm_w=a.q_norm.weight, k_norm_w=a.k_norm.weight, k_cache=a.attn.k_cache, v_cache=a.attn.v_cache))
+            ws = nat.decoder_stack_workspace(c.hidden_size, c.q_size, c.kv_size, c.intermediate_size, dev)
+            st = self._df_state = (dev, layers[0]["k_cache"].data_ptr(), layers, nat.stack_layer_array(layers), ws)
+        _, _, layers, arr, ws = st
+        rope = self.layers[0].self_attn.rotary_emb
+        return nat.decoder_stack_decode(
+            input_embeds, layers, self.norm.weight, positions, rope.inv_freq, ctx.slot_mapping, ctx.block_tables,
+            ctx.context_lens, num_heads=c.num_attention_heads, num_kv_heads=c.num_key_value_heads, head_dim=c.head_dim,
+            intermediate=c.intermediate_size, eps=c.rms_norm_eps, scale=self.layers[0].self_attn.scaling, workspace=ws,
+            attention_scaling=rope.attention_scaling, rounding=self.rounding, layer_array=arr)
+
     def run_layers(self, input_embeds: torch.Tensor, positions: torch.Tensor,
                    input_ssq: torch.Tensor | None = None, tail_weight=None) -> torch.Tensor:
         """``tail_weight``: the weight streamed right after the stack (the LM head), prefetched by the last layer."""
+        ctx = get_context()
+        if (DATAFLOW_STACK and not ctx.is_prefill and ctx.block_tables is not None and positions.dim() == 1
+                and 1 <= input_embeds.shape[0] <= nat.DECODER_STACK_MAX_M and input_embeds.dim() == 2
+                and self.layers[0].self_attn.attn.k_cache.numel() > 0 and self.dataflow_plan() is not None):
+            return self.run_layers_dataflow(input_embeds, positions)
         if GEMM_CHAIN and 1 <= input_embeds.shape[0] <= nat.GEMM_CHAIN_MAX_M and self._chain_supported():
             return self.run_layers_chained(input_embeds, positions, input_ssq)
         if 1 <= input_embeds.shape[0] <= GEMM_NATIVE_MAX_M and self._native_gemm_shapes():
