@@ -82,7 +82,9 @@ struct DsParams {
   unsigned* sync;
   __nv_bfloat16 *xn, *resid, *qkv, *attn, *act;
   float *part_o, *part_d;
+  unsigned long long* trace;                     // debug: 16 globaltimer stamps per (CTA, layer) (null = off)
 };
+#define DS_TRACE(l, slot) do { if (p.trace) p.trace[((int64_t)cta * DS_MAX_LAYERS + (l)) * 16 + (slot)] = gtimer(); } while (0)
 
 // ---------------------------------------------------------------- bounded waits
 __device__ __forceinline__ unsigned ds_ld_acquire(const unsigned* p) {
@@ -452,6 +454,7 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
   const uint32_t tmem_base = *tmem_slot;
   const unsigned E = __ldcg(p.sync);               // launch epoch: counter targets are (E + 1) * arrivals
   const unsigned E1 = E + 1u;
+  if (threadIdx.x == 0) DS_TRACE(0, 13);
 
   if (warp == 0) {
     // =========================== W producer: runs ahead through all layers, bounded only by the ring
@@ -484,6 +487,7 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
         for (int kb = kb0; kb < kb1; ++kb) {
           ds_mbar_wait(p.sync, wfull + slot, ph, 0x300u + l);
           ds_mbar_wait(p.sync, xfull + slot, ph, 0x400u + l);
+          if (kb == kb0 && lane == 0) DS_TRACE(l, 11);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + slot * DS_STAGE_BYTES);
           const uint32_t b_addr = a_addr + G_WTILE_BYTES;
@@ -496,6 +500,7 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
             if (kb == kb1 - 1) umma_commit(accfull);
           }
           __syncwarp();
+          if (kb == kb1 - 1 && lane == 0) DS_TRACE(l, 12);
           if (++slot == (uint32_t)DS_STAGES) { slot = 0; ph ^= 1; }
         }
       }
@@ -514,6 +519,7 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
           else ds_wait(p.sync, ds_ctr(p, l, DS_ACT), E1 * (unsigned)p.ng_tiles, 0x800u + l);
         }
         __syncwarp();
+        if (lane == 0) DS_TRACE(l, 9);
         ds_fence_proxy_async_all();
         for (int kb = kb0; kb < kb1; ++kb) {
           ds_mbar_wait(p.sync, empty + slot, ph, 0x900u + l);
@@ -528,6 +534,7 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
           __syncwarp();
           if (++slot == (uint32_t)DS_STAGES) { slot = 0; ph ^= 1; }
         }
+        if (lane == 0) DS_TRACE(l, 10);
       }
     }
     __syncwarp();
@@ -569,6 +576,7 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
     // split-K job: accumulator -> L2 scratch, per-tile counter, fixed-order reduce of this CTA's feature slice + residual
     auto split_job = [&](int l, float* part, int N, int tctr, const __nv_bfloat16* res, int64_t res_stride) {
       ds_mbar_wait(p.sync, accfull, (uint32_t)(l & 1), 0xa00u + l);
+      if (tw == 0) DS_TRACE(l, 1);
       tc_fence_after();
       uint32_t v[64];
       load_acc(v);
@@ -580,7 +588,9 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
       for (int c = 0; c < 64; ++c)
         if (c < M) __stcg(dst + (int64_t)c * N, __uint_as_float(v[c]));
       publish(ds_ctr(p, l, tctr + tile));
+      if (tw == 0) DS_TRACE(l, 2);
       await(ds_ctr(p, l, tctr + tile), E1 * (unsigned)S, 0xb00u + l);
+      if (tw == 0) DS_TRACE(l, 3);
       const int rows_own = G_BN / S;
       const int upr = rows_own >> 3;                // (row, 8 features) units per batch row
       const int n0 = tile * G_BN + split * rows_own;
@@ -612,8 +622,10 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
     }
     for (int l = 0; l < L; ++l) {
       const DsLayer& ly = p.layer[l];
+      if (tw == 0) DS_TRACE(l, 0);
       if (op == OP_QKV) {
         ds_mbar_wait(p.sync, accfull, (uint32_t)(l & 1), 0xc00u + l);
+        if (tw == 0) DS_TRACE(l, 1);
         tc_fence_after();
         uint32_t v[64];
         load_acc(v);
@@ -626,23 +638,30 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
         for (int c = 0; c < 64; ++c)
           if (c < M) dst[(int64_t)c * qkv_w] = __float2bfloat16_rn(__uint_as_float(v[c]));
         publish(ds_ctr(p, l, DS_QKV));
+        if (tw == 0) DS_TRACE(l, 2);
       }
       // ---- attention: every CTA's workers, one (row, kv head) item per warp
       await(ds_ctr(p, l, DS_QKV), E1 * (unsigned)p.nq_tiles, 0xd00u + l);
+      if (tw == 0) DS_TRACE(l, 7);
       {
         const int items = M * p.kvh;
         for (int it = ww * G + cta; it < items; it += 4 * G)
           ds_attn_item<EAGER>(p, ly, it / p.kvh, it % p.kvh, lane, scr, frq);
       }
       publish(ds_ctr(p, l, DS_ATT));
+      if (tw == 0) DS_TRACE(l, 8);
       if (op == OP_O) {
         split_job(l, p.part_o, p.H, DS_T_O, l == 0 ? p.x_in : p.resid, l == 0 ? p.x_stride : (int64_t)p.H);
         publish(ds_ctr(p, l, DS_O));
+        if (tw == 0) DS_TRACE(l, 4);
         await(ds_ctr(p, l, DS_O), E1 * (unsigned)n_o, 0xe00u + l);
+        if (tw == 0) DS_TRACE(l, 5);
         norm_rows(p.resid, p.H, ly.ln_post, p.xn, p.H, cta - p.nq_tiles, n_o);
         publish(ds_ctr(p, l, DS_XN_B));
+        if (tw == 0) DS_TRACE(l, 6);
       } else if (op == OP_GU) {
         ds_mbar_wait(p.sync, accfull, (uint32_t)(l & 1), 0xf00u + l);
+        if (tw == 0) DS_TRACE(l, 1);
         tc_fence_after();
         uint32_t v[64];
         load_acc(v);
@@ -663,19 +682,24 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
           }
         }
         publish(ds_ctr(p, l, DS_ACT));
+        if (tw == 0) DS_TRACE(l, 2);
       } else if (op == OP_DOWN) {
         split_job(l, p.part_d, p.H, DS_T_D, p.resid, p.H);
         publish(ds_ctr(p, l, DS_DOWN));
+        if (tw == 0) DS_TRACE(l, 4);
         await(ds_ctr(p, l, DS_DOWN), E1 * (unsigned)n_d, 0x1000u + l);
+        if (tw == 0) DS_TRACE(l, 5);
         const int j = cta - (p.nq_tiles + n_o + p.ng_tiles);
         if (l + 1 < L) norm_rows(p.resid, p.H, p.layer[l + 1].ln_in, p.xn, p.H, j, n_d);
         else norm_rows(p.resid, p.H, p.final_w, p.out, p.out_stride, j, n_d);
         publish(ds_ctr(p, l + 1, DS_XN_A));
+        if (tw == 0) DS_TRACE(l, 6);
       }
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) DS_TRACE(0, 14);
   if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
   // the last CTA to leave opens the next epoch (every CTA has read this one long ago)
   if (threadIdx.x == 0) {
@@ -688,6 +712,7 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
   }
 }
 
+static unsigned long long* g_ds_trace = nullptr;   // debug only (b2tts_debug_stack_trace)
 struct DsPlan { int nq, no, so, ng, nd, sd; };
 static bool ds_plan(int hidden, int q_size, int kv_size, int inter, DsPlan* out) {
   if (hidden <= 0 || q_size <= 0 || kv_size <= 0 || inter <= 0) return false;
@@ -807,6 +832,7 @@ extern "C" B2TTS_API int b2tts_decoder_stack_decode(
   p.act = reinterpret_cast<__nv_bfloat16*>(w); w += ds_align(rows * intermediate * 2);
   p.part_o = reinterpret_cast<float*>(w); w += ds_align((size_t)pl.so * rows * hidden * 4);
   p.part_d = reinterpret_cast<float*>(w);
+  p.trace = g_ds_trace;
   CUtensorMap tm_xn, tm_attn, tm_act;
   int rc = make_x_tensor_map(&tm_xn, p.xn, hidden, DS_MAX_M, hidden, p.mpad, what);
   if (rc) return rc;
@@ -837,5 +863,12 @@ extern "C" B2TTS_API int b2tts_decoder_stack_decode(
   e = cudaLaunchKernelEx(&cfg, kern, p, tm_xn, tm_attn, tm_act);
   count_launch();
   if (e != cudaSuccess) return cuda_fail(e, what);
+  return B2TTS_OK;
+}
+
+// Debug aid (tools/stack_trace.py): following launches record 16 globaltimer stamps per (CTA, layer) into
+// buffer[(cta * 8 + layer) * 16 + slot] (uint64).  NULL switches tracing off.
+extern "C" B2TTS_API int b2tts_debug_stack_trace(void* buffer) {
+  b2::g_ds_trace = static_cast<unsigned long long*>(buffer);
   return B2TTS_OK;
 }
