@@ -8,19 +8,20 @@
 // enough that ONE (projection, 128-feature tile, K split) job per layer fits on its own SM: 32 qkv tiles + 8 x 4 o
 // splits + 48 gate_up tiles + 8 x 4 down splits = 144 <= 148 SMs.  So the assignment is STATIC:
 //   * every CTA owns the same job in every layer; its producer warp streams the job's packed weight tiles
-//     (b2tts_gemm_pack_weight images, 16 KiB 1-D bulk copies) into a 9-stage ring and runs AHEAD: while layer l
+//     (b2tts_gemm_pack_weight images, 16 KiB 1-D bulk copies) into a 7-stage ring and runs AHEAD: while layer l
 //     waits for its activations, layer l's (and then l+1's) weights are already in shared memory, so HBM never
 //     waits for a dependency and no phase pays a weight-fetch latency;
 //   * phases are linked by monotonic arrival counters in L2 (red.release / ld.acquire, epoch-scaled so that a CUDA
 //     graph can replay the launch without a memset) instead of kernel boundaries; the activations (<= 64 rows) are
 //     fetched by 2-D tensor-map copies as the UMMA B operand once their counter is complete;
 //   * tcgen05.mma (weights = 128-row A operand, batch = N, fp32 accumulator in TMEM) exactly as gemm_stream_kernel;
-//   * the o / down splits reduce through an L2 scratch in fixed split order (deterministic), apply the residual
-//     add, and the same CTAs then normalise the finished rows (RMSNorm, arithmetic of rmsnorm_kernel) for the next
-//     projection;
+//   * the o / down splits leave fp32 partials in an L2 scratch; the same CTAs then each FINISH whole rows: fixed-order
+//     sum over the splits (deterministic), residual add, and the RMSNorm of the finished row for the next projection
+//     (arithmetic and reduction tree of rmsnorm_kernel) - one hand-over instead of reduce -> barrier -> norm;
 //   * attention (q/k head norm + RoPE + paged KV write + GQA attention over the cached tokens, arithmetic and
-//     summation order of fused_decode_attn_kernel) runs on the 4 worker warps of ALL CTAs, one (sequence, kv head)
-//     per warp, between the qkv and o phases.
+//     summation order of fused_decode_attn_kernel) runs on 4 worker warps of ALL CTAs, one (sequence, kv head) per
+//     warp, between the qkv and o phases; the cached K / V rows of the item (written by earlier launches) are staged
+//     in shared memory by cp.async while the QKV projection is still running.
 // Rounding points are those of the separate launches; with the same K splits the result is
 // bit-identical to rmsnorm -> gemm -> fused_decode_attn -> gemm(residual) -> rmsnorm -> gemm(SiLU*mul) -> gemm(residual).
 //
@@ -33,25 +34,27 @@
 namespace b2 {
 
 constexpr int DS_MAX_LAYERS = 8;
-constexpr int DS_THREADS = 224;                  // warp 0: W producer, 1: MMA issuer, 2: x producer, 3-6: workers
+constexpr int DS_THREADS = 352;                  // warp 0: W producer, 1: MMA issuer, 2: x producer, 3-10: workers
 constexpr int DS_W0 = 96;                        // first worker thread
-constexpr int DS_WORKERS = 128;
+constexpr int DS_WORKERS = 256;
 constexpr int DS_MAX_M = 64;                     // batch rows (UMMA N)
-constexpr int DS_STAGES = 9;
+constexpr int DS_STAGES = 7;
 constexpr int DS_STAGE_BYTES = G_WTILE_BYTES + DS_MAX_M * 128;   // 24 KiB: W tile + x tile
 constexpr int DS_HD = 128;
 constexpr int DS_GROUP = 2;                      // q heads per kv head
 constexpr int DS_ATT_TILE = 8;                   // tokens per online-softmax step (as fused_decode_attn_kernel)
-constexpr int DS_SCR_BYTES = 1024;               // per worker warp: q [2][128], k [128], v [128] bf16
+constexpr int DS_ATT_WARPS = 4;                  // worker warps that own an attention item
+constexpr int DS_SCR_BYTES = 1024;               // per attention warp: q [2][128], k [128], v [128] bf16 of the new token
+constexpr int DS_KV_PRE = 16;                    // cached tokens staged in shared memory per item
+constexpr int DS_KV_BYTES = 2 * DS_KV_PRE * DS_HD * 2;   // K and V rows of one head
 constexpr int DS_MAX_SPLIT_TILES = 16;
-constexpr int DS_CTRS = 8 + 2 * DS_MAX_SPLIT_TILES;   // counters per layer
+constexpr int DS_CTRS = 8;                       // counters per layer
 constexpr int DS_CTR_STRIDE = 8;                 // words between counters (one 32-byte sector each)
 constexpr int DS_CTR_BASE = 64;                  // words 0..63: epoch, exit counter, error
 constexpr size_t DS_SYNC_BYTES = 32768;
 constexpr unsigned long long DS_TIMEOUT_NS = 4000000000ull;
 
-enum { DS_XN_A = 0, DS_QKV = 1, DS_ATT = 2, DS_O = 3, DS_XN_B = 4, DS_ACT = 5, DS_DOWN = 6, DS_T_O = 8,
-       DS_T_D = 8 + DS_MAX_SPLIT_TILES };
+enum { DS_XN_A = 0, DS_QKV = 1, DS_ATT = 2, DS_PO = 3, DS_XN_B = 4, DS_ACT = 5, DS_PD = 6 };
 enum { OP_QKV = 0, OP_O = 1, OP_GU = 2, OP_DOWN = 3, OP_NONE = 4 };
 
 struct DsLayer {
@@ -133,7 +136,7 @@ __device__ __forceinline__ void ds_mbar_wait(unsigned* sync, uint64_t* bar, uint
   }
 }
 __device__ __forceinline__ void ds_fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
-__device__ __forceinline__ void ds_workers_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void ds_workers_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 __device__ __forceinline__ unsigned* ds_ctr(const DsParams& p, int l, int k) {
   return p.sync + DS_CTR_BASE + (l * DS_CTRS + k) * DS_CTR_STRIDE;
 }
@@ -154,17 +157,50 @@ __device__ __forceinline__ uint4 ds_pack8(const float* f) {
 __device__ __forceinline__ uint4 ds_ldcg_v4(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
 __device__ __forceinline__ uint32_t ds_ldcg_u32(const void* p) { return __ldcg(reinterpret_cast<const unsigned*>(p)); }
 
+__device__ __forceinline__ void ds_cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void ds_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void ds_cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// The (row, kv head) item an attention warp owns for the whole launch: everything that does not depend on the
+// layer (context length, cache slot, RoPE cos/sin, where the cached tokens live) is worked out once.
+struct DsAttnItem {
+  int row, hk, L, slot, npre;                    // npre: cached tokens staged in shared memory (<= DS_KV_PRE)
+  float c1[2], s1[2];
+  uint32_t tokslot[DS_KV_PRE / 2];               // cache slot of the token copy i of this lane stages (or ~0u)
+};
+
+// stage the cached K / V rows of this item's head (tokens 0 .. npre-1) in shared memory: lanes 0-15 copy the 16
+// 16-byte pieces of token 2i, lanes 16-31 those of token 2i+1.  They were written by earlier launches, so the copies
+// run while the QKV projection of the layer is still being computed.
+__device__ __forceinline__ void ds_kv_prefetch(const DsLayer& ly, const DsAttnItem& it, int kv_dim, int lane,
+                                               __nv_bfloat16* ksm, __nv_bfloat16* vsm) {
+  const int part = lane & 15;
+#pragma unroll
+  for (int i = 0; i < DS_KV_PRE / 2; ++i) {
+    if (it.tokslot[i] != 0xffffffffu) {
+      const int tok = 2 * i + (lane >> 4);
+      const int64_t off = (int64_t)it.tokslot[i] * kv_dim + it.hk * DS_HD + part * 8;
+      ds_cp_async16(ksm + tok * DS_HD + part * 8, ly.k_cache + off);
+      ds_cp_async16(vsm + tok * DS_HD + part * 8, ly.v_cache + off);
+    }
+  }
+  ds_cp_async_commit();
+}
+
 // ---------------------------------------------------------------- one attention item: (row, kv head) on one warp.
 // Arithmetic, lane mapping and summation order of fused_decode_attn_kernel (attention_fused.cu) with nsplit == 1;
-// the cached tokens are read straight from the paged cache (L2), the new token from the warp's scratch.
+// cached tokens come from the shared-memory copy (or, beyond DS_KV_PRE tokens, straight from the paged cache),
+// the new token from the warp's scratch.
 template <bool EAGER>
-__device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& ly, int row, int hk, int lane,
-                                             __nv_bfloat16* scr, const float* frq) {
+__device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& ly, const DsAttnItem& it, int lane,
+                                             __nv_bfloat16* scr, const __nv_bfloat16* ksm, const __nv_bfloat16* vsm) {
   const int kv_dim = p.kvh * DS_HD;
   const int qkv_w = p.Q + 2 * p.KV;
+  const int row = it.row, hk = it.hk, L = it.L;
   const int head0 = hk * DS_GROUP;
   const int g = lane >> 3, j = lane & 7;
-  int L = __ldg(p.context_lens + row);
   if (L <= 0) {                                   // CUDA-graph padding row: zeros
     if (g == 0) {
 #pragma unroll
@@ -176,8 +212,6 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
     }
     return;
   }
-  const int slot = __ldg(p.slot_mapping + row);
-  const int64_t pos = __ldg(p.positions + row);
   const __nv_bfloat16* qkv_row = p.qkv + (int64_t)row * qkv_w;
   uint32_t raw1[DS_GROUP + 1], raw2[DS_GROUP + 1];
 #pragma unroll
@@ -196,15 +230,7 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
   __nv_bfloat16* q_s = scr;
   __nv_bfloat16* kn_s = scr + DS_GROUP * DS_HD;
   __nv_bfloat16* vn_s = kn_s + DS_HD;
-  __syncwarp();                                   // the previous item's readers are done with the scratch
   {
-    float c1[2], s1[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const float a1 = (float)pos * frq[e];
-      c1[e] = rbf(cosf(a1) * p.attention_scaling);
-      s1[e] = rbf(sinf(a1) * p.attention_scaling);
-    }
 #pragma unroll
     for (int i = 0; i < DS_GROUP + 1; ++i) {
       const bool is_k = i == DS_GROUP;
@@ -226,25 +252,26 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
       float o1[2], o2[2];
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        o1[e] = rbf(x1[e] * c1[e]) + rbf(-x2[e] * s1[e]);
-        o2[e] = rbf(x2[e] * c1[e]) + rbf(x1[e] * s1[e]);
+        o1[e] = rbf(x1[e] * it.c1[e]) + rbf(-x2[e] * it.s1[e]);
+        o2[e] = rbf(x2[e] * it.c1[e]) + rbf(x1[e] * it.s1[e]);
       }
       const uint32_t y1 = pack_bf16(o1[0], o1[1]), y2 = pack_bf16(o2[0], o2[1]);
       __nv_bfloat16* dst = is_k ? kn_s : q_s + i * DS_HD;
       *reinterpret_cast<uint32_t*>(dst + 2 * lane) = y1;
       *reinterpret_cast<uint32_t*>(dst + 64 + 2 * lane) = y2;
-      if (is_k && slot >= 0) {
-        __nv_bfloat16* cd = ly.k_cache + (int64_t)slot * kv_dim + hk * DS_HD;
+      if (is_k && it.slot >= 0) {
+        __nv_bfloat16* cd = ly.k_cache + (int64_t)it.slot * kv_dim + hk * DS_HD;
         *reinterpret_cast<uint32_t*>(cd + 2 * lane) = y1;
         *reinterpret_cast<uint32_t*>(cd + 64 + 2 * lane) = y2;
       }
     }
     if (lane < 16) {
       *reinterpret_cast<uint4*>(vn_s + 8 * lane) = vraw;
-      if (slot >= 0) stg_v4(ly.v_cache + (int64_t)slot * kv_dim + hk * DS_HD + 8 * lane, vraw);
+      if (it.slot >= 0) stg_v4(ly.v_cache + (int64_t)it.slot * kv_dim + hk * DS_HD + 8 * lane, vraw);
     }
   }
-  __syncwarp();
+  ds_cp_async_wait_all();                         // this lane's staged K / V pieces have landed ...
+  __syncwarp();                                   // ... and so have everybody else's, and the scratch rows
 
   float qv[DS_GROUP][16];
 #pragma unroll
@@ -267,35 +294,38 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
   for (int i = 0; i < n_tiles; ++i) {
     const int tok0 = i * DS_ATT_TILE;
     const int ntok = min(DS_ATT_TILE, L - tok0);
-    // both token slots of this lane: K and V rows requested together (one L2 round trip per tile)
     uint4 kraw[2][2], vr[2][2];
     bool valid[2];
 #pragma unroll
-    for (int it = 0; it < DS_ATT_TILE / 4; ++it) {
-      const int tok = it * 4 + g;
-      valid[it] = tok < ntok;
-      const int t = tok0 + (valid[it] ? tok : 0);
-      if (t == L - 1) {
-        kraw[it][0] = *reinterpret_cast<const uint4*>(kn_s + 8 * j);
-        kraw[it][1] = *reinterpret_cast<const uint4*>(kn_s + 64 + 8 * j);
-        vr[it][0] = *reinterpret_cast<const uint4*>(vn_s + 8 * j);
-        vr[it][1] = *reinterpret_cast<const uint4*>(vn_s + 64 + 8 * j);
+    for (int s = 0; s < DS_ATT_TILE / 4; ++s) {
+      const int tok = s * 4 + g;
+      valid[s] = tok < ntok;
+      const int t = tok0 + (valid[s] ? tok : 0);
+      const __nv_bfloat16 *kp, *vp;
+      if (t == L - 1) { kp = kn_s; vp = vn_s; }
+      else if (t < it.npre) { kp = ksm + t * DS_HD; vp = vsm + t * DS_HD; }
+      else { kp = nullptr; vp = nullptr; }
+      if (kp) {
+        kraw[s][0] = *reinterpret_cast<const uint4*>(kp + 8 * j);
+        kraw[s][1] = *reinterpret_cast<const uint4*>(kp + 64 + 8 * j);
+        vr[s][0] = *reinterpret_cast<const uint4*>(vp + 8 * j);
+        vr[s][1] = *reinterpret_cast<const uint4*>(vp + 64 + 8 * j);
       } else {
         int page = __ldg(bt + t / p.page_size);
         if (page < 0) page = 0;
         const int64_t off = ((int64_t)page * p.page_size + t % p.page_size) * kv_dim + hk * DS_HD;
-        kraw[it][0] = ds_ldcg_v4(ly.k_cache + off + 8 * j);
-        kraw[it][1] = ds_ldcg_v4(ly.k_cache + off + 64 + 8 * j);
-        vr[it][0] = ds_ldcg_v4(ly.v_cache + off + 8 * j);
-        vr[it][1] = ds_ldcg_v4(ly.v_cache + off + 64 + 8 * j);
+        kraw[s][0] = ds_ldcg_v4(ly.k_cache + off + 8 * j);
+        kraw[s][1] = ds_ldcg_v4(ly.k_cache + off + 64 + 8 * j);
+        vr[s][0] = ds_ldcg_v4(ly.v_cache + off + 8 * j);
+        vr[s][1] = ds_ldcg_v4(ly.v_cache + off + 64 + 8 * j);
       }
     }
-    float s[DS_ATT_TILE / 4][DS_GROUP];
+    float sc[DS_ATT_TILE / 4][DS_GROUP];
 #pragma unroll
-    for (int it = 0; it < DS_ATT_TILE / 4; ++it) {
+    for (int s = 0; s < DS_ATT_TILE / 4; ++s) {
       float kf[16];
-      ds_unpack8(kraw[it][0], kf);
-      ds_unpack8(kraw[it][1], kf + 8);
+      ds_unpack8(kraw[s][0], kf);
+      ds_unpack8(kraw[s][1], kf + 8);
 #pragma unroll
       for (int h = 0; h < DS_GROUP; ++h) {
         float d0 = 0.f, d1 = 0.f;
@@ -308,15 +338,15 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
         dot += __shfl_xor_sync(0xffffffffu, dot, 1);
         dot += __shfl_xor_sync(0xffffffffu, dot, 2);
         dot += __shfl_xor_sync(0xffffffffu, dot, 4);
-        s[it][h] = valid[it] ? dot : -INFINITY;
+        sc[s][h] = valid[s] ? dot : -INFINITY;
       }
     }
     float alpha[DS_GROUP];
 #pragma unroll
     for (int h = 0; h < DS_GROUP; ++h) {
-      float mt = s[0][h];
+      float mt = sc[0][h];
 #pragma unroll
-      for (int it = 1; it < DS_ATT_TILE / 4; ++it) mt = fmaxf(mt, s[it][h]);
+      for (int s = 1; s < DS_ATT_TILE / 4; ++s) mt = fmaxf(mt, sc[s][h]);
       mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, 8));
       mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, 16));
       const float mn = fmaxf(mx[h], mt);
@@ -324,23 +354,23 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
       mx[h] = mn;
       float ps = 0.f;
 #pragma unroll
-      for (int it = 0; it < DS_ATT_TILE / 4; ++it) {
-        s[it][h] = ds_exp2(s[it][h] - mn);
-        ps += s[it][h];
+      for (int s = 0; s < DS_ATT_TILE / 4; ++s) {
+        sc[s][h] = ds_exp2(sc[s][h] - mn);
+        ps += sc[s][h];
       }
       l[h] = fmaf(l[h], alpha[h], ps);
 #pragma unroll
       for (int d = 0; d < 16; ++d) acc[h][d] *= alpha[h];
     }
 #pragma unroll
-    for (int it = 0; it < DS_ATT_TILE / 4; ++it) {
+    for (int s = 0; s < DS_ATT_TILE / 4; ++s) {
       float vf[16];
-      ds_unpack8(vr[it][0], vf);
-      ds_unpack8(vr[it][1], vf + 8);
+      ds_unpack8(vr[s][0], vf);
+      ds_unpack8(vr[s][1], vf + 8);
 #pragma unroll
       for (int h = 0; h < DS_GROUP; ++h)
 #pragma unroll
-        for (int d = 0; d < 16; ++d) acc[h][d] = fmaf(s[it][h], vf[d], acc[h][d]);
+        for (int d = 0; d < 16; ++d) acc[h][d] = fmaf(sc[s][h], vf[d], acc[h][d]);
     }
   }
 #pragma unroll
@@ -365,47 +395,70 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
       stg_v4(op + 64 + 8 * j, ds_pack8(o + 8));
     }
   }
+  __syncwarp();                                   // the scratch / staged rows may be overwritten from here on
 }
 
-// ---------------------------------------------------------------- RMSNorm of one row on one warp: the arithmetic and
-// reduction tree of rmsnorm_kernel (norm_rope.cu: 256 threads, thread t owns the 16-byte vector t; warp sums,
-// then one butterfly over the 8 warp totals) with the 8 warps of that kernel walked in sequence.
+// ---------------------------------------------------------------- one finished row on the 256 worker threads:
+// fixed-order sum of the split-K partials + residual add (bf16(residual + bf16(acc)), written back to the residual
+// stream), then the RMSNorm of the rounded row for the next projection.  Thread t owns the 16-byte vector t, warp
+// sums, then one butterfly over the 8 warp totals: the mapping and reduction tree of rmsnorm_kernel (norm_rope.cu).
 template <bool EAGER>
-__device__ __forceinline__ void ds_norm_row(const __nv_bfloat16* x, const __nv_bfloat16* w, __nv_bfloat16* y, int cols,
-                                            float eps, int lane) {
-  const int nvec = cols >> 3;                     // <= 256
-  uint4 raw[8];
-  float tot[8];
+__device__ __forceinline__ void ds_row_phase(const DsParams& p, int row, const float* part, int S, const __nv_bfloat16* res,
+                                             int64_t res_stride, const __nv_bfloat16* w, __nv_bfloat16* dst, int tw, float* red) {
+  const int nvec = p.H >> 3;                      // <= 256
+  const int lane = tw & 31, ww = tw >> 5;
+  const bool active = tw < nvec;
+  uint4 rowv = make_uint4(0, 0, 0, 0), wv = make_uint4(0, 0, 0, 0);
+  float ss = 0.f;
+  if (active) {
+    wv = ldg_v4(w + 8 * tw);
+    const uint4 rw = ds_ldcg_v4(res + (int64_t)row * res_stride + 8 * tw);
+    if (part) {
+      float4 a[8], b[8];
+      const float* src = part + (int64_t)row * p.H + 8 * tw;
 #pragma unroll
-  for (int vw = 0; vw < 8; ++vw) {
-    const int v = vw * 32 + lane;
-    float ss = 0.f;
-    raw[vw] = make_uint4(0, 0, 0, 0);
-    if (v < nvec) {
-      raw[vw] = ds_ldcg_v4(x + 8 * v);
-      float f[8];
-      ds_unpack8(raw[vw], f);
+      for (int s = 0; s < 8; ++s)
+        if (s < S) {
+          a[s] = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)s * DS_MAX_M * p.H));
+          b[s] = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)s * DS_MAX_M * p.H) + 1);
+        }
+      float acc[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) ss = fmaf(f[e], f[e], ss);
+      for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll
+      for (int s = 0; s < 8; ++s)
+        if (s < S) {
+          acc[0] += a[s].x; acc[1] += a[s].y; acc[2] += a[s].z; acc[3] += a[s].w;
+          acc[4] += b[s].x; acc[5] += b[s].y; acc[6] += b[s].z; acc[7] += b[s].w;
+        }
+      acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
+      acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
+      acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
+      acc[6] = rbf(acc[6]) + bf16lo(rw.w); acc[7] = rbf(acc[7]) + bf16hi(rw.w);
+      rowv = ds_pack8(acc);
+      stg_v4(p.resid + (int64_t)row * p.H + 8 * tw, rowv);
+    } else {
+      rowv = rw;
     }
-    tot[vw] = warp_sum(ss);
+    float f[8];
+    ds_unpack8(rowv, f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ss = fmaf(f[e], f[e], ss);
   }
-  float t = 0.f;
-#pragma unroll
-  for (int vw = 0; vw < 8; ++vw) t = lane == vw ? tot[vw] : t;
-  const float var = warp_sum(t) / (float)cols + eps;
+  ss = warp_sum(ss);
+  if (lane == 0) red[ww] = ss;
+  ds_workers_bar();
+  float t = lane < 8 ? red[lane] : 0.f;
+  t = warp_sum(t);
+  const float var = t / (float)p.H + p.eps;
   const float rstd = EAGER ? 1.0f / sqrtf(var) : rsqrtf(var);
+  if (active) {
+    float f[8], wf[8], o[8];
+    ds_unpack8(rowv, f);
+    ds_unpack8(wv, wf);
 #pragma unroll
-  for (int vw = 0; vw < 8; ++vw) {
-    const int v = vw * 32 + lane;
-    if (v < nvec) {
-      float f[8], wf[8], o[8];
-      ds_unpack8(raw[vw], f);
-      ds_unpack8(ldg_v4(w + 8 * v), wf);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) o[e] = EAGER ? rbf(rbf(f[e] * rstd) * wf[e]) : (f[e] * rstd) * wf[e];
-      stg_v4(y + 8 * v, ds_pack8(o));
-    }
+    for (int e = 0; e < 8; ++e) o[e] = EAGER ? rbf(rbf(f[e] * rstd) * wf[e]) : (f[e] * rstd) * wf[e];
+    stg_v4(dst + 8 * tw, ds_pack8(o));
   }
 }
 
@@ -415,8 +468,10 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
                      const __grid_constant__ CUtensorMap tm_act) {
   extern __shared__ uint8_t smem_dyn[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
-  uint8_t* scr_base = smem + DS_STAGES * DS_STAGE_BYTES;
-  uint64_t* wfull = reinterpret_cast<uint64_t*>(scr_base + 4 * DS_SCR_BYTES);
+  uint8_t* kv_base = smem + DS_STAGES * DS_STAGE_BYTES;
+  uint8_t* scr_base = kv_base + DS_ATT_WARPS * DS_KV_BYTES;
+  float* red_s = reinterpret_cast<float*>(scr_base + DS_ATT_WARPS * DS_SCR_BYTES);      // [2][8]
+  uint64_t* wfull = reinterpret_cast<uint64_t*>(red_s + 16);
   uint64_t* xfull = wfull + DS_STAGES;
   uint64_t* empty = xfull + DS_STAGES;
   uint64_t* accfull = empty + DS_STAGES;
@@ -430,13 +485,14 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
   const int L = p.num_layers;
 
   // ---- this CTA's job (the same in every layer)
-  int op = OP_NONE, tile = 0, split = 0, S = 1, kblocks = 0;
+  int op = OP_NONE, tile = 0, split = 0, S = 1, kblocks = 0, job = 0;
   {
     int c = cta;
     if (c < p.nq_tiles) { op = OP_QKV; tile = c; kblocks = p.H / G_BK; }
     else if ((c -= p.nq_tiles) < p.no_tiles * p.so) { op = OP_O; S = p.so; tile = c / S; split = c - tile * S; kblocks = p.Q / G_BK; }
     else if ((c -= p.no_tiles * p.so) < p.ng_tiles) { op = OP_GU; tile = c; kblocks = p.H / G_BK; }
     else if ((c -= p.ng_tiles) < p.nd_tiles * p.sd) { op = OP_DOWN; S = p.sd; tile = c / S; split = c - tile * S; kblocks = p.I / G_BK; }
+    job = c;
   }
   const int kb0 = (split * kblocks) / S, kb1 = ((split + 1) * kblocks) / S;
   const int n_o = p.no_tiles * p.so, n_d = p.nd_tiles * p.sd;
@@ -444,7 +500,7 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
   if (threadIdx.x == 0) {
     for (int s = 0; s < DS_STAGES; ++s) { mbar_init(wfull + s, 1); mbar_init(xfull + s, 1); mbar_init(empty + s, 1); }
     mbar_init(accfull, 1);
-    mbar_init(accempty, 4);
+    mbar_init(accempty, DS_WORKERS / 32);
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols);
@@ -464,6 +520,12 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
         const DsLayer& ly = p.layer[l];
         const uint8_t* wp = op == OP_QKV ? ly.w_qkv : op == OP_O ? ly.w_o : op == OP_GU ? ly.w_gu : ly.w_down;
         const uint8_t* src = wp + ((int64_t)tile * kblocks + kb0) * G_WTILE_BYTES;
+        // the k-blocks that do not fit the ring are at least pulled into L2 now, a layer ahead of their use
+        if (elect_one())
+          for (int kb = kb0 + DS_STAGES; kb < kb1; ++kb)
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;"
+                         :: "l"(src + (int64_t)(kb - kb0) * G_WTILE_BYTES), "r"(G_WTILE_BYTES) : "memory");
+        __syncwarp();
         for (int kb = kb0; kb < kb1; ++kb, src += G_WTILE_BYTES) {
           ds_mbar_wait(p.sync, empty + slot, ph, 0x100u + l);
           if (elect_one()) {
@@ -539,26 +601,51 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
     }
     __syncwarp();
   } else {
-    // =========================== workers: epilogues, split reduce, row norms, attention
-    const int tw = threadIdx.x - DS_W0;             // 0..127
-    const int ww = warp - 3;                        // 0..3
+    // =========================== workers (8 warps): epilogues, split reduce + row norms, attention
+    const int tw = threadIdx.x - DS_W0;             // 0..255
+    const int ww = warp - 3;                        // 0..7
     const int wq = warp & 3;                        // TMEM lane quarter this warp may read
+    const int ch = ww >> 2;                         // which 32 accumulator columns (batch rows) this warp drains
     const int r = wq * 32 + lane;                   // row of the 128-feature tile held by this thread
     const int M = p.m;
-    __nv_bfloat16* scr = reinterpret_cast<__nv_bfloat16*>(scr_base + ww * DS_SCR_BYTES);
-    float frq[2];
-    frq[0] = __ldg(p.inv_freq + 2 * lane);
-    frq[1] = __ldg(p.inv_freq + 2 * lane + 1);
+    const int kv_dim = p.kvh * DS_HD;
+    __nv_bfloat16* scr = reinterpret_cast<__nv_bfloat16*>(scr_base + (ww & (DS_ATT_WARPS - 1)) * DS_SCR_BYTES);
+    __nv_bfloat16* ksm = reinterpret_cast<__nv_bfloat16*>(kv_base + (ww & (DS_ATT_WARPS - 1)) * DS_KV_BYTES);
+    __nv_bfloat16* vsm = ksm + DS_KV_PRE * DS_HD;
     pdl_wait();
 
-    // rows this CTA normalises after its split reduce: CTA j of the n jobs of the op takes rows j, j + n, ...
-    auto norm_rows = [&](const __nv_bfloat16* src, int64_t src_stride, const __nv_bfloat16* w, __nv_bfloat16* dst,
-                         int64_t dst_stride, int j, int n) {
-      for (int row = j + ww * n; row < M; row += 4 * n)
-        ds_norm_row<EAGER>(src + (int64_t)row * src_stride, w, dst + (int64_t)row * dst_stride, p.H, p.eps, lane);
-    };
-    auto publish = [&](unsigned* ctr) {             // this CTA's stores -> visible, one arrival
-      __threadfence();
+    // ---- this warp's attention item (warps 0-3: item = warp * G + cta), fixed for the launch
+    DsAttnItem item;
+    const int item_id = ww * G + cta;
+    const bool has_item = ww < DS_ATT_WARPS && item_id < M * p.kvh;
+    item.row = has_item ? item_id / p.kvh : 0;
+    item.hk = has_item ? item_id % p.kvh : 0;
+    item.L = 0; item.slot = -1; item.npre = 0;
+    if (has_item) {
+      item.L = __ldg(p.context_lens + item.row);
+      item.slot = __ldg(p.slot_mapping + item.row);
+      const int64_t pos = __ldg(p.positions + item.row);
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const float a1 = (float)pos * __ldg(p.inv_freq + 2 * lane + e);
+        item.c1[e] = rbf(cosf(a1) * p.attention_scaling);
+        item.s1[e] = rbf(sinf(a1) * p.attention_scaling);
+      }
+      item.npre = max(0, min(item.L - 1, DS_KV_PRE));
+      const int32_t* bt = p.block_table + (int64_t)item.row * p.bt_stride;
+#pragma unroll
+      for (int i = 0; i < DS_KV_PRE / 2; ++i) {
+        const int tok = 2 * i + (lane >> 4);
+        item.tokslot[i] = 0xffffffffu;
+        if (tok < item.npre) {
+          int page = __ldg(bt + tok / p.page_size);
+          if (page < 0) page = 0;
+          item.tokslot[i] = (uint32_t)(page * p.page_size + tok % p.page_size);
+        }
+      }
+    }
+
+    auto publish = [&](unsigned* ctr) {             // bar.sync orders every worker's stores before the one release
       ds_workers_bar();
       if (tw == 0) ds_arrive(ctr);
     };
@@ -566,132 +653,102 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
       if (tw == 0) ds_wait(p.sync, ctr, target, code);
       ds_workers_bar();
     };
-    auto load_acc = [&](uint32_t* v) {
-      const int nq = p.mpad >> 4;
-#pragma unroll
-      for (int qq = 0; qq < 4; ++qq)
-        if (qq < nq) tmem_ld16_nowait(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(16 * qq), v + 16 * qq);
-      tmem_ld_wait();
-    };
-    // split-K job: accumulator -> L2 scratch, per-tile counter, fixed-order reduce of this CTA's feature slice + residual
-    auto split_job = [&](int l, float* part, int N, int tctr, const __nv_bfloat16* res, int64_t res_stride) {
-      ds_mbar_wait(p.sync, accfull, (uint32_t)(l & 1), 0xa00u + l);
+    auto load_acc = [&](int l, uint32_t* v, unsigned code) {      // this warp's 32 accumulator columns of row r
+      ds_mbar_wait(p.sync, accfull, (uint32_t)(l & 1), code);
       if (tw == 0) DS_TRACE(l, 1);
       tc_fence_after();
-      uint32_t v[64];
-      load_acc(v);
+      const int nq = p.mpad >> 4;
+#pragma unroll
+      for (int qq = 0; qq < 2; ++qq)
+        if (ch * 2 + qq < nq)
+          tmem_ld16_nowait(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(ch * 32 + 16 * qq), v + 16 * qq);
+      tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(accempty);
-      float* dst = part + (int64_t)split * DS_MAX_M * N + (int64_t)tile * G_BN + r;
-#pragma unroll
-      for (int c = 0; c < 64; ++c)
-        if (c < M) __stcg(dst + (int64_t)c * N, __uint_as_float(v[c]));
-      publish(ds_ctr(p, l, tctr + tile));
-      if (tw == 0) DS_TRACE(l, 2);
-      await(ds_ctr(p, l, tctr + tile), E1 * (unsigned)S, 0xb00u + l);
-      if (tw == 0) DS_TRACE(l, 3);
-      const int rows_own = G_BN / S;
-      const int upr = rows_own >> 3;                // (row, 8 features) units per batch row
-      const int n0 = tile * G_BN + split * rows_own;
-      for (int u = tw; u < M * upr; u += DS_WORKERS) {
-        const int m = u / upr, n = n0 + (u - m * upr) * 8;
-        float acc[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-        const float* src = part + (int64_t)m * N + n;
-        for (int s = 0; s < S; ++s, src += (int64_t)DS_MAX_M * N) {
-          const float4 a = __ldcg(reinterpret_cast<const float4*>(src));
-          const float4 b = __ldcg(reinterpret_cast<const float4*>(src) + 1);
-          acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
-          acc[4] += b.x; acc[5] += b.y; acc[6] += b.z; acc[7] += b.w;
-        }
-        const uint4 rw = ds_ldcg_v4(res + (int64_t)m * res_stride + n);
-        acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
-        acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
-        acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
-        acc[6] = rbf(acc[6]) + bf16lo(rw.w); acc[7] = rbf(acc[7]) + bf16hi(rw.w);
-        stg_v4(p.resid + (int64_t)m * p.H + n, ds_pack8(acc));
+    };
+    // rows this CTA finishes after a split-K projection: job j of the n jobs of the op owns rows j, j + n, ...
+    int red_flip = 0;
+    auto rows_phase = [&](const float* part, int nsplit, const __nv_bfloat16* res, int64_t res_stride, const __nv_bfloat16* w,
+                          __nv_bfloat16* dst, int64_t dst_stride, int n) {
+      for (int row = job; row < M; row += n) {
+        ds_row_phase<EAGER>(p, row, part, nsplit, res, res_stride, w, dst + (int64_t)row * dst_stride, tw, red_s + 8 * red_flip);
+        red_flip ^= 1;
       }
     };
+    auto drain_partial = [&](int l, float* part, unsigned code) {
+      uint32_t v[32];
+      load_acc(l, v, code);
+      float* dst = part + (int64_t)split * DS_MAX_M * p.H + (int64_t)tile * G_BN + r;
+#pragma unroll
+      for (int c = 0; c < 32; ++c)
+        if (ch * 32 + c < M) __stcg(dst + (int64_t)(ch * 32 + c) * p.H, __uint_as_float(v[c]));
+    };
 
-    // the first layer's input norm: done by the down jobs (they are idle until the first MLP)
+    // the first layer's input norm: done by the down jobs (idle until the first MLP)
     if (op == OP_DOWN) {
-      norm_rows(p.x_in, p.x_stride, p.layer[0].ln_in, p.xn, p.H, cta - (p.nq_tiles + n_o + p.ng_tiles), n_d);
+      rows_phase(nullptr, 0, p.x_in, p.x_stride, p.layer[0].ln_in, p.xn, p.H, n_d);
       publish(ds_ctr(p, 0, DS_XN_A));
     }
     for (int l = 0; l < L; ++l) {
       const DsLayer& ly = p.layer[l];
       if (tw == 0) DS_TRACE(l, 0);
+      if (has_item && item.L > 0) ds_kv_prefetch(ly, item, kv_dim, lane, ksm, vsm);
       if (op == OP_QKV) {
-        ds_mbar_wait(p.sync, accfull, (uint32_t)(l & 1), 0xc00u + l);
-        if (tw == 0) DS_TRACE(l, 1);
-        tc_fence_after();
-        uint32_t v[64];
-        load_acc(v);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(accempty);
+        uint32_t v[32];
+        load_acc(l, v, 0xc00u + l);
         __nv_bfloat16* dst = p.qkv + tile * G_BN + r;
         const int qkv_w = p.Q + 2 * p.KV;
 #pragma unroll
-        for (int c = 0; c < 64; ++c)
-          if (c < M) dst[(int64_t)c * qkv_w] = __float2bfloat16_rn(__uint_as_float(v[c]));
+        for (int c = 0; c < 32; ++c)
+          if (ch * 32 + c < M) dst[(int64_t)(ch * 32 + c) * qkv_w] = __float2bfloat16_rn(__uint_as_float(v[c]));
         publish(ds_ctr(p, l, DS_QKV));
         if (tw == 0) DS_TRACE(l, 2);
       }
-      // ---- attention: every CTA's workers, one (row, kv head) item per warp
+      // ---- attention: the first 4 worker warps of every CTA, one (row, kv head) item each
       await(ds_ctr(p, l, DS_QKV), E1 * (unsigned)p.nq_tiles, 0xd00u + l);
       if (tw == 0) DS_TRACE(l, 7);
-      {
-        const int items = M * p.kvh;
-        for (int it = ww * G + cta; it < items; it += 4 * G)
-          ds_attn_item<EAGER>(p, ly, it / p.kvh, it % p.kvh, lane, scr, frq);
-      }
+      if (has_item) ds_attn_item<EAGER>(p, ly, item, lane, scr, ksm, vsm);
       publish(ds_ctr(p, l, DS_ATT));
       if (tw == 0) DS_TRACE(l, 8);
       if (op == OP_O) {
-        split_job(l, p.part_o, p.H, DS_T_O, l == 0 ? p.x_in : p.resid, l == 0 ? p.x_stride : (int64_t)p.H);
-        publish(ds_ctr(p, l, DS_O));
-        if (tw == 0) DS_TRACE(l, 4);
-        await(ds_ctr(p, l, DS_O), E1 * (unsigned)n_o, 0xe00u + l);
-        if (tw == 0) DS_TRACE(l, 5);
-        norm_rows(p.resid, p.H, ly.ln_post, p.xn, p.H, cta - p.nq_tiles, n_o);
+        drain_partial(l, p.part_o, 0xa00u + l);
+        publish(ds_ctr(p, l, DS_PO));
+        if (tw == 0) DS_TRACE(l, 2);
+        await(ds_ctr(p, l, DS_PO), E1 * (unsigned)n_o, 0xe00u + l);
+        if (tw == 0) DS_TRACE(l, 3);
+        rows_phase(p.part_o, p.so, l == 0 ? p.x_in : p.resid, l == 0 ? p.x_stride : (int64_t)p.H, ly.ln_post, p.xn, p.H, n_o);
         publish(ds_ctr(p, l, DS_XN_B));
         if (tw == 0) DS_TRACE(l, 6);
       } else if (op == OP_GU) {
-        ds_mbar_wait(p.sync, accfull, (uint32_t)(l & 1), 0xf00u + l);
-        if (tw == 0) DS_TRACE(l, 1);
-        tc_fence_after();
-        uint32_t v[64];
-        load_acc(v);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(accempty);
+        uint32_t v[32];
+        load_acc(l, v, 0xf00u + l);
         // packed gate_up rows (b2tts_gemm_pack_weight, B2TTS_PACK_GATE_UP): rows r with (r & 4) == 0 are gate features,
-        // r + 4 the matching up features; activation feature = tile * 64 + (r >> 3) * 4 + (r & 3)
+        // r + 4 the matching up features; activation feature = tile * 64 + (r >> 3) * 4 + (r & 3).  The two lanes of a
+        // pair exchange their values and share the work: the gate lane finishes the even batch rows, the up lane the odd.
+        const bool is_gate = (r & 4) == 0;
         __nv_bfloat16* dst = p.act + tile * 64 + (r >> 3) * 4 + (r & 3);
 #pragma unroll
-        for (int c = 0; c < 64; ++c) {
+        for (int c = 0; c < 32; ++c) {
+          const int cc = ch * 32 + c;
           const float mine = __uint_as_float(v[c]);
-          const float other = __shfl_down_sync(0xffffffffu, mine, 4);
-          if (c < M && (r & 4) == 0) {
-            const float gt = rbf(mine), up = rbf(other);
+          const float other = __shfl_xor_sync(0xffffffffu, mine, 4);
+          if (cc < M && ((cc & 1) == (is_gate ? 0 : 1))) {
+            const float gt = rbf(is_gate ? mine : other), up = rbf(is_gate ? other : mine);
             const float o = EAGER ? rbf(gsilu_f(gt)) * up : gsilu_f(gt) * up;
-            dst[(int64_t)c * p.I] = __float2bfloat16_rn(o);
+            dst[(int64_t)cc * p.I] = __float2bfloat16_rn(o);
           }
         }
         publish(ds_ctr(p, l, DS_ACT));
         if (tw == 0) DS_TRACE(l, 2);
       } else if (op == OP_DOWN) {
-        split_job(l, p.part_d, p.H, DS_T_D, p.resid, p.H);
-        publish(ds_ctr(p, l, DS_DOWN));
-        if (tw == 0) DS_TRACE(l, 4);
-        await(ds_ctr(p, l, DS_DOWN), E1 * (unsigned)n_d, 0x1000u + l);
-        if (tw == 0) DS_TRACE(l, 5);
-        const int j = cta - (p.nq_tiles + n_o + p.ng_tiles);
-        if (l + 1 < L) norm_rows(p.resid, p.H, p.layer[l + 1].ln_in, p.xn, p.H, j, n_d);
-        else norm_rows(p.resid, p.H, p.final_w, p.out, p.out_stride, j, n_d);
+        drain_partial(l, p.part_d, 0xb00u + l);
+        publish(ds_ctr(p, l, DS_PD));
+        if (tw == 0) DS_TRACE(l, 2);
+        await(ds_ctr(p, l, DS_PD), E1 * (unsigned)n_d, 0x1000u + l);
+        if (tw == 0) DS_TRACE(l, 3);
+        if (l + 1 < L) rows_phase(p.part_d, p.sd, p.resid, p.H, p.layer[l + 1].ln_in, p.xn, p.H, n_d);
+        else rows_phase(p.part_d, p.sd, p.resid, p.H, p.final_w, p.out, p.out_stride, n_d);
         publish(ds_ctr(p, l + 1, DS_XN_A));
         if (tw == 0) DS_TRACE(l, 6);
       }
@@ -785,6 +842,8 @@ extern "C" B2TTS_API int b2tts_decoder_stack_decode(
   DsPlan pl;
   B2_REQUIRE(ds_plan(hidden, Q, KV, intermediate, &pl), B2TTS_EUNSUPPORTED,
              "%s: hidden %d / intermediate %d do not fit one job per SM", what, hidden, intermediate);
+  B2_REQUIRE(m * num_kv_heads <= DS_ATT_WARPS * sm_count(), B2TTS_EUNSUPPORTED,
+             "%s: %d attention items exceed %d warps", what, m * num_kv_heads, DS_ATT_WARPS * sm_count());
   B2_REQUIRE(x && out && final_norm_weight && positions && inv_freq && slot_mapping && block_table && context_lens && workspace,
              B2TTS_EINVAL, "%s: null pointer", what);
   B2_REQUIRE(rounding == B2TTS_ROUND_EAGER || rounding == B2TTS_ROUND_FUSED, B2TTS_EINVAL, "%s: rounding %d", what, rounding);
@@ -842,7 +901,8 @@ extern "C" B2TTS_API int b2tts_decoder_stack_decode(
   if (rc) return rc;
 
   auto kern = rounding == B2TTS_ROUND_EAGER ? decoder_stack_kernel<true> : decoder_stack_kernel<false>;
-  const size_t smem_bytes = (size_t)DS_STAGES * DS_STAGE_BYTES + 4 * DS_SCR_BYTES + (3 * DS_STAGES + 2) * 8 + 16 + 1024;
+  const size_t smem_bytes = (size_t)DS_STAGES * DS_STAGE_BYTES + DS_ATT_WARPS * (DS_KV_BYTES + DS_SCR_BYTES) + 64 +
+                            (3 * DS_STAGES + 2) * 8 + 16 + 1024;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return cuda_fail(e, "decoder_stack_decode(smem attr)");
   cudaLaunchConfig_t cfg{};
