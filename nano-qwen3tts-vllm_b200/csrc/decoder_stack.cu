@@ -63,8 +63,7 @@ struct DsLayer {
   __nv_bfloat16 *k_cache, *v_cache;                      // [pages, page, kvh, 128]
 };
 
-struct DsParams {
-  DsLayer layer[DS_MAX_LAYERS];
+struct DsCore {
   int num_layers;
   const __nv_bfloat16* x_in;
   int64_t x_stride;
@@ -87,7 +86,10 @@ struct DsParams {
   float *part_o, *part_d;
   unsigned long long* trace;                     // debug: 16 globaltimer stamps per (CTA, layer) (null = off)
 };
-#define DS_TRACE(l, slot) do { if (p.trace) p.trace[((int64_t)cta * DS_MAX_LAYERS + (l)) * 16 + (slot)] = gtimer(); } while (0)
+struct DsParams : DsCore {
+  DsLayer layer[DS_MAX_LAYERS];
+};
+#define DS_TRACE(l, slot) do { if (p.trace) p.trace[((int64_t)blockIdx.x * DS_MAX_LAYERS + (l)) * 16 + (slot)] = gtimer(); } while (0)
 
 // ---------------------------------------------------------------- bounded waits
 __device__ __forceinline__ unsigned ds_ld_acquire(const unsigned* p) {
@@ -194,11 +196,12 @@ __device__ __forceinline__ void ds_kv_prefetch(const DsLayer& ly, const DsAttnIt
 // cached tokens come from the shared-memory copy (or, beyond DS_KV_PRE tokens, straight from the paged cache),
 // the new token from the warp's scratch.
 template <bool EAGER>
-__device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& ly, const DsAttnItem& it, int lane,
-                                             __nv_bfloat16* scr, const __nv_bfloat16* ksm, const __nv_bfloat16* vsm) {
+__device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& ly, int row, int hk, int L, int slot, int npre,
+                                          float c10, float c11, float s10, float s11, int lane,
+                                          __nv_bfloat16* scr, const __nv_bfloat16* ksm, const __nv_bfloat16* vsm) {
   const int kv_dim = p.kvh * DS_HD;
   const int qkv_w = p.Q + 2 * p.KV;
-  const int row = it.row, hk = it.hk, L = it.L;
+  const float c1[2] = {c10, c11}, s1[2] = {s10, s11};
   const int head0 = hk * DS_GROUP;
   const int g = lane >> 3, j = lane & 7;
   if (L <= 0) {                                   // CUDA-graph padding row: zeros
@@ -252,22 +255,22 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
       float o1[2], o2[2];
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
-        o1[e] = rbf(x1[e] * it.c1[e]) + rbf(-x2[e] * it.s1[e]);
-        o2[e] = rbf(x2[e] * it.c1[e]) + rbf(x1[e] * it.s1[e]);
+        o1[e] = rbf(x1[e] * c1[e]) + rbf(-x2[e] * s1[e]);
+        o2[e] = rbf(x2[e] * c1[e]) + rbf(x1[e] * s1[e]);
       }
       const uint32_t y1 = pack_bf16(o1[0], o1[1]), y2 = pack_bf16(o2[0], o2[1]);
       __nv_bfloat16* dst = is_k ? kn_s : q_s + i * DS_HD;
       *reinterpret_cast<uint32_t*>(dst + 2 * lane) = y1;
       *reinterpret_cast<uint32_t*>(dst + 64 + 2 * lane) = y2;
-      if (is_k && it.slot >= 0) {
-        __nv_bfloat16* cd = ly.k_cache + (int64_t)it.slot * kv_dim + hk * DS_HD;
+      if (is_k && slot >= 0) {
+        __nv_bfloat16* cd = ly.k_cache + (int64_t)slot * kv_dim + hk * DS_HD;
         *reinterpret_cast<uint32_t*>(cd + 2 * lane) = y1;
         *reinterpret_cast<uint32_t*>(cd + 64 + 2 * lane) = y2;
       }
     }
     if (lane < 16) {
       *reinterpret_cast<uint4*>(vn_s + 8 * lane) = vraw;
-      if (it.slot >= 0) stg_v4(ly.v_cache + (int64_t)it.slot * kv_dim + hk * DS_HD + 8 * lane, vraw);
+      if (slot >= 0) stg_v4(ly.v_cache + (int64_t)slot * kv_dim + hk * DS_HD + 8 * lane, vraw);
     }
   }
   ds_cp_async_wait_all();                         // this lane's staged K / V pieces have landed ...
@@ -294,38 +297,36 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
   for (int i = 0; i < n_tiles; ++i) {
     const int tok0 = i * DS_ATT_TILE;
     const int ntok = min(DS_ATT_TILE, L - tok0);
-    uint4 kraw[2][2], vr[2][2];
-    bool valid[2];
+    // K rows of this lane's two token slots, then (after the softmax) the V rows: staged tokens and the new token come
+    // from shared memory, anything beyond the staged window straight from the paged cache
+    const __nv_bfloat16* vp[DS_ATT_TILE / 4];
+    bool vsh[DS_ATT_TILE / 4];
+    float sc[DS_ATT_TILE / 4][DS_GROUP];
 #pragma unroll
     for (int s = 0; s < DS_ATT_TILE / 4; ++s) {
       const int tok = s * 4 + g;
-      valid[s] = tok < ntok;
-      const int t = tok0 + (valid[s] ? tok : 0);
-      const __nv_bfloat16 *kp, *vp;
-      if (t == L - 1) { kp = kn_s; vp = vn_s; }
-      else if (t < it.npre) { kp = ksm + t * DS_HD; vp = vsm + t * DS_HD; }
-      else { kp = nullptr; vp = nullptr; }
-      if (kp) {
-        kraw[s][0] = *reinterpret_cast<const uint4*>(kp + 8 * j);
-        kraw[s][1] = *reinterpret_cast<const uint4*>(kp + 64 + 8 * j);
-        vr[s][0] = *reinterpret_cast<const uint4*>(vp + 8 * j);
-        vr[s][1] = *reinterpret_cast<const uint4*>(vp + 64 + 8 * j);
+      const bool valid = tok < ntok;
+      const int t = tok0 + (valid ? tok : 0);
+      uint4 k0, k1;
+      if (t == L - 1) {
+        k0 = *reinterpret_cast<const uint4*>(kn_s + 8 * j);
+        k1 = *reinterpret_cast<const uint4*>(kn_s + 64 + 8 * j);
+        vp[s] = vn_s; vsh[s] = true;
+      } else if (t < npre) {
+        k0 = *reinterpret_cast<const uint4*>(ksm + t * DS_HD + 8 * j);
+        k1 = *reinterpret_cast<const uint4*>(ksm + t * DS_HD + 64 + 8 * j);
+        vp[s] = vsm + t * DS_HD; vsh[s] = true;
       } else {
         int page = __ldg(bt + t / p.page_size);
         if (page < 0) page = 0;
         const int64_t off = ((int64_t)page * p.page_size + t % p.page_size) * kv_dim + hk * DS_HD;
-        kraw[s][0] = ds_ldcg_v4(ly.k_cache + off + 8 * j);
-        kraw[s][1] = ds_ldcg_v4(ly.k_cache + off + 64 + 8 * j);
-        vr[s][0] = ds_ldcg_v4(ly.v_cache + off + 8 * j);
-        vr[s][1] = ds_ldcg_v4(ly.v_cache + off + 64 + 8 * j);
+        k0 = ds_ldcg_v4(ly.k_cache + off + 8 * j);
+        k1 = ds_ldcg_v4(ly.k_cache + off + 64 + 8 * j);
+        vp[s] = ly.v_cache + off; vsh[s] = false;
       }
-    }
-    float sc[DS_ATT_TILE / 4][DS_GROUP];
-#pragma unroll
-    for (int s = 0; s < DS_ATT_TILE / 4; ++s) {
       float kf[16];
-      ds_unpack8(kraw[s][0], kf);
-      ds_unpack8(kraw[s][1], kf + 8);
+      ds_unpack8(k0, kf);
+      ds_unpack8(k1, kf + 8);
 #pragma unroll
       for (int h = 0; h < DS_GROUP; ++h) {
         float d0 = 0.f, d1 = 0.f;
@@ -338,7 +339,7 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
         dot += __shfl_xor_sync(0xffffffffu, dot, 1);
         dot += __shfl_xor_sync(0xffffffffu, dot, 2);
         dot += __shfl_xor_sync(0xffffffffu, dot, 4);
-        sc[s][h] = valid[s] ? dot : -INFINITY;
+        sc[s][h] = valid ? dot : -INFINITY;
       }
     }
     float alpha[DS_GROUP];
@@ -364,9 +365,17 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
     }
 #pragma unroll
     for (int s = 0; s < DS_ATT_TILE / 4; ++s) {
+      uint4 v0, v1;
+      if (vsh[s]) {
+        v0 = *reinterpret_cast<const uint4*>(vp[s] + 8 * j);
+        v1 = *reinterpret_cast<const uint4*>(vp[s] + 64 + 8 * j);
+      } else {
+        v0 = ds_ldcg_v4(vp[s] + 8 * j);
+        v1 = ds_ldcg_v4(vp[s] + 64 + 8 * j);
+      }
       float vf[16];
-      ds_unpack8(vr[s][0], vf);
-      ds_unpack8(vr[s][1], vf + 8);
+      ds_unpack8(v0, vf);
+      ds_unpack8(v1, vf + 8);
 #pragma unroll
       for (int h = 0; h < DS_GROUP; ++h)
 #pragma unroll
@@ -414,23 +423,26 @@ __device__ __forceinline__ void ds_row_phase(const DsParams& p, int row, const f
     wv = ldg_v4(w + 8 * tw);
     const uint4 rw = ds_ldcg_v4(res + (int64_t)row * res_stride + 8 * tw);
     if (part) {
-      float4 a[8], b[8];
       const float* src = part + (int64_t)row * p.H + 8 * tw;
-#pragma unroll
-      for (int s = 0; s < 8; ++s)
-        if (s < S) {
-          a[s] = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)s * DS_MAX_M * p.H));
-          b[s] = __ldcg(reinterpret_cast<const float4*>(src + (int64_t)s * DS_MAX_M * p.H) + 1);
-        }
+      const int64_t sstride = (int64_t)DS_MAX_M * p.H;
       float acc[8];
 #pragma unroll
       for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+      for (int s0 = 0; s0 < S; s0 += 4) {           // 4 splits in flight; summed in split order
+        float4 a[4], b[4];
 #pragma unroll
-      for (int s = 0; s < 8; ++s)
-        if (s < S) {
-          acc[0] += a[s].x; acc[1] += a[s].y; acc[2] += a[s].z; acc[3] += a[s].w;
-          acc[4] += b[s].x; acc[5] += b[s].y; acc[6] += b[s].z; acc[7] += b[s].w;
-        }
+        for (int s = 0; s < 4; ++s)
+          if (s0 + s < S) {
+            a[s] = __ldcg(reinterpret_cast<const float4*>(src + (s0 + s) * sstride));
+            b[s] = __ldcg(reinterpret_cast<const float4*>(src + (s0 + s) * sstride) + 1);
+          }
+#pragma unroll
+        for (int s = 0; s < 4; ++s)
+          if (s0 + s < S) {
+            acc[0] += a[s].x; acc[1] += a[s].y; acc[2] += a[s].z; acc[3] += a[s].w;
+            acc[4] += b[s].x; acc[5] += b[s].y; acc[6] += b[s].z; acc[7] += b[s].w;
+          }
+      }
       acc[0] = rbf(acc[0]) + bf16lo(rw.x); acc[1] = rbf(acc[1]) + bf16hi(rw.x);
       acc[2] = rbf(acc[2]) + bf16lo(rw.y); acc[3] = rbf(acc[3]) + bf16hi(rw.y);
       acc[4] = rbf(acc[4]) + bf16lo(rw.z); acc[5] = rbf(acc[5]) + bf16hi(rw.z);
@@ -462,9 +474,186 @@ __device__ __forceinline__ void ds_row_phase(const DsParams& p, int row, const f
   }
 }
 
+// Everything a worker warp needs about its CTA's job (scalarised by the compiler: every user is inlined).
+struct DsCtx {
+  uint32_t tmem_base;
+  uint64_t *accfull, *accempty;
+  unsigned E1;
+  int G, cta, L, tile, split, job, n_o, n_d;
+  DsLayer* layers;
+  uint8_t *scr_base, *kv_base;
+  float* red_s;
+};
+
+// One worker warp for the whole launch, specialised by the CTA's job so that each job's layer loop carries only its
+// own epilogue (one merged loop made the compiler keep every job's hoisted addresses live at once, and spill).
+template <bool EAGER, int OP>
+__device__ __forceinline__ void ds_worker(const DsParams& p, const DsCtx& c, int warp, int lane) {
+  const int cta = c.cta, G = c.G, L = c.L;
+  const int tw = threadIdx.x - DS_W0;             // 0..255
+  const int ww = warp - 3;                        // 0..7
+  const int wq = warp & 3;                        // TMEM lane quarter this warp may read
+  const int ch = ww >> 2;                         // which 32 accumulator columns (batch rows) this warp drains
+  const int r = wq * 32 + lane;                   // row of the 128-feature tile held by this thread
+  const int M = p.m;
+  const int kv_dim = p.kvh * DS_HD;
+  const unsigned E1 = c.E1;
+  __nv_bfloat16* scr = reinterpret_cast<__nv_bfloat16*>(c.scr_base + (ww & (DS_ATT_WARPS - 1)) * DS_SCR_BYTES);
+  __nv_bfloat16* ksm = reinterpret_cast<__nv_bfloat16*>(c.kv_base + (ww & (DS_ATT_WARPS - 1)) * DS_KV_BYTES);
+  __nv_bfloat16* vsm = ksm + DS_KV_PRE * DS_HD;
+
+  // ---- this warp's attention item (warps 0-3: item = warp * G + cta), fixed for the launch
+  DsAttnItem item;
+  const int item_id = ww * G + cta;
+  const bool has_item = ww < DS_ATT_WARPS && item_id < M * p.kvh;
+  item.row = has_item ? item_id / p.kvh : 0;
+  item.hk = has_item ? item_id % p.kvh : 0;
+  item.L = 0; item.slot = -1; item.npre = 0;
+  item.c1[0] = item.c1[1] = item.s1[0] = item.s1[1] = 0.f;
+#pragma unroll
+  for (int i = 0; i < DS_KV_PRE / 2; ++i) item.tokslot[i] = 0xffffffffu;
+  if (has_item) {
+    item.L = __ldg(p.context_lens + item.row);
+    item.slot = __ldg(p.slot_mapping + item.row);
+    const int64_t pos = __ldg(p.positions + item.row);
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const float a1 = (float)pos * __ldg(p.inv_freq + 2 * lane + e);
+      item.c1[e] = rbf(cosf(a1) * p.attention_scaling);
+      item.s1[e] = rbf(sinf(a1) * p.attention_scaling);
+    }
+    item.npre = max(0, min(item.L - 1, DS_KV_PRE));
+    const int32_t* bt = p.block_table + (int64_t)item.row * p.bt_stride;
+#pragma unroll
+    for (int i = 0; i < DS_KV_PRE / 2; ++i) {
+      const int tok = 2 * i + (lane >> 4);
+      if (tok < item.npre) {
+        int page = __ldg(bt + tok / p.page_size);
+        if (page < 0) page = 0;
+        item.tokslot[i] = (uint32_t)(page * p.page_size + tok % p.page_size);
+      }
+    }
+  }
+
+  auto publish = [&](unsigned* ctr) {             // bar.sync orders every worker's stores before the one release
+    ds_workers_bar();
+    if (tw == 0) ds_arrive(ctr);
+  };
+  auto await = [&](unsigned* ctr, unsigned target, unsigned code) {
+    if (tw == 0) ds_wait(p.sync, ctr, target, code);
+    ds_workers_bar();
+  };
+  auto load_acc = [&](int l, uint32_t* v, unsigned code) {      // this warp's 32 accumulator columns of row r
+    ds_mbar_wait(p.sync, c.accfull, (uint32_t)(l & 1), code);
+    if (tw == 0) DS_TRACE(l, 1);
+    tc_fence_after();
+    const int nq = p.mpad >> 4;
+#pragma unroll
+    for (int qq = 0; qq < 2; ++qq)
+      if (ch * 2 + qq < nq)
+        tmem_ld16_nowait(c.tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(ch * 32 + 16 * qq), v + 16 * qq);
+    tmem_ld_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(c.accempty);
+  };
+  // rows this CTA finishes after a split-K projection: job j of the n jobs of the op owns rows j, j + n, ...
+  int red_flip = 0;
+  auto rows_phase = [&](const float* part, int nsplit, const __nv_bfloat16* res, int64_t res_stride, const __nv_bfloat16* w,
+                        __nv_bfloat16* dst, int64_t dst_stride, int n) {
+    for (int row = c.job; row < M; row += n) {
+      ds_row_phase<EAGER>(p, row, part, nsplit, res, res_stride, w, dst + (int64_t)row * dst_stride, tw, c.red_s + 8 * red_flip);
+      red_flip ^= 1;
+    }
+  };
+  auto drain_partial = [&](int l, float* part, unsigned code) {
+    uint32_t v[32];
+    load_acc(l, v, code);
+    float* dst = part + (int64_t)c.split * DS_MAX_M * p.H + (int64_t)c.tile * G_BN + r;
+    asm volatile("" : "+l"(dst));                 // keeps the 32 store addresses from being hoisted out of the layer loop
+#pragma unroll
+    for (int cc = 0; cc < 32; ++cc)
+      if (ch * 32 + cc < M) __stcg(dst + (int64_t)(ch * 32 + cc) * p.H, __uint_as_float(v[cc]));
+  };
+
+  // the first layer's input norm: done by the down jobs (idle until the first MLP)
+  if (OP == OP_DOWN) {
+    rows_phase(nullptr, 0, p.x_in, p.x_stride, c.layers[0].ln_in, p.xn, p.H, c.n_d);
+    publish(ds_ctr(p, 0, DS_XN_A));
+  }
+  for (int l = 0; l < L; ++l) {
+    const DsLayer& ly = c.layers[l];
+    if (tw == 0) DS_TRACE(l, 0);
+    if (has_item && item.L > 0) ds_kv_prefetch(ly, item, kv_dim, lane, ksm, vsm);
+    if (OP == OP_QKV) {
+      uint32_t v[32];
+      load_acc(l, v, 0xc00u + l);
+      __nv_bfloat16* dst = p.qkv + c.tile * G_BN + r;
+      asm volatile("" : "+l"(dst));
+      const int qkv_w = p.Q + 2 * p.KV;
+#pragma unroll
+      for (int cc = 0; cc < 32; ++cc)
+        if (ch * 32 + cc < M) dst[(int64_t)(ch * 32 + cc) * qkv_w] = __float2bfloat16_rn(__uint_as_float(v[cc]));
+      publish(ds_ctr(p, l, DS_QKV));
+      if (tw == 0) DS_TRACE(l, 2);
+    }
+    // ---- attention: the first 4 worker warps of every CTA, one (row, kv head) item each
+    await(ds_ctr(p, l, DS_QKV), E1 * (unsigned)p.nq_tiles, 0xd00u + l);
+    if (tw == 0) DS_TRACE(l, 7);
+    if (has_item)
+      ds_attn_item<EAGER>(p, ly, item.row, item.hk, item.L, item.slot, item.npre, item.c1[0], item.c1[1], item.s1[0],
+                          item.s1[1], lane, scr, ksm, vsm);
+    publish(ds_ctr(p, l, DS_ATT));
+    if (tw == 0) DS_TRACE(l, 8);
+    if (OP == OP_O) {
+      drain_partial(l, p.part_o, 0xa00u + l);
+      publish(ds_ctr(p, l, DS_PO));
+      if (tw == 0) DS_TRACE(l, 2);
+      await(ds_ctr(p, l, DS_PO), E1 * (unsigned)c.n_o, 0xe00u + l);
+      if (tw == 0) DS_TRACE(l, 3);
+      rows_phase(p.part_o, p.so, l == 0 ? p.x_in : p.resid, l == 0 ? p.x_stride : (int64_t)p.H, ly.ln_post, p.xn, p.H, c.n_o);
+      publish(ds_ctr(p, l, DS_XN_B));
+      if (tw == 0) DS_TRACE(l, 6);
+    } else if (OP == OP_GU) {
+      uint32_t v[32];
+      load_acc(l, v, 0xf00u + l);
+      // packed gate_up rows (b2tts_gemm_pack_weight, B2TTS_PACK_GATE_UP): rows r with (r & 4) == 0 are gate features,
+      // r + 4 the matching up features; activation feature = tile * 64 + (r >> 3) * 4 + (r & 3).  The two lanes of a
+      // pair exchange their values and share the work: the gate lane finishes the even batch rows, the up lane the odd.
+      const bool is_gate = (r & 4) == 0;
+      __nv_bfloat16* dst = p.act + c.tile * 64 + (r >> 3) * 4 + (r & 3);
+      asm volatile("" : "+l"(dst));
+#pragma unroll
+      for (int cc = 0; cc < 32; ++cc) {
+        const int col = ch * 32 + cc;
+        const float mine = __uint_as_float(v[cc]);
+        const float other = __shfl_xor_sync(0xffffffffu, mine, 4);
+        if (col < M && ((col & 1) == (is_gate ? 0 : 1))) {
+          const float gt = rbf(is_gate ? mine : other), up = rbf(is_gate ? other : mine);
+          const float o = EAGER ? rbf(gsilu_f(gt)) * up : gsilu_f(gt) * up;
+          dst[(int64_t)col * p.I] = __float2bfloat16_rn(o);
+        }
+      }
+      publish(ds_ctr(p, l, DS_ACT));
+      if (tw == 0) DS_TRACE(l, 2);
+    } else if (OP == OP_DOWN) {
+      drain_partial(l, p.part_d, 0xb00u + l);
+      publish(ds_ctr(p, l, DS_PD));
+      if (tw == 0) DS_TRACE(l, 2);
+      await(ds_ctr(p, l, DS_PD), E1 * (unsigned)c.n_d, 0x1000u + l);
+      if (tw == 0) DS_TRACE(l, 3);
+      if (l + 1 < L) rows_phase(p.part_d, p.sd, p.resid, p.H, c.layers[l + 1].ln_in, p.xn, p.H, c.n_d);
+      else rows_phase(p.part_d, p.sd, p.resid, p.H, p.final_w, p.out, p.out_stride, c.n_d);
+      publish(ds_ctr(p, l + 1, DS_XN_A));
+      if (tw == 0) DS_TRACE(l, 6);
+    }
+  }
+}
+
+
 template <bool EAGER>
 __global__ void __launch_bounds__(DS_THREADS, 1)
-decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn, const __grid_constant__ CUtensorMap tm_attn,
+decoder_stack_kernel(const DsParams kp, const __grid_constant__ CUtensorMap tm_xn, const __grid_constant__ CUtensorMap tm_attn,
                      const __grid_constant__ CUtensorMap tm_act) {
   extern __shared__ uint8_t smem_dyn[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
@@ -477,38 +666,47 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
   uint64_t* accfull = empty + DS_STAGES;
   uint64_t* accempty = accfull + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accempty + 1);
+  // the per-layer pointer table, copied out of param space once: indexing p.layer[] with a run-time layer would make
+  // the compiler keep a copy in LOCAL memory, and every acquire / release invalidates L1 (each pointer read = L2 trip)
+  DsParams* ps = reinterpret_cast<DsParams*>(tmem_slot + 4);
+  DsLayer* layers_s = ps->layer;
+  const DsParams& p = *ps;                          // the shared-memory copy (valid after the first __syncthreads)
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const int G = gridDim.x;
   const int cta = blockIdx.x;
-  const int L = p.num_layers;
+  const int L = kp.num_layers;
 
   // ---- this CTA's job (the same in every layer)
   int op = OP_NONE, tile = 0, split = 0, S = 1, kblocks = 0, job = 0;
   {
     int c = cta;
-    if (c < p.nq_tiles) { op = OP_QKV; tile = c; kblocks = p.H / G_BK; }
-    else if ((c -= p.nq_tiles) < p.no_tiles * p.so) { op = OP_O; S = p.so; tile = c / S; split = c - tile * S; kblocks = p.Q / G_BK; }
-    else if ((c -= p.no_tiles * p.so) < p.ng_tiles) { op = OP_GU; tile = c; kblocks = p.H / G_BK; }
-    else if ((c -= p.ng_tiles) < p.nd_tiles * p.sd) { op = OP_DOWN; S = p.sd; tile = c / S; split = c - tile * S; kblocks = p.I / G_BK; }
+    if (c < kp.nq_tiles) { op = OP_QKV; tile = c; kblocks = kp.H / G_BK; }
+    else if ((c -= kp.nq_tiles) < kp.no_tiles * kp.so) { op = OP_O; S = kp.so; tile = c / S; split = c - tile * S; kblocks = kp.Q / G_BK; }
+    else if ((c -= kp.no_tiles * kp.so) < kp.ng_tiles) { op = OP_GU; tile = c; kblocks = kp.H / G_BK; }
+    else if ((c -= kp.ng_tiles) < kp.nd_tiles * kp.sd) { op = OP_DOWN; S = kp.sd; tile = c / S; split = c - tile * S; kblocks = kp.I / G_BK; }
     job = c;
   }
   const int kb0 = (split * kblocks) / S, kb1 = ((split + 1) * kblocks) / S;
-  const int n_o = p.no_tiles * p.so, n_d = p.nd_tiles * p.sd;
+  const int n_o = kp.no_tiles * kp.so, n_d = kp.nd_tiles * kp.sd;
 
+#pragma unroll
+  for (int i = 0; i < DS_MAX_LAYERS; ++i)
+    if ((int)threadIdx.x == 32 + i) layers_s[i] = kp.layer[i];
+  if (threadIdx.x == 64) static_cast<DsCore&>(*ps) = static_cast<const DsCore&>(kp);
   if (threadIdx.x == 0) {
     for (int s = 0; s < DS_STAGES; ++s) { mbar_init(wfull + s, 1); mbar_init(xfull + s, 1); mbar_init(empty + s, 1); }
     mbar_init(accfull, 1);
     mbar_init(accempty, DS_WORKERS / 32);
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)p.tmem_cols);
+  if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)kp.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const unsigned E = __ldcg(p.sync);               // launch epoch: counter targets are (E + 1) * arrivals
+  const unsigned E = __ldcg(kp.sync);               // launch epoch: counter targets are (E + 1) * arrivals
   const unsigned E1 = E + 1u;
   if (threadIdx.x == 0) DS_TRACE(0, 13);
 
@@ -517,7 +715,7 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
     if (op != OP_NONE) {
       uint32_t slot = 0, ph = 1;
       for (int l = 0; l < L; ++l) {
-        const DsLayer& ly = p.layer[l];
+        const DsLayer& ly = layers_s[l];
         const uint8_t* wp = op == OP_QKV ? ly.w_qkv : op == OP_O ? ly.w_o : op == OP_GU ? ly.w_gu : ly.w_down;
         const uint8_t* src = wp + ((int64_t)tile * kblocks + kb0) * G_WTILE_BYTES;
         // the k-blocks that do not fit the ring are at least pulled into L2 now, a layer ahead of their use
@@ -602,156 +800,17 @@ decoder_stack_kernel(const DsParams p, const __grid_constant__ CUtensorMap tm_xn
     __syncwarp();
   } else {
     // =========================== workers (8 warps): epilogues, split reduce + row norms, attention
-    const int tw = threadIdx.x - DS_W0;             // 0..255
-    const int ww = warp - 3;                        // 0..7
-    const int wq = warp & 3;                        // TMEM lane quarter this warp may read
-    const int ch = ww >> 2;                         // which 32 accumulator columns (batch rows) this warp drains
-    const int r = wq * 32 + lane;                   // row of the 128-feature tile held by this thread
-    const int M = p.m;
-    const int kv_dim = p.kvh * DS_HD;
-    __nv_bfloat16* scr = reinterpret_cast<__nv_bfloat16*>(scr_base + (ww & (DS_ATT_WARPS - 1)) * DS_SCR_BYTES);
-    __nv_bfloat16* ksm = reinterpret_cast<__nv_bfloat16*>(kv_base + (ww & (DS_ATT_WARPS - 1)) * DS_KV_BYTES);
-    __nv_bfloat16* vsm = ksm + DS_KV_PRE * DS_HD;
     pdl_wait();
-
-    // ---- this warp's attention item (warps 0-3: item = warp * G + cta), fixed for the launch
-    DsAttnItem item;
-    const int item_id = ww * G + cta;
-    const bool has_item = ww < DS_ATT_WARPS && item_id < M * p.kvh;
-    item.row = has_item ? item_id / p.kvh : 0;
-    item.hk = has_item ? item_id % p.kvh : 0;
-    item.L = 0; item.slot = -1; item.npre = 0;
-    if (has_item) {
-      item.L = __ldg(p.context_lens + item.row);
-      item.slot = __ldg(p.slot_mapping + item.row);
-      const int64_t pos = __ldg(p.positions + item.row);
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const float a1 = (float)pos * __ldg(p.inv_freq + 2 * lane + e);
-        item.c1[e] = rbf(cosf(a1) * p.attention_scaling);
-        item.s1[e] = rbf(sinf(a1) * p.attention_scaling);
-      }
-      item.npre = max(0, min(item.L - 1, DS_KV_PRE));
-      const int32_t* bt = p.block_table + (int64_t)item.row * p.bt_stride;
-#pragma unroll
-      for (int i = 0; i < DS_KV_PRE / 2; ++i) {
-        const int tok = 2 * i + (lane >> 4);
-        item.tokslot[i] = 0xffffffffu;
-        if (tok < item.npre) {
-          int page = __ldg(bt + tok / p.page_size);
-          if (page < 0) page = 0;
-          item.tokslot[i] = (uint32_t)(page * p.page_size + tok % p.page_size);
-        }
-      }
-    }
-
-    auto publish = [&](unsigned* ctr) {             // bar.sync orders every worker's stores before the one release
-      ds_workers_bar();
-      if (tw == 0) ds_arrive(ctr);
-    };
-    auto await = [&](unsigned* ctr, unsigned target, unsigned code) {
-      if (tw == 0) ds_wait(p.sync, ctr, target, code);
-      ds_workers_bar();
-    };
-    auto load_acc = [&](int l, uint32_t* v, unsigned code) {      // this warp's 32 accumulator columns of row r
-      ds_mbar_wait(p.sync, accfull, (uint32_t)(l & 1), code);
-      if (tw == 0) DS_TRACE(l, 1);
-      tc_fence_after();
-      const int nq = p.mpad >> 4;
-#pragma unroll
-      for (int qq = 0; qq < 2; ++qq)
-        if (ch * 2 + qq < nq)
-          tmem_ld16_nowait(tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(ch * 32 + 16 * qq), v + 16 * qq);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(accempty);
-    };
-    // rows this CTA finishes after a split-K projection: job j of the n jobs of the op owns rows j, j + n, ...
-    int red_flip = 0;
-    auto rows_phase = [&](const float* part, int nsplit, const __nv_bfloat16* res, int64_t res_stride, const __nv_bfloat16* w,
-                          __nv_bfloat16* dst, int64_t dst_stride, int n) {
-      for (int row = job; row < M; row += n) {
-        ds_row_phase<EAGER>(p, row, part, nsplit, res, res_stride, w, dst + (int64_t)row * dst_stride, tw, red_s + 8 * red_flip);
-        red_flip ^= 1;
-      }
-    };
-    auto drain_partial = [&](int l, float* part, unsigned code) {
-      uint32_t v[32];
-      load_acc(l, v, code);
-      float* dst = part + (int64_t)split * DS_MAX_M * p.H + (int64_t)tile * G_BN + r;
-#pragma unroll
-      for (int c = 0; c < 32; ++c)
-        if (ch * 32 + c < M) __stcg(dst + (int64_t)(ch * 32 + c) * p.H, __uint_as_float(v[c]));
-    };
-
-    // the first layer's input norm: done by the down jobs (idle until the first MLP)
-    if (op == OP_DOWN) {
-      rows_phase(nullptr, 0, p.x_in, p.x_stride, p.layer[0].ln_in, p.xn, p.H, n_d);
-      publish(ds_ctr(p, 0, DS_XN_A));
-    }
-    for (int l = 0; l < L; ++l) {
-      const DsLayer& ly = p.layer[l];
-      if (tw == 0) DS_TRACE(l, 0);
-      if (has_item && item.L > 0) ds_kv_prefetch(ly, item, kv_dim, lane, ksm, vsm);
-      if (op == OP_QKV) {
-        uint32_t v[32];
-        load_acc(l, v, 0xc00u + l);
-        __nv_bfloat16* dst = p.qkv + tile * G_BN + r;
-        const int qkv_w = p.Q + 2 * p.KV;
-#pragma unroll
-        for (int c = 0; c < 32; ++c)
-          if (ch * 32 + c < M) dst[(int64_t)(ch * 32 + c) * qkv_w] = __float2bfloat16_rn(__uint_as_float(v[c]));
-        publish(ds_ctr(p, l, DS_QKV));
-        if (tw == 0) DS_TRACE(l, 2);
-      }
-      // ---- attention: the first 4 worker warps of every CTA, one (row, kv head) item each
-      await(ds_ctr(p, l, DS_QKV), E1 * (unsigned)p.nq_tiles, 0xd00u + l);
-      if (tw == 0) DS_TRACE(l, 7);
-      if (has_item) ds_attn_item<EAGER>(p, ly, item, lane, scr, ksm, vsm);
-      publish(ds_ctr(p, l, DS_ATT));
-      if (tw == 0) DS_TRACE(l, 8);
-      if (op == OP_O) {
-        drain_partial(l, p.part_o, 0xa00u + l);
-        publish(ds_ctr(p, l, DS_PO));
-        if (tw == 0) DS_TRACE(l, 2);
-        await(ds_ctr(p, l, DS_PO), E1 * (unsigned)n_o, 0xe00u + l);
-        if (tw == 0) DS_TRACE(l, 3);
-        rows_phase(p.part_o, p.so, l == 0 ? p.x_in : p.resid, l == 0 ? p.x_stride : (int64_t)p.H, ly.ln_post, p.xn, p.H, n_o);
-        publish(ds_ctr(p, l, DS_XN_B));
-        if (tw == 0) DS_TRACE(l, 6);
-      } else if (op == OP_GU) {
-        uint32_t v[32];
-        load_acc(l, v, 0xf00u + l);
-        // packed gate_up rows (b2tts_gemm_pack_weight, B2TTS_PACK_GATE_UP): rows r with (r & 4) == 0 are gate features,
-        // r + 4 the matching up features; activation feature = tile * 64 + (r >> 3) * 4 + (r & 3).  The two lanes of a
-        // pair exchange their values and share the work: the gate lane finishes the even batch rows, the up lane the odd.
-        const bool is_gate = (r & 4) == 0;
-        __nv_bfloat16* dst = p.act + tile * 64 + (r >> 3) * 4 + (r & 3);
-#pragma unroll
-        for (int c = 0; c < 32; ++c) {
-          const int cc = ch * 32 + c;
-          const float mine = __uint_as_float(v[c]);
-          const float other = __shfl_xor_sync(0xffffffffu, mine, 4);
-          if (cc < M && ((cc & 1) == (is_gate ? 0 : 1))) {
-            const float gt = rbf(is_gate ? mine : other), up = rbf(is_gate ? other : mine);
-            const float o = EAGER ? rbf(gsilu_f(gt)) * up : gsilu_f(gt) * up;
-            dst[(int64_t)cc * p.I] = __float2bfloat16_rn(o);
-          }
-        }
-        publish(ds_ctr(p, l, DS_ACT));
-        if (tw == 0) DS_TRACE(l, 2);
-      } else if (op == OP_DOWN) {
-        drain_partial(l, p.part_d, 0xb00u + l);
-        publish(ds_ctr(p, l, DS_PD));
-        if (tw == 0) DS_TRACE(l, 2);
-        await(ds_ctr(p, l, DS_PD), E1 * (unsigned)n_d, 0x1000u + l);
-        if (tw == 0) DS_TRACE(l, 3);
-        if (l + 1 < L) rows_phase(p.part_d, p.sd, p.resid, p.H, p.layer[l + 1].ln_in, p.xn, p.H, n_d);
-        else rows_phase(p.part_d, p.sd, p.resid, p.H, p.final_w, p.out, p.out_stride, n_d);
-        publish(ds_ctr(p, l + 1, DS_XN_A));
-        if (tw == 0) DS_TRACE(l, 6);
-      }
+    DsCtx c;
+    c.tmem_base = tmem_base; c.accfull = accfull; c.accempty = accempty; c.E1 = E1;
+    c.G = G; c.cta = cta; c.L = L; c.tile = tile; c.split = split; c.job = job; c.n_o = n_o; c.n_d = n_d;
+    c.layers = layers_s; c.scr_base = scr_base; c.kv_base = kv_base; c.red_s = red_s;
+    switch (op) {
+      case OP_QKV: ds_worker<EAGER, OP_QKV>(p, c, warp, lane); break;
+      case OP_O: ds_worker<EAGER, OP_O>(p, c, warp, lane); break;
+      case OP_GU: ds_worker<EAGER, OP_GU>(p, c, warp, lane); break;
+      case OP_DOWN: ds_worker<EAGER, OP_DOWN>(p, c, warp, lane); break;
+      default: ds_worker<EAGER, OP_NONE>(p, c, warp, lane); break;
     }
   }
   tc_fence_before();
@@ -902,7 +961,7 @@ extern "C" B2TTS_API int b2tts_decoder_stack_decode(
 
   auto kern = rounding == B2TTS_ROUND_EAGER ? decoder_stack_kernel<true> : decoder_stack_kernel<false>;
   const size_t smem_bytes = (size_t)DS_STAGES * DS_STAGE_BYTES + DS_ATT_WARPS * (DS_KV_BYTES + DS_SCR_BYTES) + 64 +
-                            (3 * DS_STAGES + 2) * 8 + 16 + 1024;
+                            (3 * DS_STAGES + 2) * 8 + 16 + sizeof(DsParams) + 1024;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return cuda_fail(e, "decoder_stack_decode(smem attr)");
   cudaLaunchConfig_t cfg{};
