@@ -84,12 +84,12 @@ struct DsCore {
   unsigned* sync;
   __nv_bfloat16 *xn, *resid, *qkv, *attn, *act;
   float *part_o, *part_d;
-  unsigned long long* trace;                     // debug: 16 globaltimer stamps per (CTA, layer) (null = off)
+  unsigned long long* trace;                     // debug: 32 globaltimer stamps per (CTA, layer) (null = off)
 };
 struct DsParams : DsCore {
   DsLayer layer[DS_MAX_LAYERS];
 };
-#define DS_TRACE(l, slot) do { if (p.trace) p.trace[((int64_t)blockIdx.x * DS_MAX_LAYERS + (l)) * 16 + (slot)] = gtimer(); } while (0)
+#define DS_TRACE(l, slot) do { if (p.trace) p.trace[((int64_t)blockIdx.x * DS_MAX_LAYERS + (l)) * 32 + (slot)] = gtimer(); } while (0)
 
 // ---------------------------------------------------------------- bounded waits
 __device__ __forceinline__ unsigned ds_ld_acquire(const unsigned* p) {
@@ -198,7 +198,8 @@ __device__ __forceinline__ void ds_kv_prefetch(const DsLayer& ly, const DsAttnIt
 template <bool EAGER>
 __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& ly, int row, int hk, int L, int slot, int npre,
                                           float c10, float c11, float s10, float s11, int lane,
-                                          __nv_bfloat16* scr, const __nv_bfloat16* ksm, const __nv_bfloat16* vsm) {
+                                          __nv_bfloat16* scr, const __nv_bfloat16* ksm, const __nv_bfloat16* vsm,
+                                          unsigned long long* tr) {
   const int kv_dim = p.kvh * DS_HD;
   const int qkv_w = p.Q + 2 * p.KV;
   const float c1[2] = {c10, c11}, s1[2] = {s10, s11};
@@ -273,6 +274,7 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
       if (slot >= 0) stg_v4(ly.v_cache + (int64_t)slot * kv_dim + hk * DS_HD + 8 * lane, vraw);
     }
   }
+  if (tr && lane == 0) tr[4] = gtimer();
   ds_cp_async_wait_all();                         // this lane's staged K / V pieces have landed ...
   __syncwarp();                                   // ... and so have everybody else's, and the scratch rows
 
@@ -392,6 +394,7 @@ __device__ __forceinline__ void ds_attn_item(const DsParams& p, const DsLayer& l
       acc[h][d] += __shfl_xor_sync(0xffffffffu, acc[h][d], 16);
     }
   }
+  if (tr && lane == 0) tr[5] = gtimer();
   if (g == 0) {
 #pragma unroll
     for (int h = 0; h < DS_GROUP; ++h) {
@@ -576,6 +579,9 @@ __device__ __forceinline__ void ds_worker(const DsParams& p, const DsCtx& c, int
       if (ch * 32 + cc < M) __stcg(dst + (int64_t)(ch * 32 + cc) * p.H, __uint_as_float(v[cc]));
   };
 
+  // the cached K / V rows of an item do not depend on this launch: layer 0's are staged now, layer l + 1's as soon as
+  // the attention of layer l has released the staging area
+  if (has_item && item.L > 0) ds_kv_prefetch(c.layers[0], item, kv_dim, lane, ksm, vsm);
   // the first layer's input norm: done by the down jobs (idle until the first MLP)
   if (OP == OP_DOWN) {
     rows_phase(nullptr, 0, p.x_in, p.x_stride, c.layers[0].ln_in, p.xn, p.H, c.n_d);
@@ -584,7 +590,6 @@ __device__ __forceinline__ void ds_worker(const DsParams& p, const DsCtx& c, int
   for (int l = 0; l < L; ++l) {
     const DsLayer& ly = c.layers[l];
     if (tw == 0) DS_TRACE(l, 0);
-    if (has_item && item.L > 0) ds_kv_prefetch(ly, item, kv_dim, lane, ksm, vsm);
     if (OP == OP_QKV) {
       uint32_t v[32];
       load_acc(l, v, 0xc00u + l);
@@ -602,8 +607,15 @@ __device__ __forceinline__ void ds_worker(const DsParams& p, const DsCtx& c, int
     if (tw == 0) DS_TRACE(l, 7);
     if (has_item)
       ds_attn_item<EAGER>(p, ly, item.row, item.hk, item.L, item.slot, item.npre, item.c1[0], item.c1[1], item.s1[0],
-                          item.s1[1], lane, scr, ksm, vsm);
-    publish(ds_ctr(p, l, DS_ATT));
+                          item.s1[1], lane, scr, ksm, vsm,
+                          (p.trace && ww == 0) ? p.trace + ((int64_t)cta * DS_MAX_LAYERS + l) * 32 : nullptr);
+    if (tw == 0) DS_TRACE(l, 15);
+    if (lane == 0 && ww < 4) DS_TRACE(l, 20 + ww);
+    ds_workers_bar();
+    if (tw == 0) DS_TRACE(l, 16);
+    if (tw == 0) ds_arrive(ds_ctr(p, l, DS_ATT));
+    if (tw == 0) DS_TRACE(l, 17);
+    if (has_item && item.L > 0 && l + 1 < L) ds_kv_prefetch(c.layers[l + 1], item, kv_dim, lane, ksm, vsm);
     if (tw == 0) DS_TRACE(l, 8);
     if (OP == OP_O) {
       drain_partial(l, p.part_o, 0xa00u + l);
@@ -624,12 +636,12 @@ __device__ __forceinline__ void ds_worker(const DsParams& p, const DsCtx& c, int
       __nv_bfloat16* dst = p.act + c.tile * 64 + (r >> 3) * 4 + (r & 3);
       asm volatile("" : "+l"(dst));
 #pragma unroll
-      for (int cc = 0; cc < 32; ++cc) {
-        const int col = ch * 32 + cc;
-        const float mine = __uint_as_float(v[cc]);
-        const float other = __shfl_xor_sync(0xffffffffu, mine, 4);
-        if (col < M && ((col & 1) == (is_gate ? 0 : 1))) {
-          const float gt = rbf(is_gate ? mine : other), up = rbf(is_gate ? other : mine);
+      for (int c2 = 0; c2 < 16; ++c2) {
+        const float a = __uint_as_float(v[2 * c2]), b = __uint_as_float(v[2 * c2 + 1]);
+        const float oa = __shfl_xor_sync(0xffffffffu, a, 4), ob = __shfl_xor_sync(0xffffffffu, b, 4);
+        const int col = ch * 32 + 2 * c2 + (is_gate ? 0 : 1);
+        if (col < M) {
+          const float gt = rbf(is_gate ? a : ob), up = rbf(is_gate ? oa : b);
           const float o = EAGER ? rbf(gsilu_f(gt)) * up : gsilu_f(gt) * up;
           dst[(int64_t)col * p.I] = __float2bfloat16_rn(o);
         }
@@ -642,8 +654,9 @@ __device__ __forceinline__ void ds_worker(const DsParams& p, const DsCtx& c, int
       if (tw == 0) DS_TRACE(l, 2);
       await(ds_ctr(p, l, DS_PD), E1 * (unsigned)c.n_d, 0x1000u + l);
       if (tw == 0) DS_TRACE(l, 3);
-      if (l + 1 < L) rows_phase(p.part_d, p.sd, p.resid, p.H, c.layers[l + 1].ln_in, p.xn, p.H, c.n_d);
-      else rows_phase(p.part_d, p.sd, p.resid, p.H, p.final_w, p.out, p.out_stride, c.n_d);
+      const bool last = l + 1 == L;               // the last layer's rows get the final norm and leave the kernel
+      rows_phase(p.part_d, p.sd, p.resid, p.H, last ? p.final_w : c.layers[l + 1].ln_in, last ? p.out : p.xn,
+                 last ? p.out_stride : (int64_t)p.H, c.n_d);
       publish(ds_ctr(p, l + 1, DS_XN_A));
       if (tw == 0) DS_TRACE(l, 6);
     }
@@ -985,7 +998,7 @@ extern "C" B2TTS_API int b2tts_decoder_stack_decode(
   return B2TTS_OK;
 }
 
-// Debug aid (tools/stack_trace.py): following launches record 16 globaltimer stamps per (CTA, layer) into
+// Debug aid (tools/stack_trace.py): following launches record 32 globaltimer stamps per (CTA, layer) into
 // buffer[(cta * 8 + layer) * 16 + slot] (uint64).  NULL switches tracing off.
 extern "C" B2TTS_API int b2tts_debug_stack_trace(void* buffer) {
   b2::g_ds_trace = static_cast<unsigned long long*>(buffer);

@@ -64,20 +64,21 @@ t_df = timed(lambda: stack.run_layers(x, pos))
 print(f"rows {B} ctx {CTX}: separate launches {t_sep:.1f} us / pass, dataflow {t_df:.1f} us / pass (graph replay, 5 layers)")
 
 G = nat.device_info()["sm_count"]
-trace = torch.zeros(G * 8 * 16, dtype=torch.int64, device="cuda")
+trace = torch.zeros(G * 8 * 32, dtype=torch.int64, device="cuda")
 lib.b2tts_debug_stack_trace(trace.data_ptr())
 stack.run_layers(x, pos)
 torch.cuda.synchronize()
 lib.b2tts_debug_stack_trace(None)
-t = trace.cpu().numpy().astype(np.int64).reshape(G, 8, 16)
+t = trace.cpu().numpy().astype(np.int64).reshape(G, 8, 32)
 so, sd = stack.dataflow_plan()
 nq, no, ng, nd = 32, 8 * so, 48, 8 * sd
 roles = {"qkv": range(0, nq), "o": range(nq, nq + no), "gu": range(nq + no, nq + no + ng),
          "down": range(nq + no + ng, nq + no + ng + nd), "none": range(nq + no + ng + nd, G)}
 t0 = t[:, 0, 13][t[:, 0, 13] > 0].min()
 print(f"kernel span {(t[:, 0, 14].max() - t0) / 1000:.1f} us; CTA start spread {(t[:, 0, 13].max() - t0) / 1000:.1f} us")
-names = ["top", "accfull", "pub1", "Tawait", "pubC", "Cawait", "normpub", "att_start", "att_done", "x_dep", "x_issued",
-         "mma_first", "mma_last"]
+names = ["top", "accfull", "pub1", "Tawait", "att_pro", "att_loop", "normpub", "att_start", "att_done", "x_dep", "x_issued",
+         "mma_first", "mma_last", "start", "end", "att_ret", "att_bar", "att_red", "", "", "w0", "w1", "w2", "w3"]
+ORDER = [0, 9, 11, 10, 12, 1, 2, 3, 6, 7, 4, 5, 15, 20, 21, 22, 23, 16, 17, 8]
 for l in range(L):
     print(f"--- layer {l} (us since kernel start; median [min..max] over the role's CTAs)")
     for rn, rr in roles.items():
@@ -85,7 +86,8 @@ for l in range(L):
         if not idx:
             continue
         parts = []
-        for sidx, nm in enumerate(names):
+        for sidx in ORDER:
+            nm = names[sidx]
             v = t[idx, l, sidx]
             v = v[v > 0]
             if v.size:
