@@ -451,6 +451,261 @@ fused_decode_attn_kernel(const FusedAttnParams p) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Short contexts (the code predictor: 3..17 tokens, 75 launches per codec frame).  The kernel above is built to stream
+// long contexts (bulk-copy ring, producer warp, split-KV tickets); for a handful of tokens all of that is latency.
+// Here one WARP owns one (sequence, kv head) item: no shared-memory ring, no block barrier, no split - the cached
+// rows are read straight from the paged cache, two 8-token tiles per round trip, and the new token never leaves
+// the warp.  Arithmetic, lane mapping and summation order are those of fused_decode_attn_kernel with nsplit == 1
+// (GROUP 2, 1-D RoPE), so outputs and K / V cache bytes are bit-identical.
+constexpr int FS_WARPS = 4;
+constexpr int FS_MAX_CTX = 64;
+
+template <bool EAGER>
+__global__ void __launch_bounds__(FS_WARPS * 32)
+fused_decode_attn_small_kernel(const FusedAttnParams p, int rows) {
+  constexpr int GROUP = 2;
+  __shared__ __align__(16) __nv_bfloat16 scr_all[FS_WARPS][(GROUP + 2) * FA_HD];   // q [2][128], k [128], v [128] of the new token
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kvh = p.num_kv_heads, kv_dim = kvh * FA_HD;
+  const int item = blockIdx.x * FS_WARPS + warp;
+  pdl_launch();
+  if (item >= rows * kvh) return;
+  const int row = item / kvh, hk = item - row * kvh;
+  const int head0 = hk * GROUP;
+  const int g = lane >> 3, j = lane & 7;
+  __nv_bfloat16* q_s = scr_all[warp];
+  __nv_bfloat16* kn_s = q_s + GROUP * FA_HD;
+  __nv_bfloat16* vn_s = kn_s + FA_HD;
+  // independent of the previous kernel: rotary frequencies, head-norm weights
+  float frq[2];
+  frq[0] = __ldg(p.inv_freq + 2 * lane);
+  frq[1] = __ldg(p.inv_freq + 2 * lane + 1);
+  uint32_t qw1 = 0, qw2 = 0, kw1 = 0, kw2 = 0;
+  if (p.q_w) { qw1 = *reinterpret_cast<const uint32_t*>(p.q_w + 2 * lane); qw2 = *reinterpret_cast<const uint32_t*>(p.q_w + 64 + 2 * lane); }
+  if (p.k_w) { kw1 = *reinterpret_cast<const uint32_t*>(p.k_w + 2 * lane); kw2 = *reinterpret_cast<const uint32_t*>(p.k_w + 64 + 2 * lane); }
+  pdl_wait();
+  // ---- one batch of independent requests
+  int L = __ldg(p.context_lens + row);
+  const int slot = __ldg(p.slot_mapping + row);
+  const int64_t pos = __ldg(p.positions + row);
+  const int32_t* bt = p.block_table + (int64_t)row * p.bt_stride;
+  int page0 = __ldg(bt);
+  uint32_t raw1[GROUP + 1], raw2[GROUP + 1];
+#pragma unroll
+  for (int i = 0; i < GROUP + 1; ++i) {
+    const __nv_bfloat16* src = i == GROUP ? p.k + (int64_t)row * p.k_stride + hk * FA_HD
+                                          : p.q + (int64_t)row * p.q_stride + (head0 + i) * FA_HD;
+    raw1[i] = *reinterpret_cast<const uint32_t*>(src + 2 * lane);
+    raw2[i] = *reinterpret_cast<const uint32_t*>(src + 64 + 2 * lane);
+  }
+  uint4 vraw = make_uint4(0, 0, 0, 0);
+  if (lane < 16) vraw = ldg_v4(p.v + (int64_t)row * p.v_stride + hk * FA_HD + 8 * lane);
+  if (L <= 0) {                   // CUDA-graph padding row: zeros
+    if (g == 0) {
+#pragma unroll
+      for (int h = 0; h < GROUP; ++h) {
+        __nv_bfloat16* o = p.out + ((int64_t)row * p.num_heads + head0 + h) * FA_HD;
+        stg_v4(o + 8 * j, make_uint4(0, 0, 0, 0));
+        stg_v4(o + 64 + 8 * j, make_uint4(0, 0, 0, 0));
+      }
+    }
+    return;
+  }
+  if (page0 < 0) page0 = 0;
+  // a token's K / V row of this head in the paged cache
+  auto tok_off = [&](int t) -> int64_t {
+    int page = page0;
+    if (t >= p.page_size) { page = __ldg(bt + t / p.page_size); if (page < 0) page = 0; }
+    return ((int64_t)page * p.page_size + t % p.page_size) * kv_dim + hk * FA_HD;
+  };
+  // the cached rows of the first two tiles are requested NOW, under the prologue arithmetic
+  const int n_tiles = (L + FA_TILE - 1) / FA_TILE;
+  uint4 kbuf[2][2][2], vbuf[2][2][2];            // [tile of the pair][token slot][half]
+  auto load_pair = [&](int i0) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        const int tok0 = (i0 + u) * FA_TILE;
+        const int ntok = min(FA_TILE, L - tok0);
+        const int tok = s * 4 + g;
+        const int t = tok0 + (tok < ntok ? tok : 0);
+        if (i0 + u < n_tiles && t != L - 1) {
+          const int64_t off = tok_off(t);
+          kbuf[u][s][0] = ldg_v4(p.k_cache + off + 8 * j);
+          kbuf[u][s][1] = ldg_v4(p.k_cache + off + 64 + 8 * j);
+          vbuf[u][s][0] = ldg_v4(p.v_cache + off + 8 * j);
+          vbuf[u][s][1] = ldg_v4(p.v_cache + off + 64 + 8 * j);
+        }
+      }
+  };
+  load_pair(0);
+  // ---- prologue: q/k head norm + RoPE of the new token (the body of qknorm_rope_kvwrite_kernel), K / V to the cache
+  {
+    float c1[2], s1[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const float a1 = (float)pos * frq[e];
+      c1[e] = rbf(cosf(a1) * p.attention_scaling);
+      s1[e] = rbf(sinf(a1) * p.attention_scaling);
+    }
+#pragma unroll
+    for (int i = 0; i < GROUP + 1; ++i) {
+      const bool is_k = i == GROUP;
+      const bool has_w = is_k ? (p.k_w != nullptr) : (p.q_w != nullptr);
+      float x1[2] = {bf16lo(raw1[i]), bf16hi(raw1[i])};
+      float x2[2] = {bf16lo(raw2[i]), bf16hi(raw2[i])};
+      if (has_w) {
+        float ss = x1[0] * x1[0];
+        ss = fmaf(x1[1], x1[1], ss); ss = fmaf(x2[0], x2[0], ss); ss = fmaf(x2[1], x2[1], ss);
+        const float var = warp_sum(ss) / (float)FA_HD + p.eps;
+        const float rstd = EAGER ? 1.0f / sqrtf(var) : rsqrtf(var);
+        const uint32_t w1 = is_k ? kw1 : qw1, w2 = is_k ? kw2 : qw2;
+        const float wf[4] = {bf16lo(w1), bf16hi(w1), bf16lo(w2), bf16hi(w2)};
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          x1[e] = rbf(EAGER ? rbf(x1[e] * rstd) * wf[e] : (x1[e] * rstd) * wf[e]);
+          x2[e] = rbf(EAGER ? rbf(x2[e] * rstd) * wf[2 + e] : (x2[e] * rstd) * wf[2 + e]);
+        }
+      }
+      float o1[2], o2[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        o1[e] = rbf(x1[e] * c1[e]) + rbf(-x2[e] * s1[e]);
+        o2[e] = rbf(x2[e] * c1[e]) + rbf(x1[e] * s1[e]);
+      }
+      const uint32_t y1 = pack_bf16(o1[0], o1[1]), y2 = pack_bf16(o2[0], o2[1]);
+      __nv_bfloat16* dst = is_k ? kn_s : q_s + i * FA_HD;
+      *reinterpret_cast<uint32_t*>(dst + 2 * lane) = y1;
+      *reinterpret_cast<uint32_t*>(dst + 64 + 2 * lane) = y2;
+      if (is_k && slot >= 0) {
+        __nv_bfloat16* cd = p.k_cache + (int64_t)slot * kv_dim + hk * FA_HD;
+        *reinterpret_cast<uint32_t*>(cd + 2 * lane) = y1;
+        *reinterpret_cast<uint32_t*>(cd + 64 + 2 * lane) = y2;
+      }
+    }
+    if (lane < 16) {
+      *reinterpret_cast<uint4*>(vn_s + 8 * lane) = vraw;
+      if (slot >= 0) stg_v4(p.v_cache + (int64_t)slot * kv_dim + hk * FA_HD + 8 * lane, vraw);
+    }
+  }
+  __syncwarp();
+  float qv[GROUP][16];
+#pragma unroll
+  for (int h = 0; h < GROUP; ++h) {
+    const __nv_bfloat16* qp = q_s + h * FA_HD;
+    fa_unpack8(*reinterpret_cast<const uint4*>(qp + 8 * j), qv[h]);
+    fa_unpack8(*reinterpret_cast<const uint4*>(qp + 64 + 8 * j), qv[h] + 8);
+#pragma unroll
+    for (int d = 0; d < 16; ++d) qv[h][d] *= p.scale_log2;
+  }
+  float m[GROUP], l[GROUP], acc[GROUP][16];
+#pragma unroll
+  for (int h = 0; h < GROUP; ++h) {
+    m[h] = -INFINITY; l[h] = 0.f;
+#pragma unroll
+    for (int d = 0; d < 16; ++d) acc[h][d] = 0.f;
+  }
+  for (int i0 = 0; i0 < n_tiles; i0 += 2) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (i0 + u >= n_tiles) break;
+      const int tok0 = (i0 + u) * FA_TILE;
+      const int ntok = min(FA_TILE, L - tok0);
+      float s[FA_TILE / 4][GROUP];
+      bool isnew[FA_TILE / 4];
+#pragma unroll
+      for (int it = 0; it < FA_TILE / 4; ++it) {
+        const int tok = it * 4 + g;
+        const bool valid = tok < ntok;
+        isnew[it] = tok0 + (valid ? tok : 0) == L - 1;
+        float kf[16];
+        if (isnew[it]) {
+          fa_unpack8(*reinterpret_cast<const uint4*>(kn_s + 8 * j), kf);
+          fa_unpack8(*reinterpret_cast<const uint4*>(kn_s + 64 + 8 * j), kf + 8);
+        } else {
+          fa_unpack8(kbuf[u][it][0], kf);
+          fa_unpack8(kbuf[u][it][1], kf + 8);
+        }
+#pragma unroll
+        for (int h = 0; h < GROUP; ++h) {
+          float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+          for (int d = 0; d < 16; d += 2) {
+            d0 = fmaf(qv[h][d], kf[d], d0);
+            d1 = fmaf(qv[h][d + 1], kf[d + 1], d1);
+          }
+          float dot = d0 + d1;
+          dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+          dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+          dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+          s[it][h] = valid ? dot : -INFINITY;
+        }
+      }
+      float alpha[GROUP];
+#pragma unroll
+      for (int h = 0; h < GROUP; ++h) {
+        float mt = s[0][h];
+#pragma unroll
+        for (int it = 1; it < FA_TILE / 4; ++it) mt = fmaxf(mt, s[it][h]);
+        mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, 8));
+        mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, 16));
+        const float mn = fmaxf(m[h], mt);
+        alpha[h] = fa_exp2(m[h] - mn);
+        m[h] = mn;
+        float ps = 0.f;
+#pragma unroll
+        for (int it = 0; it < FA_TILE / 4; ++it) {
+          s[it][h] = fa_exp2(s[it][h] - mn);
+          ps += s[it][h];
+        }
+        l[h] = fmaf(l[h], alpha[h], ps);
+#pragma unroll
+        for (int d = 0; d < 16; ++d) acc[h][d] *= alpha[h];
+      }
+#pragma unroll
+      for (int it = 0; it < FA_TILE / 4; ++it) {
+        float vf[16];
+        if (isnew[it]) {
+          fa_unpack8(*reinterpret_cast<const uint4*>(vn_s + 8 * j), vf);
+          fa_unpack8(*reinterpret_cast<const uint4*>(vn_s + 64 + 8 * j), vf + 8);
+        } else {
+          fa_unpack8(vbuf[u][it][0], vf);
+          fa_unpack8(vbuf[u][it][1], vf + 8);
+        }
+#pragma unroll
+        for (int h = 0; h < GROUP; ++h)
+#pragma unroll
+          for (int d = 0; d < 16; ++d) acc[h][d] = fmaf(s[it][h], vf[d], acc[h][d]);
+      }
+    }
+    if (i0 + 2 < n_tiles) load_pair(i0 + 2);
+  }
+#pragma unroll
+  for (int h = 0; h < GROUP; ++h) {
+    l[h] += __shfl_xor_sync(0xffffffffu, l[h], 8);
+    l[h] += __shfl_xor_sync(0xffffffffu, l[h], 16);
+#pragma unroll
+    for (int d = 0; d < 16; ++d) {
+      acc[h][d] += __shfl_xor_sync(0xffffffffu, acc[h][d], 8);
+      acc[h][d] += __shfl_xor_sync(0xffffffffu, acc[h][d], 16);
+    }
+  }
+  if (g == 0) {
+#pragma unroll
+    for (int h = 0; h < GROUP; ++h) {
+      const float inv = 1.f / l[h];
+      float o[16];
+#pragma unroll
+      for (int d = 0; d < 16; ++d) o[d] = acc[h][d] * inv;
+      __nv_bfloat16* op = p.out + ((int64_t)row * p.num_heads + head0 + h) * FA_HD;
+      stg_v4(op + 8 * j, fa_pack8(o));
+      stg_v4(op + 64 + 8 * j, fa_pack8(o + 8));
+    }
+  }
+}
+
 static size_t fa_smem_bytes(int kv_heads, int num_heads) {
   return (size_t)2 * FA_NSTAGE * FA_TILE * kv_heads * FA_HD * 2 + 2 * FA_NSTAGE * sizeof(uint64_t) + 16 +
          (size_t)(num_heads + 2 * kv_heads) * FA_HD * 2;
@@ -542,6 +797,25 @@ extern "C" int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, cons
 
   const int group = num_heads / num_kv_heads;
   const bool eager = rounding == B2TTS_ROUND_EAGER;
+  static const bool small_ok = [] { const char* e = getenv("B2TTS_FA_SMALL"); return !(e && e[0] == '0'); }();
+  if (small_ok && max_ctx <= FS_MAX_CTX && group == 2 && !modality && p.nsplit == 1) {
+    // a handful of cached tokens: one warp per (sequence, kv head), no ring, no split
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((batch * num_kv_heads + FS_WARPS - 1) / FS_WARPS, 1, 1);
+    cfg.blockDim = dim3(FS_WARPS * 32, 1, 1);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t e = eager ? cudaLaunchKernelEx(&cfg, fused_decode_attn_small_kernel<true>, p, batch)
+                          : cudaLaunchKernelEx(&cfg, fused_decode_attn_small_kernel<false>, p, batch);
+    count_launch();
+    if (e != cudaSuccess) return cuda_fail(e, what);
+    return B2TTS_OK;
+  }
   void (*kern)(const FusedAttnParams) = nullptr;
   if (group == 1) kern = eager ? fused_decode_attn_kernel<1, true> : fused_decode_attn_kernel<1, false>;
   else if (group == 2) kern = eager ? fused_decode_attn_kernel<2, true> : fused_decode_attn_kernel<2, false>;

@@ -86,3 +86,45 @@ def test_one_workspace_serves_every_batch_size(native):
     ws = native.fused_decode_attn_workspace(16, H, HD, 4096, "cuda")
     for i, b in enumerate((16, 8, 2, 1, 8, 16, 3)):
         _case(native, b, 700, i % 2 == 0, 0, seed=50 + i, ws=ws, max_ctx_override=4096)
+
+
+@pytest.mark.parametrize("b,max_len,rounding,pad", [(1, 3, 0, 0), (8, 17, 0, 2), (64, 17, 0, 0), (64, 16, 1, 1), (100, 64, 0, 0),
+                                                    (33, 40, 1, 0)])
+def test_short_context_kernel_is_bit_identical(native, b, max_len, rounding, pad):
+    """Block tables of <= 64 tokens (the code predictor) take the one-warp-per-(sequence, kv head) kernel; same
+    arithmetic and summation order as the streaming kernel without split-KV, so every byte must agree."""
+    import os
+    g = torch.Generator(device="cuda").manual_seed(b * 31 + max_len)
+    dev = "cuda"
+    lens = torch.randint(1, max_len + 1, (b,), generator=g, device=dev, dtype=torch.int32)
+    lens[0] = max_len
+    npages = b + 2
+    bt = torch.randperm(npages, generator=g, device=dev)[:b].to(torch.int32).view(b, 1).contiguous()
+    slots = (bt.view(-1) * PAGE + lens - 1).to(torch.int32)
+    if pad:
+        lens[-pad:] = 0
+        slots[-pad:] = -1
+    kc = torch.randn(npages, PAGE, KVH, HD, device=dev, generator=g).to(BF16)
+    vc = torch.randn(npages, PAGE, KVH, HD, device=dev, generator=g).to(BF16)
+    qkv = torch.randn(b, (H + 2 * KVH) * HD, device=dev, generator=g).to(BF16)
+    q = qkv[:, :H * HD].view(b, H, HD)
+    k = qkv[:, H * HD:(H + KVH) * HD].view(b, KVH, HD)
+    v = qkv[:, (H + KVH) * HD:].view(b, KVH, HD)
+    qw = (1 + 0.1 * torch.randn(HD, device=dev, generator=g)).to(BF16)
+    kw = (1 + 0.1 * torch.randn(HD, device=dev, generator=g)).to(BF16)
+    inv_freq = (1.0 / (1e6 ** (torch.arange(0, HD, 2, device=dev).float() / HD))).contiguous()
+    pos = (lens.long() - 1).clamp_min(0).contiguous()
+    eps, scale = 1e-6, HD ** -0.5
+    ws = native.fused_decode_attn_workspace(b, H, HD, PAGE, dev)
+    kc1, vc1, kc2, vc2 = kc.clone(), vc.clone(), kc.clone(), vc.clone()
+    os.environ["B2TTS_FA_NSPLIT"] = "1"
+    try:
+        want = native.fused_decode_attn(q, k, v, qw, kw, eps, pos, inv_freq, slots, kc1, vc1, bt, lens, scale, PAGE, ws,
+                                        rounding=rounding)
+    finally:
+        del os.environ["B2TTS_FA_NSPLIT"]
+    got = native.fused_decode_attn(q, k, v, qw, kw, eps, pos, inv_freq, slots, kc2, vc2, bt, lens, scale, max_len, ws,
+                                   rounding=rounding)
+    torch.cuda.synchronize()
+    assert torch.equal(kc1, kc2) and torch.equal(vc1, vc2), "KV cache bytes differ"
+    assert torch.equal(got, want), f"max abs {(got.float() - want.float()).abs().max().item()}"
