@@ -74,7 +74,9 @@ def _reference(nat, stack, cfg, x, pos, slots, bt, lens, caches, plan, max_ctx):
 
 
 def _run_case(nat, b, max_len, layers, rounding, seed, pad_rows=0, repeat=1):
+    from nano_qwen3tts_vllm_b200.models import qwen3_tts_share as share
     from nano_qwen3tts_vllm_b200.utils.context import reset_context, set_context
+    share.DATAFLOW_STACK = True                     # opt-in path (off by default)
     cfg, stack = _stack(layers, rounding)
     plan = stack.dataflow_plan()
     assert plan is not None, "predictor-sized stack must fit the dataflow kernel on this GPU"
@@ -124,7 +126,9 @@ def test_dataflow_stack_fused_rounding_padding_rows_and_replay(native):
 
 def test_dataflow_stack_in_cuda_graph(native):
     """Captured once, replayed many times: identical output every time."""
+    from nano_qwen3tts_vllm_b200.models import qwen3_tts_share as share
     from nano_qwen3tts_vllm_b200.utils.context import reset_context, set_context
+    share.DATAFLOW_STACK = True
     cfg, stack = _stack(5, 0)
     lens, bt, slots, pos, npages, width = _layout(64, 17, 11)
     g = torch.Generator(device="cuda").manual_seed(12)
@@ -145,3 +149,11 @@ def test_dataflow_stack_in_cuda_graph(native):
             assert torch.equal(out, eager)
     finally:
         reset_context()
+
+
+@pytest.fixture(autouse=True)
+def _restore_default_path():
+    from nano_qwen3tts_vllm_b200.models import qwen3_tts_share as share
+    before = share.DATAFLOW_STACK
+    yield
+    share.DATAFLOW_STACK = before
