@@ -392,6 +392,88 @@ def pin_memory_policy():
     return rows
 
 
+def prompt_config():
+    """Token ids of the prompt assembly (config.py of the reference: Qwen3TTSConfig / talker_config), toy values."""
+    tc = types.SimpleNamespace(
+        num_code_groups=16, codec_nothink_id=5, codec_think_id=6, codec_think_bos_id=7, codec_think_eos_id=8,
+        codec_pad_id=9, codec_bos_id=10, codec_language_id={"english": 20, "chinese": 21, "sichuan": 22},
+        spk_id={"anna": 30, "li": 31}, spk_is_dialect={"li": "sichuan"})
+    return types.SimpleNamespace(talker_config=tc, tts_bos_token_id=3, tts_eos_token_id=4, tts_pad_token_id=2)
+
+
+def prompt_cases(g):
+    """Seeded requests covering every branch of utils/generation.py:18-379, 412-515."""
+    ids = lambda n: torch.randint(11, 290, (1, n), generator=g)
+    code = lambda t: torch.randint(0, 90, (t, 16), generator=g)
+    vec = lambda: randn(g, 48, std=0.1)
+    clone = lambda codes, xv, icl: {"ref_code": codes, "ref_spk_embedding": [vec() for _ in codes],
+                                    "x_vector_only_mode": xv, "icl_mode": icl}
+    return {
+        "plain_stream": dict(input_ids=[ids(14)]),
+        "plain_nonstream": dict(input_ids=[ids(14)], non_streaming_mode=True),
+        "instruct_speaker_language": dict(input_ids=[ids(12)], instruct_ids=[ids(6)[0]], speakers=["Anna"], languages=["English"]),
+        "dialect": dict(input_ids=[ids(11)], speakers=["li"], languages=["auto"]),
+        "batch_mixed": dict(input_ids=[ids(10), ids(17), ids(13)], instruct_ids=[None, ids(4), None],
+                            speakers=[None, "anna", ""], languages=["auto", "chinese", "english"]),
+        "batch_nonstream": dict(input_ids=[ids(16), ids(11)], speakers=["li", None], languages=["chinese", "auto"],
+                                non_streaming_mode=True),
+        "xvector": dict(input_ids=[ids(12)], voice_clone_prompt=clone([None], [True], [False]), languages=["english"]),
+        "icl_text_longer": dict(input_ids=[ids(40)], ref_ids=[ids(12)], voice_clone_prompt=clone([code(9)], [False], [True])),
+        "icl_codec_longer": dict(input_ids=[ids(12)], ref_ids=[ids(9)], voice_clone_prompt=clone([code(30)], [False], [True]),
+                                 languages=["english"]),
+        "icl_nonstream": dict(input_ids=[ids(15)], ref_ids=[ids(10)], voice_clone_prompt=clone([code(12)], [False], [True]),
+                              non_streaming_mode=True),
+    }
+
+
+def pin_prompt():
+    """oracle.prompt == the live utils/generation.py (bit-exact, CPU bf16), every mode."""
+    from oracle import prompt as op
+    from nano_qwen3tts_vllm.utils import generation as ref
+    from nano_qwen3tts_vllm.models.qwen3_tts_talker import Qwen3TTSTalkerResizeMLP
+    g = torch.Generator().manual_seed(20261105)
+    cfg = prompt_config()
+    text_emb = torch.nn.Embedding(300, 64).to(BF16)
+    codec_emb = torch.nn.Embedding(200, 48).to(BF16)
+    proj = Qwen3TTSTalkerResizeMLP(64, 64, 48, "silu", bias=True).to(BF16)
+    books = [torch.nn.Embedding(100, 48).to(BF16) for _ in range(15)]
+    with torch.no_grad():
+        for m in [text_emb, codec_emb, *books]:
+            m.weight.copy_(randn(g, *m.weight.shape, std=0.05))
+        for lin in (proj.linear_fc1, proj.linear_fc2):
+            lin.weight.copy_(randn(g, *lin.weight.shape, std=0.12))
+            lin.bias.copy_(randn(g, *lin.bias.shape, std=0.02))
+    out = {"weights": {"text_embedding": text_emb.weight.data.clone(), "codec_embedding": codec_emb.weight.data.clone(),
+                       "fc1_w": proj.linear_fc1.weight.data.clone(), "fc1_b": proj.linear_fc1.bias.data.clone(),
+                       "fc2_w": proj.linear_fc2.weight.data.clone(), "fc2_b": proj.linear_fc2.bias.data.clone(),
+                       "books": torch.stack([b.weight.data for b in books])},
+           "cases": {}}
+
+    def icl_fn(text_id, ref_id, ref_code, tts_pad_embed, tts_eos_embed, non_streaming_mode):
+        return ref.generate_icl_prompt(text_id=text_id, ref_id=ref_id, ref_code=ref_code, tts_pad_embed=tts_pad_embed,
+                                       tts_eos_embed=tts_eos_embed, non_streaming_mode=non_streaming_mode, config=cfg,
+                                       text_embedding=text_emb, input_embedding=codec_emb, text_projection=proj,
+                                       code_predictor_embeddings=books, device="cpu")
+
+    with torch.no_grad():
+        for name, kw in prompt_cases(g).items():
+            want = ref.prepare_inputs(cfg, kw["input_ids"], instruct_ids=kw.get("instruct_ids"), ref_ids=kw.get("ref_ids"),
+                                      voice_clone_prompt=kw.get("voice_clone_prompt"), languages=kw.get("languages"),
+                                      speakers=kw.get("speakers"), non_streaming_mode=kw.get("non_streaming_mode", False),
+                                      text_embedding=text_emb, input_embedding=codec_emb, text_projection=proj, device="cpu",
+                                      generate_speaker_prompt_fn=lambda v: ref.generate_speaker_prompt(v, "cpu"),
+                                      generate_icl_prompt_fn=icl_fn)
+            got = op.prepare_inputs(cfg, kw["input_ids"], instruct_ids=kw.get("instruct_ids"), ref_ids=kw.get("ref_ids"),
+                                    voice_clone_prompt=kw.get("voice_clone_prompt"), languages=kw.get("languages"),
+                                    speakers=kw.get("speakers"), non_streaming_mode=kw.get("non_streaming_mode", False),
+                                    text_embedding=text_emb, input_embedding=codec_emb, text_projection=proj,
+                                    predictor_embeddings=books)
+            for a, b, what in zip(got, want, ("prompts", "trailing", "tts_pad", "mask")):
+                eq(a, b, f"prompt {name}: {what}")
+            out["cases"][name] = {"inputs": kw, "prompts": want[0], "trailing": want[1], "tts_pad": want[2], "mask": want[3]}
+    return out
+
+
 def main():
     import_reference()
     os.makedirs(GOLDEN, exist_ok=True)
@@ -406,6 +488,9 @@ def main():
     model_vec = pin_models()
     torch.save(model_vec, os.path.join(GOLDEN, "models.pt"))
     print("models pinned:", ", ".join(k for k in model_vec))
+    prompt_vec = pin_prompt()
+    torch.save(prompt_vec, os.path.join(GOLDEN, "prompt.pt"))
+    print("prompt assembly pinned:", ", ".join(prompt_vec["cases"]))
     for f in sorted(os.listdir(GOLDEN)):
         print(f, os.path.getsize(os.path.join(GOLDEN, f)), "bytes")
 
