@@ -330,6 +330,18 @@ B2TTS_API int b2tts_fused_decode_attn(const void* q, int64_t q_row_stride, const
                             int batch, int num_heads, int num_kv_heads, int head_dim, int page_size,
                             float scale, int max_ctx, int rounding, int pdl, void* stream);
 
+/* ---- f3: prompt-prep embedding assembly -------------------------------------------------------------------
+ * replaces the per-request tensor ops of prepare_inputs / generate_icl_prompt   utils/generation.py:18-379, 412-515
+ * (torch.cat / expand / `+` of projected text rows, codec-tag rows, the speaker row and the ICL reference frames,
+ * then pad_sequence into the left-padded batch, :329-377).  The host plans every row of every request of a batch;
+ * one launch writes  out[r] = a[a_index[r]] (+) b[b_index[r]]  (bf16 rows of `cols`; the add is bf16(f32 + f32),
+ * torch's bf16 tensor add; an index < 0 = that side absent, both absent = a zero padding row).
+ * a = the projected text rows text_projection(text_embedding(ids)), b = codec-side rows; indices are NOT range-checked
+ * on the device (a_rows / b_rows are validated by the host wrapper). */
+B2TTS_API int b2tts_prompt_assemble(const void* a, int64_t a_row_stride, int a_rows, const void* b, int64_t b_row_stride,
+                                    int b_rows, const int32_t* a_index, const int32_t* b_index, void* out,
+                                    int64_t out_row_stride, int rows, int cols, void* stream);
+
 /* ---- a10 in one launch: the decode pass of a whole (small) decoder stack ----------------------------------------
  * replaces, for one decode step of up to 64 sequences, the layer loop of Qwen3TTSCodePredictorModel.forward /
  * Qwen3TTSTalkerModel.forward                          models/qwen3_tts_predictor.py:30-44, qwen3_tts_talker.py:53-62

@@ -72,6 +72,7 @@ def _load():
         "b2tts_gemm_chain_ssq_slots": (I, [I]),
         "b2tts_gemm_chain_workspace_bytes": (Z, [I, P, P, I]),
         "b2tts_gemm_chain": (I, [P, I, I, F, I, P, Z, I, P]),
+        "b2tts_prompt_assemble": (I, [P, L, I, P, L, I, P, P, P, L, I, I, P]),
         "b2tts_decoder_stack_plan": (I, [I, I, I, I, P, P]),
         "b2tts_decoder_stack_workspace_bytes": (Z, [I, I, I, I]),
         "b2tts_decoder_stack_decode": (I, [P, L, P, L, P, I, P, I, I, I, I, I, I, F, I, P, P, F, P, P, I, P, I, F, P, Z, P]),
@@ -616,3 +617,25 @@ def stack_layer_array(layers: list[dict]):
         for name, _ in StackLayer._fields_:
             setattr(a, name, d[name].data_ptr())
     return arr
+
+
+# ------------------------------------------------------------------------------------------ f3: prompt assembly
+def prompt_assemble(a_rows, b_rows, a_index, b_index, out):
+    """out[r] = a_rows[a_index[r]] (+) b_rows[b_index[r]] (bf16 add; index < 0 = side absent) - ``b2tts_prompt_assemble``.
+    a_rows [Na, H] / b_rows [Nb, H] bf16 (either may be empty), indices int32 [R], out [R, H] bf16 (row stride free)."""
+    _cuda(out, BF16, "out"); _cuda(a_index, I32, "a_index"); _cuda(b_index, I32, "b_index")
+    rows, cols = out.shape
+    if a_index.numel() != rows or b_index.numel() != rows:
+        raise ValueError("prompt_assemble: one index per output row")
+    for t, name in ((a_rows, "a_rows"), (b_rows, "b_rows")):
+        if t is not None and t.numel():
+            _cuda(t, BF16, name)
+            if t.shape[1] != cols or t.stride(1) != 1:
+                raise ValueError(f"prompt_assemble: {name} must be [n, {cols}] with contiguous rows")
+    na = 0 if a_rows is None else a_rows.shape[0]
+    nb = 0 if b_rows is None else b_rows.shape[0]
+    _check(_load().b2tts_prompt_assemble(
+        a_rows.data_ptr() if na else None, a_rows.stride(0) if na else cols, na,
+        b_rows.data_ptr() if nb else None, b_rows.stride(0) if nb else cols, nb,
+        a_index.data_ptr(), b_index.data_ptr(), out.data_ptr(), out.stride(0), rows, cols, _stream()), "prompt_assemble")
+    return out

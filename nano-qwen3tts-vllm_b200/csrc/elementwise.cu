@@ -235,3 +235,56 @@ extern "C" int b2tts_frame_advance(const int64_t* code0, int eos_id, int32_t* ac
   B2_CHECK_LAUNCH("frame_advance");
   return B2TTS_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// f3 - prompt assembly (utils/generation.py:18-379, 412-515 of the reference).  Every row of a talker prompt (and of
+// the trailing text hiddens) is  text side (+) codec side : a projected text-embedding row, a codec / speaker / ICL
+// reference-frame row, or their bf16 sum.  The host plans the rows of ALL requests of a batch as two index vectors
+// and this one launch gathers, adds and scatters them into the left-padded [B, Tmax, H] batch the reference builds
+// with ~10 tiny tensor ops per request: out[r] = a[a_idx[r]] + b[b_idx[r]], an index < 0 = absent side (both absent =
+// zero padding row).  The add is torch's bf16 tensor add: bf16(f32(a) + f32(b)).
+namespace b2 {
+__global__ void __launch_bounds__(256)
+prompt_assemble_kernel(const __nv_bfloat16* __restrict__ a, int64_t a_stride, const __nv_bfloat16* __restrict__ b,
+                       int64_t b_stride, const int32_t* __restrict__ a_idx, const int32_t* __restrict__ b_idx,
+                       __nv_bfloat16* __restrict__ out, int64_t out_stride, int cols) {
+  const int r = blockIdx.x;
+  const int ia = a_idx[r], ib = b_idx[r];
+  const __nv_bfloat16* pa = ia >= 0 ? a + (int64_t)ia * a_stride : nullptr;
+  const __nv_bfloat16* pb = ib >= 0 ? b + (int64_t)ib * b_stride : nullptr;
+  __nv_bfloat16* po = out + (int64_t)r * out_stride;
+  for (int v = threadIdx.x; v < (cols >> 3); v += blockDim.x) {
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (pa && pb) {
+      const uint4 x = ldg_nc_v4(pa + 8 * v), y = ldg_nc_v4(pb + 8 * v);
+      o.x = pack_bf16(bf16lo(x.x) + bf16lo(y.x), bf16hi(x.x) + bf16hi(y.x));
+      o.y = pack_bf16(bf16lo(x.y) + bf16lo(y.y), bf16hi(x.y) + bf16hi(y.y));
+      o.z = pack_bf16(bf16lo(x.z) + bf16lo(y.z), bf16hi(x.z) + bf16hi(y.z));
+      o.w = pack_bf16(bf16lo(x.w) + bf16lo(y.w), bf16hi(x.w) + bf16hi(y.w));
+    } else if (pa) {
+      o = ldg_nc_v4(pa + 8 * v);
+    } else if (pb) {
+      o = ldg_nc_v4(pb + 8 * v);
+    }
+    stg_na_v4(po + 8 * v, o);
+  }
+}
+}  // namespace b2
+
+extern "C" int b2tts_prompt_assemble(const void* a, int64_t a_row_stride, int a_rows, const void* b, int64_t b_row_stride,
+                                     int b_rows, const int32_t* a_index, const int32_t* b_index, void* out,
+                                     int64_t out_row_stride, int rows, int cols, void* stream) {
+  using namespace b2;
+  const char* what = "prompt_assemble";
+  B2_REQUIRE(rows >= 0 && cols > 0 && cols % 8 == 0 && a_rows >= 0 && b_rows >= 0, B2TTS_EINVAL,
+             "%s: rows=%d cols=%d (multiple of 8)", what, rows, cols);
+  if (rows == 0) return B2TTS_OK;
+  B2_REQUIRE(a_index && b_index && out && (a || a_rows == 0) && (b || b_rows == 0), B2TTS_EINVAL, "%s: null pointer", what);
+  B2_REQUIRE(aligned16(out) && (!a || aligned16(a)) && (!b || aligned16(b)) && a_row_stride % 8 == 0 && b_row_stride % 8 == 0 &&
+                 out_row_stride % 8 == 0, B2TTS_EALIGN, "%s: pointers / strides must be 16-byte aligned", what);
+  prompt_assemble_kernel<<<rows, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(a), a_row_stride, static_cast<const __nv_bfloat16*>(b), b_row_stride, a_index,
+      b_index, static_cast<__nv_bfloat16*>(out), out_row_stride, cols);
+  B2_CHECK_LAUNCH(what);
+  return B2TTS_OK;
+}

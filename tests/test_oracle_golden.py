@@ -72,3 +72,33 @@ def test_attention_restatement_consistency():
     bt = torch.tensor([[2, 0, -1]], dtype=torch.int32)
     dec = O.paged_attn_decode(q[-1:], kc, vc, torch.tensor([t], dtype=torch.int32), bt, 128 ** -0.5)
     assert torch.equal(dec[0], full[-1])
+
+
+def test_prompt_oracle_reproduces_the_reference_golden():
+    """oracle/prompt.py against tests/golden/prompt.pt (outputs of the live utils/generation.py, written by
+    oracle/pin_against_reference.py): every mode, every byte."""
+    import os
+    import types
+    import torch
+    from oracle import prompt as op
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    gold = torch.load(os.path.join(root, "tests", "golden", "prompt.pt"))
+    w = gold["weights"]
+    tc = types.SimpleNamespace(
+        num_code_groups=16, codec_nothink_id=5, codec_think_id=6, codec_think_bos_id=7, codec_think_eos_id=8,
+        codec_pad_id=9, codec_bos_id=10, codec_language_id={"english": 20, "chinese": 21, "sichuan": 22},
+        spk_id={"anna": 30, "li": 31}, spk_is_dialect={"li": "sichuan"})
+    cfg = types.SimpleNamespace(talker_config=tc, tts_bos_token_id=3, tts_eos_token_id=4, tts_pad_token_id=2)
+    lin = torch.nn.functional.linear
+    proj = lambda x: lin(torch.nn.functional.silu(lin(x, w["fc1_w"], w["fc1_b"])), w["fc2_w"], w["fc2_b"])
+    books = [(lambda ids, i=i: w["books"][i][ids]) for i in range(15)]
+    for name, case in gold["cases"].items():
+        kw = case["inputs"]
+        got = op.prepare_inputs(cfg, kw["input_ids"], instruct_ids=kw.get("instruct_ids"), ref_ids=kw.get("ref_ids"),
+                                voice_clone_prompt=kw.get("voice_clone_prompt"), languages=kw.get("languages"),
+                                speakers=kw.get("speakers"), non_streaming_mode=kw.get("non_streaming_mode", False),
+                                text_embedding=lambda ids: w["text_embedding"][ids],
+                                input_embedding=lambda ids: w["codec_embedding"][ids], text_projection=proj,
+                                predictor_embeddings=books)
+        for g, key in zip(got, ("prompts", "trailing", "tts_pad", "mask")):
+            assert torch.equal(g, case[key]), f"{name}: {key}"
