@@ -14,6 +14,7 @@ synthetic streams with a 64-token prompt, top-k 50 sampling at T=1.0/0.9, EOS ig
   roofline  the dominant kernel (weight-streaming tcgen05 GEMM) + roofline_kernels for every other kernel of the path
   reference_kernels   cuBLAS / flash-attn / Triton on the same shapes, timed the same way (bench_kernels.py)
   other_workloads     1 / 8 / 128 / 256 / 512 streams;  icl_workload = BASELINE configs[3] (4k-token prompts)
+  prompt_prep         f3: prompt assembly for a 64-request burst and for one 4096-frame ICL request
   cpu_baseline   the CPU oracle (port of the reference's torch path) on the host cores, bounded sample
 
 N > 1: independent per-GPU replicas (no collective on the data path); barrier + max-over-ranks timing.
@@ -389,6 +390,58 @@ def reference_arm(a):
     print(json.dumps(line), flush=True)
 
 
+def time_prompt_prep(device):
+    """Prompt assembly for (a) 64 simultaneous arrivals of ~20-word prompts (BASELINE configs[4]'s admission burst) and
+    (b) one voice-clone ICL request with a 4096-frame reference (configs[3]); random-init embeddings at the 1.7B widths
+    (text 151936 x 2048 -> hidden 2048).  CUDA events around the public call, host planning included."""
+    import types
+    from nano_qwen3tts_vllm_b200.models.qwen3_tts_talker import Qwen3TTSTalkerResizeMLP
+    from nano_qwen3tts_vllm_b200.utils.generation import prepare_inputs
+    g = torch.Generator(device=device).manual_seed(77)
+    rnd = lambda *s: (torch.randn(*s, device=device, generator=g) * 0.02).to(torch.bfloat16)
+    tc = types.SimpleNamespace(num_code_groups=16, codec_nothink_id=2155, codec_think_id=2154, codec_think_bos_id=2156,
+                               codec_think_eos_id=2157, codec_pad_id=2148, codec_bos_id=2149,
+                               codec_language_id={"english": 2050}, spk_id={}, spk_is_dialect={})
+    cfg = types.SimpleNamespace(talker_config=tc, tts_bos_token_id=151672, tts_eos_token_id=151673, tts_pad_token_id=151671)
+    text = types.SimpleNamespace(weight=rnd(151936, 2048))
+    codec = types.SimpleNamespace(weight=rnd(3072, 2048))
+    books = rnd(15, 2048, 2048)
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        proj = Qwen3TTSTalkerResizeMLP(2048, 2048, 2048, bias=True).to(device)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    with torch.no_grad():
+        for p in proj.parameters():
+            p.copy_(rnd(*p.shape))
+    ids = lambda n: torch.randint(1000, 150000, (1, n), device=device, generator=g)
+    kw = dict(text_embedding=text, input_embedding=codec, text_projection=proj, device=device, code_predictor_embeddings=books)
+
+    def timed(fn, iters=10):
+        fn(); fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            out = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters, out
+
+    burst = [ids(40) for _ in range(64)]
+    ms_a, out_a = timed(lambda: prepare_inputs(cfg, burst, languages=["english"] * 64, **kw))
+    code = torch.randint(0, 2048, (4096, 16), device=device, generator=g)
+    clone = {"ref_code": [code], "ref_spk_embedding": [rnd(2048)], "x_vector_only_mode": [False], "icl_mode": [True]}
+    one, ref = [ids(80)], [ids(60)]
+    ms_b, out_b = timed(lambda: prepare_inputs(cfg, one, ref_ids=ref, voice_clone_prompt=clone, languages=["english"],
+                                               voice_clone_spk_embeds=clone["ref_spk_embedding"], **kw))
+    return {"what": "prepare_inputs (utils/generation.py:18-379, 412-515): one text_embedding gather + one text_projection "
+                    "over all tokens, one codec gather / 16-codebook gather-sum, ONE b2tts_prompt_assemble launch; host "
+                    "planning inside the timed region",
+            "burst_64_requests_ms": round(ms_a, 3), "burst_prompt_rows": int(out_a[0].shape[1]),
+            "icl_4096_frames_ms": round(ms_b, 3), "icl_prompt_rows": int(out_b[0].shape[1])}
+
+
 def workload_config(a, streams):
     return {"workload": f"Qwen3-TTS-12Hz-{a.model} talker+code-predictor, {streams} concurrent streams per GPU "
                         f"(BASELINE configs[4]; configs[1]/[2] = 1/8 streams under other_workloads), prompt {PROMPT_LEN} tokens, "
@@ -601,6 +654,12 @@ def main():
         except Exception as e:
             line["icl_workload"] = {"failed": f"{type(e).__name__}: {e}"[:300]}
             mc, talker, predictor = None, None, None
+    # ---- f3: prompt-prep embedding assembly (utils/generation.py of the reference) at the 1.7B widths
+    if rank == 0 and world == 1 and not a.no_icl:
+        try:
+            line["prompt_prep"] = time_prompt_prep(device)
+        except Exception as e:
+            line["prompt_prep"] = {"failed": f"{type(e).__name__}: {e}"[:300]}
     if rank == 0 and not a.no_cpu_baseline and world == 1:
         fps, cores, what, dt = cpu_oracle_frames(a.model, a.cpu_streams or a.streams, 2, 1, budget_s=25.0)
         line["cpu_baseline"] = {"value": round(fps, 3), "unit": "frames/s", "cores": cores, "kind": "port", "sample": what}
