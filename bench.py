@@ -395,6 +395,7 @@ def time_prompt_prep(device):
     (b) one voice-clone ICL request with a 4096-frame reference (configs[3]); random-init embeddings at the 1.7B widths
     (text 151936 x 2048 -> hidden 2048).  CUDA events around the public call, host planning included."""
     import types
+    import torch
     from nano_qwen3tts_vllm_b200.models.qwen3_tts_talker import Qwen3TTSTalkerResizeMLP
     from nano_qwen3tts_vllm_b200.utils.generation import prepare_inputs
     g = torch.Generator(device=device).manual_seed(77)
