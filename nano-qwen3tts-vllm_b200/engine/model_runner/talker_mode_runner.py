@@ -5,6 +5,7 @@ Quirk kept on purpose: the decode RoPE position is ``l
 index is ``len(seq) - 1`` (talker_mode_runner.py:126-128)."""
 from __future__ import annotations
 
+import numpy as np
 import torch
 
 from ...models.qwen3_tts_talker import Qwen3TTSTalkerForCausalLM
@@ -32,18 +33,75 @@ class TalkerModeModelRunner(ModelRunner):
                                          dtype=BF16, device=torch.device(self.config.device))
         super().post_init()
 
+    def exit(self):
+        self._pf_static = None                                               # prefill graphs + their static tensors
+        super().exit()
+
     def decode_position(self, seq: Sequence) -> int:
         return len(seq)                                                      # talker_mode_runner.py:126
 
     def decode_body(self, rows: int) -> torch.Tensor:
         return self.model(self.static_embeds[:rows], self.layout.d["positions"][:rows])
 
+    # ------------------------------------------------------------------ prefill graphs
+    PREFILL_GRAPH_MAX_TOKENS = 256                                            # talker_mode_runner.py:206
+
+    def _prefill_static(self):
+        """Static tensors of the single-sequence prefill graphs (talker_mode_runner.py:194-234): embeddings, one
+        int64 index buffer (positions | slots) uploaded as one copy, per-length cu_seqlens."""
+        st = getattr(self, "_pf_static", None)
+        if st is None:
+            t, dev = self.PREFILL_GRAPH_MAX_TOKENS, self.device
+            st = self._pf_static = dict(
+                embeds=torch.zeros(t, self.stack_config.hidden_size, dtype=BF16, device=dev),
+                index=torch.zeros(2 * t, dtype=torch.int64, device=dev),
+                slots=torch.zeros(t, dtype=torch.int32, device=dev),
+                host=torch.zeros(2 * t, dtype=torch.int64).pin_memory(),
+                graphs={})
+        return st
+
+    def _prefill_graph_ok(self, seqs: list[Sequence]) -> bool:
+        return (not self.enforce_eager and len(seqs) == 1 and seqs[0].num_cached_tokens == 0
+                and 1 <= len(seqs[0]) <= self.PREFILL_GRAPH_MAX_TOKENS and bool(self.graphs))
+
+    def _run_prefill_graph(self, seq: Sequence) -> torch.Tensor:
+        """Single-sequence prompt of T <= 256 tokens through a captured graph (layers + final norm, as the reference
+        captures them).  The reference captures all 256 lengths at start-up; here a length is captured the first time it
+        is seen (one warm run + capture) and replayed afterwards."""
+        from ...utils.context import set_context
+        st, t, bs = self._prefill_static(), len(seq), self.block_size
+        ar = np.arange(t, dtype=np.int64)
+        h = st["host"].numpy()
+        h[:t] = ar
+        h[self.PREFILL_GRAPH_MAX_TOKENS:self.PREFILL_GRAPH_MAX_TOKENS + t] = \
+            np.asarray(seq.block_table, dtype=np.int64)[ar // bs] * bs + ar % bs
+        st["index"].copy_(st["host"], non_blocking=True)
+        st["slots"].copy_(st["index"][self.PREFILL_GRAPH_MAX_TOKENS:])        # int64 -> int32 on the device
+        st["embeds"][:t].copy_(seq.input_embeds.reshape(-1, seq.input_embeds.shape[-1]), non_blocking=True)
+        ent = st["graphs"].get(t)
+        if ent is None:
+            cu = torch.tensor([0, t], dtype=torch.int32, device=self.device)
+            ent = st["graphs"][t] = dict(cu=cu, graph=None, out=None)
+        set_context(True, ent["cu"], ent["cu"], t, t, st["slots"][:t], None, None)
+        if ent["graph"] is None:
+            body = lambda: self.model(st["embeds"][:t], st["index"][:t])
+            body()                                                           # warm-up at this length (outside capture)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, self.graph_pool):
+                ent["out"] = body()
+            ent["graph"] = g
+        ent["graph"].replay()
+        return ent["out"]
+
     @torch.inference_mode()
     def run_model(self, seqs: list[Sequence], is_prefill: bool):
         n = len(seqs)
         if is_prefill:
-            embeds, positions = self.prepare_prefill(seqs)
-            hidden = self.model(embeds, positions)
+            if self._prefill_graph_ok(seqs):
+                hidden = self._run_prefill_graph(seqs[0])
+            else:
+                embeds, positions = self.prepare_prefill(seqs)
+                hidden = self.model(embeds, positions)
             logits = self.model.compute_logits(hidden)                       # last token per sequence
             from ...utils.context import get_context
             last = (get_context().cu_seqlens_q[1:] - 1).to(torch.int64)

@@ -211,3 +211,35 @@ def test_predictor_deferred_tokens_equal_per_step_readback(engines):
     for rid in want:
         assert len(want[rid]) == 15 and all(0 <= c < pd.vocab_size for c in got[rid]), rid
         assert got[rid] == want[rid], rid
+
+
+def test_talker_prefill_graph_equals_eager_prefill(engines):
+    """Single-sequence prompts of <= 256 tokens run through a CUDA graph per length (captured on first use,
+    reference talker_mode_runner.py:194-234 captures all 256 at start-up): same sampled token, same hidden state and
+    the same KV pages as the eager prefill, on capture AND on replay."""
+    from nano_qwen3tts_vllm_b200.engine.sequence import Sequence
+    from nano_qwen3tts_vllm_b200.sampling_params import SamplingParams
+    talker, _, (td, pd, tw, pw) = engines
+    r = talker.model_runner
+    r.top_k = 1
+    g = torch.Generator().manual_seed(21)
+    try:
+        for n in (5, 64, 5, 200, 64):
+            prompt = (torch.randn(1, n, td.hidden_size, generator=g) * 0.05).to(BF16)
+            out = {}
+            for mode in ("eager", "graph"):
+                r.enforce_eager = mode == "eager"
+                r.kv_cache.zero_()
+                seq = Sequence([], SamplingParams(temperature=1.0, max_tokens=4, ignore_eos=True), input_embeds=prompt)
+                seq.block_table = [3]
+                assert r._prefill_graph_ok([seq]) == (mode == "graph")
+                toks, hidden = r.run([seq], True)
+                torch.cuda.synchronize()
+                out[mode] = (toks, hidden.clone(), r.kv_cache.clone())
+            assert out["eager"][0] == out["graph"][0]
+            assert torch.equal(out["eager"][1], out["graph"][1]), f"hidden differs at T={n}"
+            assert torch.equal(out["eager"][2], out["graph"][2]), f"KV pages differ at T={n}"
+        assert sorted(r._pf_static["graphs"]) == [5, 64, 200]
+    finally:
+        r.enforce_eager = False
+        r.top_k = 50
