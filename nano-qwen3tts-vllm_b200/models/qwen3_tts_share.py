@@ -35,6 +35,8 @@ from ..utils.context import get_context
 
 FUSED_DECODE_ATTENTION = True     # False: separate qknorm_rope_kvwrite + paged_attn_decode launches
 GEMM_CHAIN = False                # decode: the 4 projections between two attention calls as ONE persistent launch
+# experiments: RMSNorms applied by a separate launch instead of inside the consuming GEMM ("gate_up", "qkv", "gate_up,qkv")
+UNFUSED_NORMS = os.environ.get("B2TTS_UNFUSED_NORMS", "")
 # decode of a small stack (the code predictor) as ONE persistent dataflow launch (csrc/decoder_stack.cu).  Opt-in:
 # bit-identical to the separate launches, but measured at 260 us per 5-layer pass against their 246 us at 64 rows
 # (every hand-over between phases costs a gpu-scope release + an L2 poll, ~2.5 us, 7 per layer)
@@ -146,7 +148,7 @@ class Qwen3TTSDecoderLayer(nn.Module):
         ``in_place`` False keeps the caller's tensor (the first layer's input embeddings) intact.
         ``nxt``: the weight the GEMM after this layer streams (the next layer's qkv_proj, or the LM head): every GEMM
         here pulls its successor's weights into L2 while it runs.  Returns (residual, ssq)."""
-        if ssq is None:
+        if ssq is None or "qkv" in UNFUSED_NORMS:
             h = nat.rmsnorm(residual, self.input_layernorm.weight, self.eps, self.rounding)
             o = self.self_attn.attend(positions, h)
         else:
@@ -154,9 +156,13 @@ class Qwen3TTSDecoderLayer(nn.Module):
                                       RowNorm(self.input_layernorm.weight, ssq, self.eps, self.rounding))
         residual, ssq = linear_residual(o, self.self_attn.o_proj.weight, residual, out=residual if in_place else None,
                                         want_ssq=True, nxt=(self.mlp.gate_up_proj.weight, nat.PACK_GATE_UP))
-        act = linear_silu_mul(residual, self.mlp.gate_up_proj.weight, self.rounding,
-                              norm=RowNorm(self.post_attention_layernorm.weight, ssq, self.eps, self.rounding),
-                              nxt=self.mlp.down_proj.weight)
+        if "gate_up" in UNFUSED_NORMS:
+            h = nat.rmsnorm(residual, self.post_attention_layernorm.weight, self.eps, self.rounding)
+            act = linear_silu_mul(h, self.mlp.gate_up_proj.weight, self.rounding, nxt=self.mlp.down_proj.weight)
+        else:
+            act = linear_silu_mul(residual, self.mlp.gate_up_proj.weight, self.rounding,
+                                  norm=RowNorm(self.post_attention_layernorm.weight, ssq, self.eps, self.rounding),
+                                  nxt=self.mlp.down_proj.weight)
         return linear_residual(act, self.mlp.down_proj.weight, residual, out=residual, want_ssq=True, nxt=nxt)
 
 
