@@ -342,6 +342,12 @@ B2TTS_API int b2tts_prompt_assemble(const void* a, int64_t a_row_stride, int a_r
                                     int b_rows, const int32_t* a_index, const int32_t* b_index, void* out,
                                     int64_t out_row_stride, int rows, int cols, void* stream);
 
+/* ---- f4 (tail): decoded waveform -> PCM16 ----------------------------------------------------------------------
+ * replaces _float_to_pcm16 / _apply_volume_pcm16                                    examples/server.py:338-349
+ *   out[i] = (int16) trunc(clip(wav[i], -1, 1) * 32767);  volume != 1: out[i] = clip(rint(out[i] * volume), -32768, 32767)
+ * (the vocoder itself - qwen_tts 0.0.5, not part of the reference tree - is out of reach). */
+B2TTS_API int b2tts_float_to_pcm16(const float* wav, int16_t* out, int64_t n, float volume, void* stream);
+
 /* ---- a10 in one launch: the decode pass of a whole (small) decoder stack ----------------------------------------
  * replaces, for one decode step of up to 64 sequences, the layer loop of Qwen3TTSCodePredictorModel.forward /
  * Qwen3TTSTalkerModel.forward                          models/qwen3_tts_predictor.py:30-44, qwen3_tts_talker.py:53-62

@@ -73,6 +73,7 @@ def _load():
         "b2tts_gemm_chain_workspace_bytes": (Z, [I, P, P, I]),
         "b2tts_gemm_chain": (I, [P, I, I, F, I, P, Z, I, P]),
         "b2tts_prompt_assemble": (I, [P, L, I, P, L, I, P, P, P, L, I, I, P]),
+        "b2tts_float_to_pcm16": (I, [P, P, L, F, P]),
         "b2tts_decoder_stack_plan": (I, [I, I, I, I, P, P]),
         "b2tts_decoder_stack_workspace_bytes": (Z, [I, I, I, I]),
         "b2tts_decoder_stack_decode": (I, [P, L, P, L, P, I, P, I, I, I, I, I, I, F, I, P, P, F, P, P, I, P, I, F, P, Z, P]),
@@ -638,4 +639,17 @@ def prompt_assemble(a_rows, b_rows, a_index, b_index, out):
         a_rows.data_ptr() if na else None, a_rows.stride(0) if na else cols, na,
         b_rows.data_ptr() if nb else None, b_rows.stride(0) if nb else cols, nb,
         a_index.data_ptr(), b_index.data_ptr(), out.data_ptr(), out.stride(0), rows, cols, _stream()), "prompt_assemble")
+    return out
+
+
+# ------------------------------------------------------------------------------------------ f4 (tail): PCM16
+def float_to_pcm16(wav: torch.Tensor, volume: float = 1.0, out: torch.Tensor | None = None) -> torch.Tensor:
+    """fp32 waveform (any shape, contiguous) -> int16 PCM on the device (``b2tts_float_to_pcm16``)."""
+    _cuda(wav, F32, "wav")
+    if not wav.is_contiguous():
+        wav = wav.contiguous()
+    if out is None:
+        out = torch.empty(wav.shape, dtype=torch.int16, device=wav.device)
+    _check(_load().b2tts_float_to_pcm16(wav.data_ptr(), out.data_ptr(), wav.numel(), float(volume), _stream()),
+           "float_to_pcm16")
     return out

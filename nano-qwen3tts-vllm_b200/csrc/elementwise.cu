@@ -288,3 +288,36 @@ extern "C" int b2tts_prompt_assemble(const void* a, int64_t a_row_stride, int a_
   B2_CHECK_LAUNCH(what);
   return B2TTS_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// f4 - the tail of the codec decode window (examples/server.py:338-349 of the reference): float waveform -> PCM16,
+//   pcm = (int16) trunc(clip(x, -1, 1) * 32767)                       _float_to_pcm16   (numpy astype: toward zero)
+//   pcm = (int16) clip(rint((float)pcm * volume), -32768, 32767)      _apply_volume_pcm16 (numpy round: half to even)
+// on the device, so that a decoded window leaves the GPU as 2 bytes per sample instead of 4.
+namespace b2 {
+__global__ void __launch_bounds__(256)
+pcm16_kernel(const float* __restrict__ wav, int16_t* __restrict__ out, int64_t n, float volume) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float x = wav[i];
+    x = fminf(fmaxf(x, -1.0f), 1.0f);                  // NaN -> -1 like np.clip? np.clip keeps NaN; the cast is then UB there
+    int v = (int)(x * 32767.0f);                       // truncation toward zero
+    if (volume != 1.0f) {
+      const float s = rintf((float)v * volume);        // round half to even
+      v = (int)fminf(fmaxf(s, -32768.0f), 32767.0f);
+    }
+    out[i] = (int16_t)v;
+  }
+}
+}  // namespace b2
+
+extern "C" int b2tts_float_to_pcm16(const float* wav, int16_t* out, int64_t n, float volume, void* stream) {
+  using namespace b2;
+  B2_REQUIRE(n >= 0, B2TTS_EINVAL, "float_to_pcm16: n=%lld", (long long)n);
+  if (n == 0) return B2TTS_OK;
+  B2_REQUIRE(wav && out, B2TTS_EINVAL, "float_to_pcm16: null pointer");
+  const int64_t want = (n + 255) / 256;
+  const int blocks = (int)(want < 148 * 8 ? want : 148 * 8);
+  pcm16_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(wav, out, n, volume);
+  B2_CHECK_LAUNCH("float_to_pcm16");
+  return B2TTS_OK;
+}
