@@ -200,12 +200,16 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
           for (int k = 0; k < G_BK / 16; ++k)
             umma_bf16(tmem_base, umma_desc_sw128(a_addr + k * 32), umma_desc_sw128(b_addr + k * 32), idesc,
                       (uint32_t)((i | k) != 0));
-          umma_commit(empty_bar + stage);       // stage reusable once these MMAs have read it
+          // stage reusable once these MMAs have read it - but only a k-block NS later ever waits for that: the
+          // commits of the last NS k-blocks (ALL of them for the split-K decode shapes, whose K range fits the ring)
+          // would be ~0.2 us of issue time each for a barrier nobody reads
+          if (i + NS < nkb) umma_commit(empty_bar + stage);
+          else if (i == nkb - 1) umma_commit(accum_bar);      // accumulator complete
         }
         __syncwarp();
         if (++stage == NS) { stage = 0; ph ^= 1; }
       }
-      if (elect_one()) umma_commit(accum_bar);  // accumulator complete
+      if (nkb == 0 && elect_one()) umma_commit(accum_bar);
     }
     __syncwarp();
   } else {
