@@ -116,7 +116,9 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) {
-      mbar_init(full_bar + s, 1 + 4);           // W producer (expect_tx arrive) + 4 x-producer warps
+      // fused norm: W producer (expect_tx arrive) + the 4 x warps that transform the landed tile; otherwise the x copy
+      // completes straight on this barrier (two expect_tx arrivals: W's and x's) - no relay through the x warps
+      mbar_init(full_bar + s, p.norm_w ? 1 + 4 : 2);
       mbar_init(empty_bar + s, 1);              // tcgen05.commit
       mbar_init(raw_bar + s, 1);
     }
@@ -154,8 +156,9 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       pdl_wait();
       if (elect_one()) {
         for (int i = 0; i < first; ++i) {
-          mbar_expect_tx(raw_bar + i, xbytes);
-          tma_load_2d(smem + i * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, row0, raw_bar + i);
+          uint64_t* landed = p.norm_w ? raw_bar + i : full_bar + i;
+          mbar_expect_tx(landed, xbytes);
+          tma_load_2d(smem + i * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, row0, landed);
         }
       }
       __syncwarp();
@@ -166,8 +169,9 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
         if (elect_one()) {
           mbar_expect_tx(full_bar + stage, G_WTILE_BYTES);
           bulk_g2s(smem + stage * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + stage);
-          mbar_expect_tx(raw_bar + stage, xbytes);
-          tma_load_2d(smem + stage * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, row0, raw_bar + stage);
+          uint64_t* landed = p.norm_w ? raw_bar + stage : full_bar + stage;
+          mbar_expect_tx(landed, xbytes);
+          tma_load_2d(smem + stage * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, row0, landed);
         }
         __syncwarp();
         if (++stage == NS) { stage = 0; ph ^= 1; }
@@ -253,7 +257,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     if (normed && nkb > 0) wv_next = ldg_v4(p.norm_w + (int64_t)kb_begin * G_BK + (tp & 7) * 8);
     int stage = 0;
     uint32_t ph = 0;
-    for (int i = 0; i < nkb; ++i) {
+    for (int i = 0; normed && i < nkb; ++i) {       // plain GEMMs: the x copies complete on full_bar themselves
       const uint4 wv = wv_next;
       if (normed && i + 1 < nkb) wv_next = ldg_v4(p.norm_w + (int64_t)(kb_begin + i + 1) * G_BK + (tp & 7) * 8);
       mbar_wait(raw_bar + stage, ph);
@@ -409,12 +413,21 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       return q;
     };
     if (p.ssq_out) {
-      // one thread per batch row walks this CTA's feature groups in order: a deterministic partial
-      // sum of squares of the stored row slice, slot = (tile, rank)
+      // the items are spread over all threads as below; every item leaves the sum of squares of its 8 stored values
+      // in the (now dead) first cell it read, and one thread per batch row then adds the row's feature groups IN ORDER:
+      // a deterministic partial sum of squares of the stored row slice, slot = (tile, rank).  (One thread per row
+      // walking its groups itself left 2/3 of the CTA idle: 2.3 us of epilogue against 1.1 us without ssq.)
       const int slots = (p.n / G_BN) * S;
+      float* qcell = const_cast<float*>(red);
+      for (int it = threadIdx.x; it < items; it += G_THREADS) {
+        const int g8 = it / m_loc, m = it - g8 * m_loc;
+        const float q = item(m, g8, it == (int)threadIdx.x);
+        qcell[(int64_t)(g8 * 8) * (mpad + 4) + m] = q;
+      }
+      __syncthreads();
       for (int m = threadIdx.x; m < m_loc; m += G_THREADS) {
         float q = 0.f;
-        for (int g8 = 0; g8 < groups; ++g8) q += item(m, g8, g8 == 0);
+        for (int g8 = 0; g8 < groups; ++g8) q += qcell[(int64_t)(g8 * 8) * (mpad + 4) + m];
         p.ssq_out[(int64_t)(row0 + m) * slots + tile * S + rank] = q;
       }
     } else {
