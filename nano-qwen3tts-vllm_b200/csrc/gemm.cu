@@ -339,15 +339,15 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     if (S > 1) {
       fence_proxy_async();                      // generic-proxy stores -> visible to the bulk copies
       bar_sync_producers();
-      if (threadIdx.x == 64) {
+      const int tp = (int)threadIdx.x - 64;
+      if (tp < S) {
+        // one lane per peer: the S copies are issued side by side (one thread issuing them in turn spent ~0.1 us each)
         const uint32_t chunk = (uint32_t)(rows_own * rstride * 4);
         const uint32_t recv_local = smem_u32(recv) + (uint32_t)rank * chunk;
         const uint32_t bar_local = smem_u32(recv_bar);
-        for (int o = 0; o < S; ++o) {
-          const int peer = (rank + o) % S;      // spread the traffic
-          bulk_s2c(mapa_u32(recv_local, (uint32_t)peer), smem_u32(stg) + (uint32_t)peer * chunk, chunk,
-                   mapa_u32(bar_local, (uint32_t)peer));
-        }
+        const int peer = (rank + tp) % S;       // spread the traffic
+        bulk_s2c(mapa_u32(recv_local, (uint32_t)peer), smem_u32(stg) + (uint32_t)peer * chunk, chunk,
+                 mapa_u32(bar_local, (uint32_t)peer));
       }
     }
     if (threadIdx.x == 64) G_TRACE(5);

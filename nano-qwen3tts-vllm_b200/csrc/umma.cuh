@@ -118,20 +118,31 @@ __device__ __forceinline__ void bar_sync_producers() { asm volatile("bar.sync 1,
 
 // fused-norm transform of 8 staged x values: EAGER = bf16(bf16(x*rstd)*w) (layernorm.py:22-27 op by op),
 // FUSED = one rounding (what inductor emits); identical to rmsnorm_kernel's norm_out.
+// bf16x2 product, each lane rounded to nearest even: equals bf16(f32(a) * f32(b)) - the fp32 product of two bf16 values
+// is exact (8 + 8 significand bits), so there is one rounding either way
+__device__ __forceinline__ uint32_t mul_bf16x2(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+// The transform runs on 4 warps per CTA (8 per SM) for every k-block of a fused-norm GEMM and is bound by instruction
+// issue, so it is written for instruction count: EAGER = bf16(bf16(x * rstd) * w): two fp32 products and one packing
+// conversion per pair, then ONE bf16x2 multiply; FUSED = bf16((x * rstd) * w) in fp32.
+__device__ __forceinline__ uint32_t norm2_eager(uint32_t x, uint32_t w, float rs) {
+  return mul_bf16x2(pack_bf16(bf16lo(x) * rs, bf16hi(x) * rs), w);
+}
+__device__ __forceinline__ uint32_t norm2_fused(uint32_t x, uint32_t w, float rs) {
+  return pack_bf16((bf16lo(x) * rs) * bf16lo(w), (bf16hi(x) * rs) * bf16hi(w));
+}
 __device__ __forceinline__ uint4 norm8(uint4 x, uint4 w, float rs, bool eager) {
-  float xf[8], wf[8];
-  xf[0] = bf16lo(x.x); xf[1] = bf16hi(x.x); xf[2] = bf16lo(x.y); xf[3] = bf16hi(x.y);
-  xf[4] = bf16lo(x.z); xf[5] = bf16hi(x.z); xf[6] = bf16lo(x.w); xf[7] = bf16hi(x.w);
-  wf[0] = bf16lo(w.x); wf[1] = bf16hi(w.x); wf[2] = bf16lo(w.y); wf[3] = bf16hi(w.y);
-  wf[4] = bf16lo(w.z); wf[5] = bf16hi(w.z); wf[6] = bf16lo(w.w); wf[7] = bf16hi(w.w);
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const float t = xf[i] * rs;
-    xf[i] = (eager ? rbf(t) : t) * wf[i];
-  }
   uint4 o;
-  o.x = pack_bf16(xf[0], xf[1]); o.y = pack_bf16(xf[2], xf[3]);
-  o.z = pack_bf16(xf[4], xf[5]); o.w = pack_bf16(xf[6], xf[7]);
+  if (eager) {
+    o.x = norm2_eager(x.x, w.x, rs); o.y = norm2_eager(x.y, w.y, rs);
+    o.z = norm2_eager(x.z, w.z, rs); o.w = norm2_eager(x.w, w.w, rs);
+  } else {
+    o.x = norm2_fused(x.x, w.x, rs); o.y = norm2_fused(x.y, w.y, rs);
+    o.z = norm2_fused(x.z, w.z, rs); o.w = norm2_fused(x.w, w.w, rs);
+  }
   return o;
 }
 
