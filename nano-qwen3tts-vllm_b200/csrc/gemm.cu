@@ -281,26 +281,13 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     }
   }
 
-  // =========================== all threads: accumulator complete => this CTA's ring is free
-  mbar_wait(accum_bar, 0);
-  tc_fence_after();
-  if (threadIdx.x == 0) G_TRACE(4);
+  // =========================== all threads.  Everything that does not need the accumulator happens BEFORE the wait
+  // for it, i.e. while the last MMAs are still running: the (long complete) cluster barrier that says every peer has
+  // initialised its receive barrier (~0.25 us of instruction latency), and the first residual / bias vector.
   if (warp < 2) pdl_wait();                     // the epilogue below reads res / writes out
-  if (S > 1) cluster_wait();                    // (long complete) every peer has initialised its receive barrier
-
-  // Split-K exchange.  Every CTA spills its 128 x mpad fp32 partial to a staging area that aliases
-  // its own (now idle) ring, rows = features, padded by 4 floats (conflict-free 16-byte stores, and
-  // the reduce reads it conflict-free with lanes along m).  Feature rows of one owner are contiguous,
-  // so ONE bulk async copy per peer (shared::cta -> shared::cluster through the TMA unit) moves the
-  // slice into the owner's receive buffer recv[src][row][mpad+4] and completes on the OWNER's
-  // mbarrier: no cluster barrier on the critical path, no per-thread remote stores.  (Tried and removed:
-  // st.async straight from the TMEM registers into the peers' buffers - no staging, no proxy fence, no closing
-  // cluster barrier, yet 1.2 us slower per launch: 2048 16-byte remote stores per CTA cost more than 8 bulk copies.)
+  if (S > 1) cluster_wait();
   const int rows_own = G_BN / S;
   const int rstride = mpad + 4;
-  float* stg = reinterpret_cast<float*>(smem);
-  const float* red = (S > 1) ? recv : stg;
-  // the first epilogue item of every thread reads a residual / bias vector: request it before the exchange wait
   const int groups = rows_own >> 3;
   const int n0 = tile * G_BN + rank * rows_own;
   const int items = m_loc * groups;
@@ -310,6 +297,21 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     if (p.epilogue == B2TTS_GEMM_RESIDUAL) pre = ldg_v4(p.res + (int64_t)(row0 + m) * p.res_stride + n0 + g8 * 8);
     else if (p.epilogue == B2TTS_GEMM_BIAS && p.bias) pre = ldg_v4(p.bias + n0 + g8 * 8);
   }
+  // accumulator complete => this CTA's ring is free
+  mbar_wait(accum_bar, 0);
+  tc_fence_after();
+  if (threadIdx.x == 0) G_TRACE(4);
+
+  // Split-K exchange.  Every CTA spills its 128 x mpad fp32 partial to a staging area that aliases
+  // its own (now idle) ring, rows = features, padded by 4 floats (conflict-free 16-byte stores, and
+  // the reduce reads it conflict-free with lanes along m).  Feature rows of one owner are contiguous,
+  // so ONE bulk async copy per peer (shared::cta -> shared::cluster through the TMA unit) moves the
+  // slice into the owner's receive buffer recv[src][row][mpad+4] and completes on the OWNER's
+  // mbarrier: no cluster barrier on the critical path, no per-thread remote stores.  (Tried and removed:
+  // st.async straight from the TMEM registers into the peers' buffers - no staging, no proxy fence, no closing
+  // cluster barrier, yet 1.2 us slower per launch: 2048 16-byte remote stores per CTA cost more than 8 bulk copies.)
+  float* stg = reinterpret_cast<float*>(smem);
+  const float* red = (S > 1) ? recv : stg;
   if (warp >= 2) {
     const int q = warp & 3;                     // TMEM lane quarter this warp may read
     const int f = q * 32 + lane;                // feature row of the tile held by this thread
