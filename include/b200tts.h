@@ -257,7 +257,8 @@ B2TTS_API int    b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void
  *     rounding(x[m, k] * rstd[m], norm_weight[k]) (same rounding points as b2tts_rmsnorm) with
  *     rstd[m] = 1/sqrt(sum_j ssq_in[m, j] / k + eps), j < ssq_in_slots summed in a fixed order.
  *   ssq_out != NULL (bias / residual epilogues): ssq_out[m, slot] = sum of squares of the bf16 values this
- *     call stored in out[m, :] over slot's feature slice; slots per row = b2tts_gemm_ssq_slots(m, n, k, splits).
+ *     call stored in out[m, :] over slot's 128-feature tile; slots per row = b2tts_gemm_ssq_slots(m, n, k, splits)
+ *     = n / 128 (the K-split CTAs of a tile combine their sums inside the cluster, in rank order).
  *     The next b2tts_gemm_norm_bf16 over `out` takes it as ssq_in: the decoder layer's two norm launches
  *     disappear, and the normalised activations never reach HBM. */
 B2TTS_API int    b2tts_gemm_ssq_slots(int m, int n, int k, int splits);

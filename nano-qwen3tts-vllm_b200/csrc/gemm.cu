@@ -99,6 +99,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   uint64_t* recv_bar = accum_bar + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(recv_bar + 1);
   float* rstd_s = reinterpret_cast<float*>(tmem_slot + 2);        // [mpad]
+  float* qx_s = rstd_s + mpad;                                    // [S][mpad]: the cluster's per-row ssq partials (rank 0's copy is used)
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);       // provably warp-uniform
   const int lane = threadIdx.x & 31;
@@ -113,6 +114,8 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
 
   if (threadIdx.x == 0) G_TRACE(0);
   pdl_launch();
+  // the x tensor map's descriptor is fetched now, under the previous kernel's tail, not by the first copy after the wait
+  if (threadIdx.x == 32) asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&tmap_x)) : "memory");
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) {
@@ -219,11 +222,15 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   } else {
     // =========================== x tiles land by TMA; with the fused norm these 4 warps transform the
     // landed tile in place (shared-memory latency only), then release it to the MMA issuer.
-    pdl_wait();
-    if (threadIdx.x == 64) G_TRACE(2);
     const int tp = threadIdx.x - 64;
     const bool normed = p.norm_w != nullptr;
     const bool eager = p.rounding == B2TTS_ROUND_EAGER;
+    // the norm weights of the first k-block are constants: requested before the wait, not after the rstd prologue
+    // (where their ~0.7 us of load latency sat in front of the first transform)
+    uint4 wv_next = make_uint4(0, 0, 0, 0);
+    if (normed && nkb > 0) wv_next = ldg_v4(p.norm_w + (int64_t)kb_begin * G_BK + (tp & 7) * 8);
+    pdl_wait();
+    if (threadIdx.x == 64) G_TRACE(2);
     if (normed) {
       // rstd[m] from the partial sums of squares the producing kernel left: G lanes per row, each a
       // contiguous chunk summed in order, then a fixed shuffle tree (deterministic).
@@ -235,7 +242,18 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
         if (r < m_loc) {
           const float* src = p.ssq_in + (int64_t)(row0 + r) * p.ssq_in_slots + gl * chunk;
           if ((chunk & 3) == 0) {
-            for (int i = 0; i < chunk; i += 4) {
+            // 8 loads in flight, added in slot order: with one load per trip the 64-slot chunk of a row (16 tiles x 8
+            // splits of the producing GEMM, two lanes per row) was ~16 dependent L2 round trips, 2 us before the first
+            // x tile could be transformed
+            int i = 0;
+            for (; i + 32 <= chunk; i += 32) {
+              float4 v[8];
+#pragma unroll
+              for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const float4*>(src + i + 4 * u);
+#pragma unroll
+              for (int u = 0; u < 8; ++u) { sum += v[u].x; sum += v[u].y; sum += v[u].z; sum += v[u].w; }
+            }
+            for (; i < chunk; i += 4) {
               const float4 v = *reinterpret_cast<const float4*>(src + i);
               sum += v.x; sum += v.y; sum += v.z; sum += v.w;
             }
@@ -253,8 +271,6 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     }
     // the norm weights of the NEXT k-block are requested before waiting for this one's x tile: the global-load
     // latency (~0.7 us) would otherwise sit on the critical path of every k-block
-    uint4 wv_next = make_uint4(0, 0, 0, 0);
-    if (normed && nkb > 0) wv_next = ldg_v4(p.norm_w + (int64_t)kb_begin * G_BK + (tp & 7) * 8);
     int stage = 0;
     uint32_t ph = 0;
     for (int i = 0; normed && i < nkb; ++i) {       // plain GEMMs: the x copies complete on full_bar themselves
@@ -357,7 +373,9 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   tc_fence_before();
   if (S > 1) {
     mbar_wait(recv_bar, 0);                     // all S slices (own included) have landed
-    cluster_arrive();                           // my receive buffer is complete; peers may retire their staging
+    // my receive buffer is complete; peers may retire their staging.  With ssq_out the arrival comes after the epilogue
+    // instead: it then also publishes this CTA's per-row sums of squares to rank 0 (below)
+    if (!p.ssq_out) cluster_arrive();
   } else {
     __syncthreads();
   }
@@ -419,7 +437,11 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       // in the (now dead) first cell it read, and one thread per batch row then adds the row's feature groups IN ORDER:
       // a deterministic partial sum of squares of the stored row slice, slot = (tile, rank).  (One thread per row
       // walking its groups itself left 2/3 of the CTA idle: 2.3 us of epilogue against 1.1 us without ssq.)
-      const int slots = (p.n / G_BN) * S;
+      // The S CTAs of a tile then combine their per-row sums inside the cluster (remote store into rank 0's shared
+      // memory, the closing cluster barrier, rank 0 adds in rank order): ONE slot per (row, tile).  With a slot per (tile,
+      // rank) every CTA of the consuming GEMM summed tiles x S partials per row - 256 CTAs reading the same 32 KB
+      // at once made a hot spot in L2 that held the first fused-norm tile back by ~3 us.
+      const int slots = p.n / G_BN;
       float* qcell = const_cast<float*>(red);
       for (int it = threadIdx.x; it < items; it += G_THREADS) {
         const int g8 = it / m_loc, m = it - g8 * m_loc;
@@ -430,7 +452,18 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       for (int m = threadIdx.x; m < m_loc; m += G_THREADS) {
         float q = 0.f;
         for (int g8 = 0; g8 < groups; ++g8) q += qcell[(int64_t)(g8 * 8) * (mpad + 4) + m];
-        p.ssq_out[(int64_t)(row0 + m) * slots + tile * S + rank] = q;
+        if (S == 1) p.ssq_out[(int64_t)(row0 + m) * slots + tile] = q;
+        else st_cluster_f32(mapa_u32(smem_u32(qx_s + rank * mpad + m), 0u), q);
+      }
+      if (S > 1) {
+        cluster_arrive();                       // release: the remote stores above; also "my receive buffer is complete"
+        cluster_wait();
+        if (rank == 0)
+          for (int m = threadIdx.x; m < m_loc; m += G_THREADS) {
+            float q = 0.f;
+            for (int r = 0; r < S; ++r) q += qx_s[r * mpad + m];
+            p.ssq_out[(int64_t)(row0 + m) * slots + tile] = q;
+          }
       }
     } else {
       // item it = (feature group g8 = it / m_loc, batch row m = it % m_loc): lanes along m read red conflict-free
@@ -440,7 +473,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       }
     }
   }
-  if (S > 1) cluster_wait();                    // peers' copies out of my staging area have completed
+  if (S > 1 && !p.ssq_out) cluster_wait();      // peers' copies out of my staging area have completed
   __syncthreads();
   if (threadIdx.x == 0) G_TRACE(7);
   if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
@@ -473,8 +506,8 @@ gemm_pack_kernel(const __nv_bfloat16* __restrict__ w, int64_t w_stride, uint8_t*
 }
 
 static size_t gemm_smem_bytes(int mpad, int stages, int splits) {
-  return (size_t)stages * (G_WTILE_BYTES + mpad * 128) + (splits > 1 ? (size_t)(mpad + 4) * 512 : 0) + 256 + (size_t)mpad * 4 +
-         1024;
+  return (size_t)stages * (G_WTILE_BYTES + mpad * 128) + (splits > 1 ? (size_t)(mpad + 4) * 512 : 0) + 384 + (size_t)mpad * 4 +
+         (splits > 1 ? (size_t)splits * mpad * 4 : 0) + 1024;
 }
 
 // ring depth: the deepest ring that still lets two CTAs share an SM (the next GEMM's weight prefetch
@@ -697,8 +730,8 @@ extern "C" int b2tts_gemm_ssq_slots(int m, int n, int k, int splits) {
   if (n <= 0 || k <= 0 || n % b2::G_BN || k % b2::G_BK) return 0;
   const int nchunks = (m + b2::G_MAX_M - 1) / b2::G_MAX_M;
   const int mpad = nchunks > 1 ? b2::G_MAX_M : (m + 15) & ~15;
-  const int s = splits > 0 ? splits : b2::choose_splits((n / b2::G_BN) * nchunks, k / b2::G_BK, mpad);
-  return (n / b2::G_BN) * s;
+  (void)m; (void)splits;                        // one slot per 128-feature tile, whatever the K split
+  return n / b2::G_BN;
 }
 
 extern "C" int b2tts_gemm_norm_bf16(const void* x, int64_t x_row_stride, const void* w_packed,

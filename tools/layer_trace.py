@@ -68,6 +68,6 @@ for l in range(nl):
     tt = (t[l, :n].double() - base) / 1e3
     gap = "" if prev_end is None else f"  [gap from previous GEMM end to dep ok: {float(tt[:, 2].min()) - prev_end:5.1f}]"
     print(f"{ops[l % 4]:30s} CTAs {n:3d} " + "  ".join(f"{names[j]} {tt[:, j].min():6.1f}/{tt[:, j].median():6.1f}/{tt[:, j].max():6.1f}" for j in (0, 2, 4, 6, 7)) + gap)
-    per = tt[:, 5] - tt[:, 4]; ex = tt[:, 6] - tt[:, 5]; ep = tt[:, 7] - tt[:, 6]
-    print(f"{'':30s} per CTA (median): accum->staged {per.median():.2f}  staged->exchanged {ex.median():.2f} (min {ex.min():.2f} max {ex.max():.2f})  exchanged->end {ep.median():.2f}")
+    per = tt[:, 5] - tt[:, 4]; ex = tt[:, 6] - tt[:, 5]; ep = tt[:, 7] - tt[:, 6]; xf = tt[:, 3] - tt[:, 2]; mm = tt[:, 4] - tt[:, 3]
+    print(f"{'':30s} per CTA (median): dep ok->first x tile released {xf.median():.2f}  ->accum {mm.median():.2f}  accum->staged {per.median():.2f}  staged->exchanged {ex.median():.2f} (min {ex.min():.2f} max {ex.max():.2f})  exchanged->end {ep.median():.2f}")
     prev_end = float(tt[:, 7].max())
