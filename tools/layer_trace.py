@@ -20,7 +20,8 @@ for _ in range(3):
     loop.step()
 torch.cuda.synchronize()
 from nano_qwen3tts_vllm_b200.utils.context import reset_context, set_context
-T = loop.talker
+WHICH = sys.argv[2] if len(sys.argv) > 2 else "talker"          # "talker" | "predictor"
+T = loop.talker if WHICH == "talker" else loop.predictor
 layers = T.model.layers
 NL = 3
 lib = nat.lib()
@@ -28,11 +29,16 @@ lib.b2tts_debug_gemm_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
 
 
 def body():
-    set_context(False, slot_mapping=loop.t_slots, context_lens=loop.t_ctx, block_tables=loop.t_tables,
-                max_context_len=loop.width * loop.page)
-    residual, ssq = loop.embeds.clone(), None
+    if WHICH == "talker":
+        set_context(False, slot_mapping=loop.t_slots, context_lens=loop.t_ctx, block_tables=loop.t_tables,
+                    max_context_len=loop.width * loop.page)
+        residual, ssq, pos = loop.embeds.clone(), None, loop.t_pos
+    else:                                                       # the predictor's decode pass for codebook 5
+        lay = loop.p_dec[4]
+        set_context(False, slot_mapping=lay["slots"], context_lens=lay["ctx"], block_tables=loop.p_tables, max_context_len=7)
+        residual, ssq, pos = torch.randn(b, layers[0].input_layernorm.weight.shape[0], device=dev).to(torch.bfloat16), None, lay["pos"]
     for i in range(NL):
-        residual, ssq = layers[i].forward_decode(loop.t_pos, residual, ssq, in_place=True)
+        residual, ssq = layers[i].forward_decode(pos, residual, ssq, in_place=True)
     reset_context()
 
 
