@@ -76,9 +76,12 @@ class PredictorModelRunner(ModelRunner):
         last = h.view(bs, 2, -1)[:, 1]
         nat.topk_sample(linear(last, model.lm_head[0], nxt=qkv0), temps, noise[0], top_k=self.top_k, out=codes[0],
                         embed_table=model.model.codec_embedding[0], embed_out=self.burst_emb[:bs])
+        # the decode passes' slots / context lengths for all codebooks at once (two small launches instead of 3 per pass)
+        steps = self.burst_steps[:n].view(n, 1)                              # [n, 1]: g + 1 of pass g
+        slots_all = torch.where(live.view(1, bs), base.view(1, bs) + steps, -1).to(torch.int32)
+        ctx_all = torch.where(live.view(1, bs), steps + 1, 0).to(torch.int32)
         for g in range(1, n):
-            set_context(False, slot_mapping=torch.where(live, base + (g + 1), -1).to(torch.int32),
-                        context_lens=torch.where(live, g + 2, 0).to(torch.int32), block_tables=tables,
+            set_context(False, slot_mapping=slots_all[g], context_lens=ctx_all[g], block_tables=tables,
                         max_context_len=g + 2)
             h = model(self.burst_emb[:bs], self.burst_posg[g][:bs], head=g)
             last_pass = g == n - 1
@@ -96,6 +99,7 @@ class PredictorModelRunner(ModelRunner):
         self.burst_emb = torch.zeros(mb, ht, dtype=torch.bfloat16, device=dev)
         self.burst_noise = torch.ones(n * mb * self.stack_config.vocab_size, dtype=torch.float32, device=dev)
         self.burst_two = torch.tensor([0, 1], dtype=torch.int32, device=dev).view(1, 2)
+        self.burst_steps = torch.arange(1, n + 1, dtype=torch.int32, device=dev)     # row g: slot offset g + 1 of pass g
         self.burst_pos2 = torch.tensor([0, 1] * mb, dtype=torch.int64, device=dev)
         self.burst_cu = (torch.arange(mb + 1, dtype=torch.int32, device=dev) * 2).contiguous()
         self.burst_posg = [None] + [torch.full((mb,), g + 1, dtype=torch.int64, device=dev) for g in range(1, n)]
