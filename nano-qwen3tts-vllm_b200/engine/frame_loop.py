@@ -311,7 +311,7 @@ class StepApiFrameLoop:
     process, as in the reference (interface.py:1276-1286)."""
 
     def __init__(self, talker_llm, predictor_llm, tts_pad_embed: torch.Tensor, ignore_eos: bool = True,
-                 codec_eos: int = 2150, batched: bool = True):
+                 codec_eos: int = 2150, batched: bool = True, device_glue: bool = True):
         """``batched``: feed each engine with ONE ``add_requests`` call per frame (one pinned buffer, one host->device
         copy) and read the talker's hidden states as one tensor; False = one ``add_request`` per stream, exactly the
         reference's call pattern.  Same bytes across PCIe, same results."""
@@ -330,6 +330,21 @@ class StepApiFrameLoop:
         self.frames: dict[str, list[list[int]]] = {}
         self._pins: dict[str, torch.Tensor] = {}
         self.timing: dict[str, float] | None = None       # set to {} to accumulate wall time per phase (tools/e2e_profile.py)
+        # Work that only needs an engine step's DEVICE results is queued from hooks the engines call before the step's
+        # one synchronisation (batched mode): the predictor input [hidden, embed(code0)] is packed on the device and is
+        # on its way to the pinned host buffer while the talker's token ids are being read back, and the 16-codebook sum
+        # of the next talker input runs behind the predictor burst on the same stream.  The bytes still cross PCIe in
+        # both directions every frame; what disappears is a second synchronisation and three launches per engine step
+        # issued while the GPU idles.
+        self._t_hook = None                    # (n, pinned [n, 2, H], device code0 [n]) left by the talker hook
+        self._t_hook_calls = 0
+        self._nxt_hook = None                  # pinned [n, H]: the next talker input, left by the predictor hook
+        self._pack_dev = None
+        self._fast_rids: list[str] | None = None
+        self.device_glue = batched and device_glue      # False: every piece of glue starts from host values (tests)
+        if self.device_glue:
+            talker_llm.model_runner.post_sample_hook = self._talker_hook
+            predictor_llm.burst_hook = self._burst_hook
 
     def _mark(self, name: str, t0: float) -> float:
         import time
@@ -353,6 +368,29 @@ class StepApiFrameLoop:
         out.copy_(t, non_blocking=True)
         return out
 
+    def _talker_hook(self, seqs, tokens: torch.Tensor, hidden: torch.Tensor):
+        n, h = hidden.shape
+        self._t_hook_calls += 1
+        if self._pack_dev is None or self._pack_dev.shape[0] < n:
+            self._pack_dev = torch.empty(max(n, 64), 2, h, dtype=BF16, device=self.dev)
+        pk = self._pack_dev[:n]
+        pk[:, 0].copy_(hidden)                                                  # interface.py:1242-1252 on the device
+        nat.gather_rows(self.tmodel.model.codec_embedding.weight, tokens, out=pk[:, 1])
+        host = self._pinned("pred_in", (n, 2, h), BF16)
+        host.copy_(pk, non_blocking=True)
+        self._t_hook = (n, host, tokens)
+
+    def _burst_hook(self, seqs, codes: torch.Tensor):
+        self._nxt_hook = None
+        fast = self._fast_rids
+        if fast is None or len(seqs) != len(fast) or any(s.request_id != r for s, r in zip(seqs, fast)):
+            return
+        code0 = self._t_hook[2]
+        codes16 = torch.cat([code0.view(-1, 1), codes], 1)                      # [n, 16] on the device
+        nxt = nat.codec_embed_sum(self.tmodel.model.codec_embedding.weight, self.pmodel.model.codec_embedding, codes16,
+                                  extra=self.extra)                             # interface.py:1276-1290
+        self._nxt_hook = self._to_host("next_in", nxt)
+
     def add_streams(self, prompts: list[torch.Tensor]):
         """prompts: host bf16 [1, T, H] each.  Queues the prefill; ``step_frame`` runs it."""
         for p in prompts:
@@ -368,6 +406,7 @@ class StepApiFrameLoop:
         import time
         t = time.perf_counter()
         outs = []
+        self._t_hook, self._t_hook_calls, self._fast_rids, self._nxt_hook = None, 0, None, None
         while len(outs) < len(self.active):
             _, _, outs_all = self.talker.step_with_outputs()
             if not outs_all:
@@ -378,12 +417,21 @@ class StepApiFrameLoop:
         t = self._mark("talker.step_with_outputs", t)
         rids = [o[0] for o in outs]
         code0 = [o[2][-1] for o in outs]
-        last = getattr(self.talker, "last_step", None)
-        whole = self.batched and last is not None and len(last[0]) == len(outs) and last[2].shape[0] == len(outs)
-        hidden_dev = last[2] if whole else torch.stack([o[3] for o in outs], 0)
-        hidden_host = self._to_host("hidden", hidden_dev.float())               # protocol.py:78-91 (fp32 numpy)
-        self.d2h_bytes += hidden_host.numel() * 4 + 8 * len(outs)
         live = [i for i, c in enumerate(code0) if self.ignore_eos or c != self.codec_eos]
+        hooked = self._t_hook
+        fast = hooked is not None and self._t_hook_calls == 1 and hooked[0] == len(outs) and len(live) == len(outs)
+        if fast:
+            # the talker hook packed [hidden, embed(code0)] on the device and its copy to the pinned buffer completed
+            # with the step's synchronisation: same bytes to the host, no second round trip
+            pin_host = hooked[1]
+            self.d2h_bytes += pin_host.numel() * 2 + 8 * len(outs)
+            self._fast_rids = rids
+        else:
+            last = getattr(self.talker, "last_step", None)
+            whole = self.batched and last is not None and len(last[0]) == len(outs) and last[2].shape[0] == len(outs)
+            hidden_dev = last[2] if whole else torch.stack([o[3] for o in outs], 0)
+            hidden_host = self._to_host("hidden", hidden_dev.float())           # protocol.py:78-91 (fp32 numpy)
+            self.d2h_bytes += hidden_host.numel() * 4 + 8 * len(outs)
         for i, rid in enumerate(rids):
             if i not in live:
                 self.talker.clear_request(rid)                                  # interface.py:1233-1239
@@ -391,15 +439,16 @@ class StepApiFrameLoop:
                 self.active.remove(rid)
         if not live:
             return 0
-        # predictor input = [hidden, embed(code0)] per stream                   interface.py:1242-1252
-        c0 = torch.tensor([code0[i] for i in live], dtype=torch.int64)
-        emb0 = nat.gather_rows(self.tmodel.model.codec_embedding.weight, c0.to(self.dev, non_blocking=True))
-        emb0_host = self._to_host("emb0", emb0)
-        torch.cuda.current_stream().synchronize()                               # hidden + embed(code0) are on the host
-        pin_host = self._pinned("pred_in", (len(live), 2, hidden_host.shape[-1]), BF16)        # [n, 2, H]
-        pin_host[:, 0].copy_(hidden_host if len(live) == len(outs) else hidden_host[live])
-        pin_host[:, 1].copy_(emb0_host)
-        self.d2h_bytes += emb0.numel() * 2
+        if not fast:
+            # predictor input = [hidden, embed(code0)] per stream               interface.py:1242-1252
+            c0 = torch.tensor([code0[i] for i in live], dtype=torch.int64)
+            emb0 = nat.gather_rows(self.tmodel.model.codec_embedding.weight, c0.to(self.dev, non_blocking=True))
+            emb0_host = self._to_host("emb0", emb0)
+            torch.cuda.current_stream().synchronize()                           # hidden + embed(code0) are on the host
+            pin_host = self._pinned("pred_in", (len(live), 2, hidden_host.shape[-1]), BF16)    # [n, 2, H]
+            pin_host[:, 0].copy_(hidden_host if len(live) == len(outs) else hidden_host[live])
+            pin_host[:, 1].copy_(emb0_host)
+            self.d2h_bytes += emb0.numel() * 2
         self.h2d_bytes += pin_host.numel() * 2
         t = self._mark("hidden + embed(code0) to host, pack", t)
         if self.batched:
@@ -416,15 +465,23 @@ class StepApiFrameLoop:
         t = self._mark("predictor.step (burst)", t)
         self.d2h_bytes += 8 * 15 * len(live)
         rows = [[code0[i]] + done[rids[i]] for i in live]
-        codes16 = torch.tensor(rows, dtype=torch.int64)
-        # next talker input                                                      interface.py:1276-1290
-        nxt = nat.codec_embed_sum(self.tmodel.model.codec_embedding.weight, self.pmodel.model.codec_embedding,
-                                  codes16.to(self.dev, non_blocking=True), extra=self.extra)
-        nxt_host = self._to_host("next_in", nxt)
-        for row, i in zip(rows, live):                                          # while the sum is on its way back
-            self.frames[rids[i]].append(row)
-        torch.cuda.current_stream().synchronize()
-        self.h2d_bytes += codes16.numel() * 8 + nxt_host.numel() * 2
+        nxt_host = self._nxt_hook
+        if nxt_host is not None:
+            # the predictor hook summed the 16 codebook embeddings behind the burst; the copy to the pinned buffer
+            # completed with the burst's synchronisation
+            for row, i in zip(rows, live):
+                self.frames[rids[i]].append(row)
+        else:
+            codes16 = torch.tensor(rows, dtype=torch.int64)
+            # next talker input                                                  interface.py:1276-1290
+            nxt = nat.codec_embed_sum(self.tmodel.model.codec_embedding.weight, self.pmodel.model.codec_embedding,
+                                      codes16.to(self.dev, non_blocking=True), extra=self.extra)
+            nxt_host = self._to_host("next_in", nxt)
+            for row, i in zip(rows, live):                                      # while the sum is on its way back
+                self.frames[rids[i]].append(row)
+            torch.cuda.current_stream().synchronize()
+            self.h2d_bytes += codes16.numel() * 8
+        self.h2d_bytes += nxt_host.numel() * 2
         self.d2h_bytes += nxt_host.numel() * 2
         t = self._mark("frames bookkeeping + embed sum to host", t)
         if self.batched:
@@ -440,3 +497,9 @@ class StepApiFrameLoop:
             self.talker.clear_request(rid)
             self.predictor.clear_request(rid)
         self.active = []
+        if self.device_glue:
+            runner = getattr(self.talker, "model_runner", None)
+            if runner is not None and getattr(runner, "post_sample_hook", None) == self._talker_hook:
+                runner.post_sample_hook = None
+            if getattr(self.predictor, "burst_hook", None) == self._burst_hook:
+                self.predictor.burst_hook = None

@@ -29,13 +29,15 @@ class PredictorLLMEngine(LLMEngine):
         """Batched ``add_request``: ``inputs_embeds`` [n, 2, H] (host, ideally pinned) crosses PCIe as ONE copy; request
         i gets row i.  Same queueing as n single calls."""
         dev = self._to_device(inputs_embeds)
+        rows = dev.unsqueeze(1).unbind(0)                  # n views [1, 2, H] from one call (a slice per request costs ~1.5 us each)
+        known, waiting = self.scheduler.request_id_to_seq, self.scheduler.waiting
         for i, rid in enumerate(request_ids):
-            seq = PredictorSequence([], input_embeds=dev[i:i + 1], sampling_params=sampling_params, generation_steps=0,
+            seq = PredictorSequence([], input_embeds=rows[i], sampling_params=sampling_params, generation_steps=0,
                                     request_id=rid)
             seq.batch_src = (dev, i)
             if rid is not None:
-                self.scheduler.request_id_to_seq[rid] = seq
-            self.scheduler.add(seq)
+                known[rid] = seq
+            waiting.append(seq)
 
     burst = True          # whole-request graphs (PredictorModelRunner.run_burst); False = step by step as the reference
 
@@ -43,6 +45,9 @@ class PredictorLLMEngine(LLMEngine):
         """Every scheduled sequence is a fresh 2-row request: one graph replay yields all of its codes."""
         n_codes = self.model_runner.burst_codes()
         codes = self.model_runner.call("run_burst", seqs)                    # replay queued; the GPU is busy from here
+        hook = getattr(self, "burst_hook", None)
+        if hook is not None:
+            hook(seqs, codes)                    # caller work on the DEVICE codes, queued before the burst's one synchronisation
         for s in seqs:                                                       # bookkeeping that needs no code values
             s.num_tokens += n_codes
             s.generation_steps += n_codes

@@ -37,10 +37,11 @@ class TalkerLLMEngine(LLMEngine):
         ideally pinned) crosses PCIe as ONE copy; row i belongs to ``request_ids[i]``."""
         dev = self._to_device(inputs_embeds)
         known = self.scheduler.request_id_to_seq
+        rows = dev.unbind(0)                               # n row views from one call
         for i, rid in enumerate(request_ids):
             seq = known.get(rid) if rid is not None else None
             if seq is not None:
-                seq.decode_input_embeds = dev[i]
+                seq.decode_input_embeds = rows[i]
                 seq.batch_src = (dev, i)
                 continue
             seq = Sequence([], input_embeds=dev[i:i + 1], sampling_params=sampling_params, request_id=rid)

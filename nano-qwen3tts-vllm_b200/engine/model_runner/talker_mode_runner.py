@@ -129,6 +129,12 @@ class TalkerModeModelRunner(ModelRunner):
     def run(self, seqs: list[Sequence], is_prefill: bool):
         logits, hidden = self.run_model(seqs, is_prefill)
         temperatures = self.layout.d["temperatures"][:len(seqs)] if not is_prefill else self.prepare_sample(seqs)
-        token_ids = self.sampler(logits, temperatures, top_k=self.top_k).tolist()              # the step's one device sync
+        tokens = self.sampler(logits, temperatures, top_k=self.top_k)
+        hook = getattr(self, "post_sample_hook", None)
+        if hook is not None:
+            # caller work that only needs the step's DEVICE results (e.g. StepApiFrameLoop packing the predictor input and
+            # starting its device->host copy) is queued before the step's one synchronisation, not after it
+            hook(seqs, tokens, hidden)
+        token_ids = tokens.tolist()                                                             # the step's one device sync
         reset_context()
         return token_ids, hidden.clone()

@@ -226,3 +226,32 @@ def test_step_api_frame_loop_greedy_vs_oracle(setup, batched):
         assert predictor.model_runner.burst_top_k == 1           # the burst graphs were re-captured for greedy and used
         talker.exit(); predictor.exit()
     _check_against_oracle(got, setup["want"], setup["margins"])
+
+
+def test_step_api_device_glue_equals_host_glue(setup):
+    """The batched step-API loop packs the predictor input and sums the next talker input from the engines' DEVICE
+    results (hooks queued before each step's synchronisation); starting every piece of glue from the host values
+    instead (the reference's order of operations) must give the same frames and the same pinned buffers."""
+    from nano_qwen3tts_vllm_b200.engine.frame_loop import StepApiFrameLoop
+    from nano_qwen3tts_vllm_b200.llm import PredictorLLM, TalkerLLM
+    _, _, tw, pw = small_weights()
+    kw = dict(num_kvcache_blocks=4 * B, max_num_seqs=max(B, 2), max_model_len=512, graph_batch_sizes=[B])
+    got = []
+    for glue in (True, False):
+        talker, predictor = TalkerLLM(small_model_config(), state_dict=tw, **kw), PredictorLLM(small_model_config(), state_dict=pw, **kw)
+        talker.model_runner.top_k = predictor.model_runner.top_k = 1
+        torch.manual_seed(4321)                     # exact ties at the top are kept by top-k and decided by the noise
+        api = StepApiFrameLoop(talker, predictor, setup["pad"], batched=True, device_glue=glue)
+        api.add_streams([x.unsqueeze(0).pin_memory() for x in setup["prompts"]])
+        for _ in range(8):
+            api.step_frame()
+        torch.cuda.synchronize()
+        got.append((torch.tensor([api.frames[f"s{i}"] for i in range(B)]), api._pins["pred_in"].clone(), api._pins["next_in"].clone(),
+                    api.h2d_bytes, api.d2h_bytes))
+        api.close()
+        assert talker.model_runner.post_sample_hook is None if glue else not hasattr(talker.model_runner, "post_sample_hook") \
+            or talker.model_runner.post_sample_hook is None
+        talker.exit(); predictor.exit()
+    assert torch.equal(got[0][0], got[1][0])
+    assert torch.equal(got[0][1], got[1][1]) and torch.equal(got[0][2], got[1][2])
+    assert got[0][3] > 0 and got[0][4] > 0
