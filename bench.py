@@ -614,7 +614,7 @@ def main():
         if rank == 0:
             line["e2e"] = {"value": round(e2e_fps, 1), "unit": "frames/s", "h2d_bytes_per_step": int(h2d),
                            "d2h_bytes_per_step": int(d2h), "steps": a.e2e_steps, "segments": "median of 3",
-                           "api": "TalkerLLM.add_request/step_with_outputs + PredictorLLM.add_request/step, pinned host tensors"}
+                           "api": "TalkerLLM.add_requests/step_launch/step_collect + PredictorLLM.add_requests/step_launch/step_collect (StepApiFrameLoop, pipelined), pinned host tensors"}
     # ---- other stream counts (BASELINE configs[1], [2], [4]) on rank 0, short runs
     if rank == 0 and world == 1 and a.also_streams:
         others = {}

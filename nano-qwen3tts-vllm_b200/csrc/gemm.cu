@@ -200,13 +200,12 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       for (int i = 0; i < nkb; ++i) {
         mbar_wait(full_bar + stage, ph);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + stage * stage_bytes);
-        const uint32_t b_addr = a_addr + G_WTILE_BYTES;
+        const uint32_t a_lo = umma_desc_lo_sw128(smem_u32(smem + stage * stage_bytes));
+        const uint32_t b_lo = a_lo + (G_WTILE_BYTES >> 4);
         if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < G_BK / 16; ++k)
-            umma_bf16(tmem_base, umma_desc_sw128(a_addr + k * 32), umma_desc_sw128(b_addr + k * 32), idesc,
-                      (uint32_t)((i | k) != 0));
+            umma_bf16_lo(tmem_base, a_lo + 2 * k, b_lo + 2 * k, idesc, (uint32_t)((i | k) != 0));
           // stage reusable once these MMAs have read it - but only a k-block NS later ever waits for that: the
           // commits of the last NS k-blocks (ALL of them for the split-K decode shapes, whose K range fits the ring)
           // would be ~0.2 us of issue time each for a barrier nobody reads

@@ -47,6 +47,23 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "}"
       :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// The descriptors of the K steps inside one SWIZZLE_128B tile differ only in the start-address field: +2 (32 bytes >> 4)
+// per step of 16 bf16, carry-free for 1024-byte aligned tiles.  Passing the low words (base + 2k, an immediate add) and the
+// constant high word keeps the per-step address arithmetic out of the issuing thread's dependent chain.
+__device__ __forceinline__ uint32_t umma_desc_lo_sw128(uint32_t smem_addr) { return ((smem_addr & 0x3ffffu) >> 4) | (1u << 16); }
+constexpr uint32_t UMMA_DESC_HI_SW128 = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ void umma_bf16_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\t"
+      "mov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t"
+      "}"
+      :: "r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(UMMA_DESC_HI_SW128) : "memory");
+}
 // one lane of a converged warp; the surrounding code stays warp-uniform, so operand descriptors live in uniform
 // registers instead of being broadcast lane by lane in front of every tcgen05.mma
 __device__ __forceinline__ bool elect_one() {

@@ -311,7 +311,7 @@ class StepApiFrameLoop:
     process, as in the reference (interface.py:1276-1286)."""
 
     def __init__(self, talker_llm, predictor_llm, tts_pad_embed: torch.Tensor, ignore_eos: bool = True,
-                 codec_eos: int = 2150, batched: bool = True, device_glue: bool = True):
+                 codec_eos: int = 2150, batched: bool = True, device_glue: bool = True, pipelined: bool = True):
         """``batched``: feed each engine with ONE ``add_requests`` call per frame (one pinned buffer, one host->device
         copy) and read the talker's hidden states as one tensor; False = one ``add_request`` per stream, exactly the
         reference's call pattern.  Same bytes across PCIe, same results."""
@@ -342,6 +342,13 @@ class StepApiFrameLoop:
         self._pack_dev = None
         self._fast_rids: list[str] | None = None
         self.device_glue = batched and device_glue      # False: every piece of glue starts from host values (tests)
+        # pipelined: each engine's step is split into launch / collect (``step_launch`` / ``step_collect``) and the next
+        # engine's work is queued - its input crossing PCIe through the pinned buffer in stream order - BEFORE the host
+        # waits for the previous one, so the GPU never idles on host bookkeeping: the predictor burst of frame f is queued
+        # behind the talker step of frame f (speculatively for streams whose code0 turns out to be the codec EOS: their
+        # codes are dropped), and the talker step of frame f + 1 behind the burst of frame f.
+        self.pipelined = self.device_glue and pipelined
+        self._launched_t = None                # a talker step in flight, launched at the end of the previous frame
         if self.device_glue:
             talker_llm.model_runner.post_sample_hook = self._talker_hook
             predictor_llm.burst_hook = self._burst_hook
@@ -360,7 +367,8 @@ class StepApiFrameLoop:
             n *= d
         buf = self._pins.get(name)
         if buf is None or buf.numel() < n or buf.dtype != dtype:
-            buf = self._pins[name] = torch.empty(max(n, 1), dtype=dtype).pin_memory()
+            with torch.inference_mode(False):      # the engine hooks run under inference_mode; these buffers are also
+                buf = self._pins[name] = torch.empty(max(n, 1), dtype=dtype).pin_memory()      # written outside of it
         return buf[:n].view(*shape)
 
     def _to_host(self, name: str, t: torch.Tensor) -> torch.Tensor:
@@ -378,7 +386,7 @@ class StepApiFrameLoop:
         nat.gather_rows(self.tmodel.model.codec_embedding.weight, tokens, out=pk[:, 1])
         host = self._pinned("pred_in", (n, 2, h), BF16)
         host.copy_(pk, non_blocking=True)
-        self._t_hook = (n, host, tokens)
+        self._t_hook = (n, host, tokens, [q.request_id for q in seqs])
 
     def _burst_hook(self, seqs, codes: torch.Tensor):
         self._nxt_hook = None
@@ -403,10 +411,95 @@ class StepApiFrameLoop:
     def step_frame(self) -> int:
         """One talker step for every active stream + the predictor burst + next-input assembly.
         Returns the number of frames completed."""
+        if self.pipelined:
+            return self._step_frame_pipelined()
+        return self._step_frame_sequential()
+
+    def _launch_talker(self):
+        self._t_hook, self._t_hook_calls, self._fast_rids, self._nxt_hook = None, 0, None, None
+        return self.talker.step_launch()
+
+    def _step_frame_pipelined(self) -> int:
+        import time
+        t = time.perf_counter()
+        lt, self._launched_t = self._launched_t, None
+        if lt is None:
+            lt = self._launch_talker()
+            if lt is None:
+                return 0
+        hooked = self._t_hook
+        if hooked is None or self._t_hook_calls != 1 or hooked[0] != len(self.active) or set(hooked[3]) != set(self.active):
+            # e.g. a prefill that needs several steps: this frame runs in the reference's order
+            return self._step_frame_sequential(first=self.talker.step_collect(lt))
+        n, pin_host, _, rids = hooked
+        # ---- predictor burst of this frame, queued behind the talker step (its input: device -> pinned -> device in
+        # stream order); speculative for streams about to hit the codec EOS            interface.py:1242-1268
+        self.predictor.add_requests(pin_host, self.p_sp, rids)
+        self._fast_rids = rids
+        lp = self.predictor.step_launch()
+        self.h2d_bytes += pin_host.numel() * 2
+        self.d2h_bytes += pin_host.numel() * 2 + 8 * n
+        t = self._mark("predictor queued behind the talker step", t)
+        # ---- the talker's token ids (the wait covers the talker step only)
+        outs = self.talker.step_collect(lt)[2]
+        t = self._mark("talker.step_collect", t)
+        code0 = [o[2][-1] for o in outs]
+        assert [o[0] for o in outs] == rids
+        live = [i for i, c in enumerate(code0) if self.ignore_eos or c != self.codec_eos]
+        for i, rid in enumerate(rids):
+            if i not in live:
+                self.talker.clear_request(rid)                                  # interface.py:1233-1239
+                self.predictor.clear_request(rid)
+                self.active.remove(rid)
+        nxt_host = self._nxt_hook
+        all_live = len(live) == n and nxt_host is not None
+        if all_live:
+            # ---- the talker step of the NEXT frame, queued behind the burst (same stream-ordered hand-over)
+            self.talker.add_requests(nxt_host.unsqueeze(1), self.t_sp, rids)
+            self.h2d_bytes += nxt_host.numel() * 2
+            self.d2h_bytes += nxt_host.numel() * 2
+            self._launched_t = self._launch_talker()
+            t = self._mark("next talker step queued behind the burst", t)
+        fin, _ = self.predictor.step_collect(lp)
+        done = {rid: codes for rid, _, codes in fin}
+        while len(done) < n:                                                    # (a burst always finishes in one step)
+            fin, _ = self.predictor.step()
+            if not fin:
+                break
+            for rid, _, codes in fin:
+                done[rid] = codes
+        t = self._mark("predictor.step_collect", t)
+        self.d2h_bytes += 8 * 15 * n
+        rows = [[code0[i]] + done[rids[i]] for i in live]
+        for row, i in zip(rows, live):
+            self.frames[rids[i]].append(row)
+        if live and not all_live:
+            # a stream retired this frame: the survivors' next inputs are picked on the host, after the burst
+            nxt_all = nxt_host if nxt_host is not None else None
+            if nxt_all is None:
+                codes16 = torch.tensor(rows, dtype=torch.int64)
+                nxt = nat.codec_embed_sum(self.tmodel.model.codec_embedding.weight, self.pmodel.model.codec_embedding,
+                                          codes16.to(self.dev, non_blocking=True), extra=self.extra)
+                sel = self._to_host("next_in", nxt)
+                torch.cuda.current_stream().synchronize()
+                self.h2d_bytes += codes16.numel() * 8
+            else:
+                sel = self._pinned("next_sel", (len(live), nxt_all.shape[-1]), BF16)
+                sel.copy_(nxt_all[live])
+            self.h2d_bytes += sel.numel() * 2
+            self.d2h_bytes += sel.numel() * 2
+            self.talker.add_requests(sel.unsqueeze(1), self.t_sp, [rids[i] for i in live])
+        self._mark("frames bookkeeping", t)
+        return len(live)
+
+    def _step_frame_sequential(self, first=None) -> int:
         import time
         t = time.perf_counter()
         outs = []
-        self._t_hook, self._t_hook_calls, self._fast_rids, self._nxt_hook = None, 0, None, None
+        if first is None:
+            self._t_hook, self._t_hook_calls, self._fast_rids, self._nxt_hook = None, 0, None, None
+        else:
+            outs += first[2]
         while len(outs) < len(self.active):
             _, _, outs_all = self.talker.step_with_outputs()
             if not outs_all:
@@ -493,6 +586,9 @@ class StepApiFrameLoop:
         return len(live)
 
     def close(self):
+        if self._launched_t is not None:                                        # a step queued ahead: let it finish
+            self.talker.step_collect(self._launched_t)
+            self._launched_t = None
         for rid in list(self.active):
             self.talker.clear_request(rid)
             self.predictor.clear_request(rid)

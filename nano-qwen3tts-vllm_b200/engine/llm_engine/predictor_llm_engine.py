@@ -41,22 +41,56 @@ class PredictorLLMEngine(LLMEngine):
 
     burst = True          # whole-request graphs (PredictorModelRunner.run_burst); False = step by step as the reference
 
-    def _step_burst(self, seqs):
-        """Every scheduled sequence is a fresh 2-row request: one graph replay yields all of its codes."""
+    def _burst_launch(self, seqs):
+        """Every scheduled sequence is a fresh 2-row request: one graph replay yields all of its codes.  Queues the
+        replay, the caller's hook and the copy of the codes to a pinned buffer; ``_burst_collect`` waits."""
         n_codes = self.model_runner.burst_codes()
         codes = self.model_runner.call("run_burst", seqs)                    # replay queued; the GPU is busy from here
         hook = getattr(self, "burst_hook", None)
         if hook is not None:
             hook(seqs, codes)                    # caller work on the DEVICE codes, queued before the burst's one synchronisation
+        n = len(seqs)
+        pins = self.__dict__.setdefault("_code_pins", [None, None, 0])
+        slot = pins[2] = pins[2] ^ 1
+        if pins[slot] is None or pins[slot].shape[0] < n:
+            pins[slot] = torch.empty(max(n, 64), n_codes, dtype=torch.int64).pin_memory()
+        host = pins[slot][:n]
+        host.copy_(codes, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record()
         for s in seqs:                                                       # bookkeeping that needs no code values
             s.num_tokens += n_codes
             s.generation_steps += n_codes
             self.scheduler._finish(s)
-        toks = codes.tolist()                                                # the one synchronisation of the burst
+        return seqs, host, done
+
+    def _burst_collect(self, launched):
+        seqs, host, done = launched
+        done.synchronize()                                                   # the one synchronisation of the burst
+        toks = host.tolist()
         for s, row in zip(seqs, toks):
             s.token_ids.extend(row)
             s.last_token = row[-1]
-        return [(s.request_id, s.seq_id, s.completion_token_ids) for s in seqs], sum(2 for _ in seqs)
+        return [(s.request_id, s.seq_id, s.completion_token_ids) for s in seqs], 2 * len(seqs)
+
+    def _step_burst(self, seqs):
+        return self._burst_collect(self._burst_launch(seqs))
+
+    def step_launch(self):
+        """Schedule and QUEUE one step without waiting for the GPU when the batch is a whole-request burst (otherwise the
+        step runs to completion here); ``step_collect`` returns what ``step`` returns."""
+        seqs, is_prefill = self.scheduler.schedule()
+        if not seqs:
+            return None
+        if is_prefill and self.burst and self.scheduler.eos < 0 and self.model_runner.burst_ok(seqs):
+            return "burst", self._burst_launch(seqs)
+        return "done", self._step_scheduled(seqs, is_prefill)
+
+    def step_collect(self, launched):
+        if launched is None:
+            return [], 0
+        kind, payload = launched
+        return self._burst_collect(payload) if kind == "burst" else payload
 
     # The predictor never stops on an EOS id (config.eos stays -1: no tokenizer, predictor_llm_engine.py:33-66 of the
     # reference finishes on max_tokens), so the sampled codes are only needed on the host when a sequence finishes.
@@ -117,6 +151,9 @@ class PredictorLLMEngine(LLMEngine):
         seqs, is_prefill = self.scheduler.schedule()
         if not seqs:
             return [], 0
+        return self._step_scheduled(seqs, is_prefill)
+
+    def _step_scheduled(self, seqs, is_prefill):
         if is_prefill and self.burst and self.scheduler.eos < 0 and self.model_runner.burst_ok(seqs):
             return self._step_burst(seqs)
         if self.defer_tokens and self.scheduler.eos < 0 and all(not s.token_ids or hasattr(s, "_deferred") for s in seqs):

@@ -49,6 +49,29 @@ class TalkerLLMEngine(LLMEngine):
                 known[rid] = seq
             self.scheduler.add(seq)
 
+    def step_launch(self):
+        """Schedule and QUEUE one step; returns a handle for ``step_collect`` (None: nothing to run).  Between the two
+        calls the GPU is busy and the host is free - e.g. to queue another engine's work that only needs this step's
+        device results (``model_runner.post_sample_hook``)."""
+        seqs, is_prefill = self.scheduler.schedule()
+        if not seqs:
+            return None
+        return seqs, is_prefill, self.model_runner.call("run_launch", seqs, is_prefill)
+
+    def step_collect(self, launched):
+        """Wait for a launched step; returns what ``step_with_outputs`` returns."""
+        if launched is None:
+            return [], 0, []
+        seqs, is_prefill, pending = launched
+        token_ids, hidden = self.model_runner.call("run_collect", pending)
+        self.scheduler.postprocess(seqs, token_ids, hidden)
+        self.last_step = (seqs, token_ids, hidden)      # the step's batch as a whole: hidden [n, H] on the device
+        num_tokens = sum(len(s) for s in seqs) if is_prefill else -len(seqs)      # counted after the append, as the reference
+        outputs = [(s.request_id, s.seq_id, s.completion_token_ids, s.last_hidden_state) for s in seqs if s.is_finished]
+        outputs_all = [(s.request_id, s.seq_id, s.completion_token_ids, s.last_hidden_state, s.is_finished)
+                       for s in seqs]
+        return outputs, num_tokens, outputs_all
+
     def _step(self):
         seqs, is_prefill = self.scheduler.schedule()
         if not seqs:

@@ -126,7 +126,9 @@ class TalkerModeModelRunner(ModelRunner):
         return self.model.compute_logits(hidden), hidden
 
     @torch.inference_mode()
-    def run(self, seqs: list[Sequence], is_prefill: bool):
+    def run_launch(self, seqs: list[Sequence], is_prefill: bool):
+        """Queue the step (layout upload, graph replay / eager pass, head, sampler, the caller's hook, the copy of the
+        token ids to a pinned buffer) and return without waiting for the GPU: ``run_collect`` does the step's one wait."""
         logits, hidden = self.run_model(seqs, is_prefill)
         temperatures = self.layout.d["temperatures"][:len(seqs)] if not is_prefill else self.prepare_sample(seqs)
         tokens = self.sampler(logits, temperatures, top_k=self.top_k)
@@ -135,6 +137,22 @@ class TalkerModeModelRunner(ModelRunner):
             # caller work that only needs the step's DEVICE results (e.g. StepApiFrameLoop packing the predictor input and
             # starting its device->host copy) is queued before the step's one synchronisation, not after it
             hook(seqs, tokens, hidden)
-        token_ids = tokens.tolist()                                                             # the step's one device sync
         reset_context()
-        return token_ids, hidden.clone()
+        n = len(seqs)
+        pins = self.__dict__.setdefault("_token_pins", [None, None, 0])
+        slot = pins[2] = pins[2] ^ 1
+        if pins[slot] is None or pins[slot].numel() < n:
+            pins[slot] = torch.empty(max(n, 64), dtype=torch.int64).pin_memory()
+        host = pins[slot][:n]
+        host.copy_(tokens, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record()
+        return host, done, hidden.clone()
+
+    def run_collect(self, launched):
+        host, done, hidden = launched
+        done.synchronize()                                                                      # the step's one device sync
+        return host.tolist(), hidden
+
+    def run(self, seqs: list[Sequence], is_prefill: bool):
+        return self.run_collect(self.run_launch(seqs, is_prefill))

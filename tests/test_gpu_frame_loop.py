@@ -228,30 +228,60 @@ def test_step_api_frame_loop_greedy_vs_oracle(setup, batched):
     _check_against_oracle(got, setup["want"], setup["margins"])
 
 
-def test_step_api_device_glue_equals_host_glue(setup):
-    """The batched step-API loop packs the predictor input and sums the next talker input from the engines' DEVICE
-    results (hooks queued before each step's synchronisation); starting every piece of glue from the host values
-    instead (the reference's order of operations) must give the same frames and the same pinned buffers."""
+def test_step_api_device_glue_and_pipelining_equal_host_glue(setup):
+    """The batched step-API loop (a) packs the predictor input and sums the next talker input from the engines' DEVICE
+    results (hooks queued before each step's synchronisation) and (b) queues the next engine's step before waiting for
+    the previous one (step_launch / step_collect).  Starting every piece of glue from the host values, in the
+    reference's order of operations, must give the same frames - and, without the run-ahead, the same pinned buffers."""
     from nano_qwen3tts_vllm_b200.engine.frame_loop import StepApiFrameLoop
     from nano_qwen3tts_vllm_b200.llm import PredictorLLM, TalkerLLM
     _, _, tw, pw = small_weights()
     kw = dict(num_kvcache_blocks=4 * B, max_num_seqs=max(B, 2), max_model_len=512, graph_batch_sizes=[B])
     got = []
-    for glue in (True, False):
+    for glue, piped in ((True, True), (True, False), (False, False)):
         talker, predictor = TalkerLLM(small_model_config(), state_dict=tw, **kw), PredictorLLM(small_model_config(), state_dict=pw, **kw)
         talker.model_runner.top_k = predictor.model_runner.top_k = 1
         torch.manual_seed(4321)                     # exact ties at the top are kept by top-k and decided by the noise
-        api = StepApiFrameLoop(talker, predictor, setup["pad"], batched=True, device_glue=glue)
+        api = StepApiFrameLoop(talker, predictor, setup["pad"], batched=True, device_glue=glue, pipelined=piped)
+        assert api.pipelined == piped
         api.add_streams([x.unsqueeze(0).pin_memory() for x in setup["prompts"]])
         for _ in range(8):
-            api.step_frame()
+            assert api.step_frame() == B
         torch.cuda.synchronize()
         got.append((torch.tensor([api.frames[f"s{i}"] for i in range(B)]), api._pins["pred_in"].clone(), api._pins["next_in"].clone(),
                     api.h2d_bytes, api.d2h_bytes))
         api.close()
-        assert talker.model_runner.post_sample_hook is None if glue else not hasattr(talker.model_runner, "post_sample_hook") \
-            or talker.model_runner.post_sample_hook is None
+        assert getattr(talker.model_runner, "post_sample_hook", None) is None and getattr(predictor, "burst_hook", None) is None
         talker.exit(); predictor.exit()
-    assert torch.equal(got[0][0], got[1][0])
-    assert torch.equal(got[0][1], got[1][1]) and torch.equal(got[0][2], got[1][2])
-    assert got[0][3] > 0 and got[0][4] > 0
+    assert torch.equal(got[0][0], got[2][0]) and torch.equal(got[1][0], got[2][0])
+    assert torch.equal(got[1][1], got[2][1]) and torch.equal(got[1][2], got[2][2])
+    assert all(g[3] > 0 and g[4] > 0 for g in got)
+
+
+def test_step_api_pipelined_retires_streams_on_codec_eos(setup):
+    """ignore_eos=False with the run-ahead: a stream whose code0 is the codec EOS leaves without a frame although its
+    predictor burst was already queued; the survivors' frames equal the sequential loop's."""
+    from nano_qwen3tts_vllm_b200.engine.frame_loop import StepApiFrameLoop
+    from nano_qwen3tts_vllm_b200.llm import PredictorLLM, TalkerLLM
+    _, _, tw, pw = small_weights()
+    kw = dict(num_kvcache_blocks=4 * B, max_num_seqs=max(B, 2), max_model_len=512, graph_batch_sizes=[1, 2, B])
+    res, eos = [], -1
+    for piped in (None, True, False):           # None: a first run that ignores EOS, to pick a code0 that really comes up
+        talker, predictor = TalkerLLM(small_model_config(), state_dict=tw, **kw), PredictorLLM(small_model_config(), state_dict=pw, **kw)
+        talker.model_runner.top_k = predictor.model_runner.top_k = 1
+        torch.manual_seed(99)
+        api = StepApiFrameLoop(talker, predictor, setup["pad"], ignore_eos=piped is None, codec_eos=eos, batched=True,
+                               pipelined=bool(piped))
+        api.add_streams([x.unsqueeze(0).pin_memory() for x in setup["prompts"]])
+        counts = [api.step_frame() for _ in range(6)]
+        torch.cuda.synchronize()
+        if piped is None:
+            eos = api.frames["s1"][2][0]        # stream 1 retires in frame 2 (any other stream emitting it earlier too)
+        else:
+            res.append((counts, {k: list(v) for k, v in api.frames.items()}, list(api.active)))
+        api.close()
+        talker.exit(); predictor.exit()
+    assert res[0] == res[1]
+    assert min(res[0][0]) < B, "the chosen EOS code never came up: the test retired no stream"
+    for rid, fr in res[0][1].items():
+        assert all(row[0] != eos for row in fr)
