@@ -231,6 +231,10 @@ B2TTS_API int b2tts_frame_advance(const int64_t* code0, int eos_id, int32_t* act
  *                                              `rounding` as b2tts_silu_and_mul)
  * splits: K-split = cluster size (1,2,4,8,16; 0 = choose so that tiles * splits fill the SMs); the
  * partial sums are exchanged through distributed shared memory and added in a fixed order.
+ * splits = -2 / -4: the cluster splits the BATCH instead (m padded to 16 must be a multiple of 32 / 64, m <= 128):
+ * every CTA runs the whole K range for its 16 - 48 rows and each weight tile is fetched once per cluster (1 / |splits|
+ * per CTA, multicast to all) - no partial sums, no exchange.  splits = 0 never picks it unless B2TTS_GEMM_BSPLIT=1
+ * (then for K <= 1024): in the decode frame it is slower than the K split.
  * pdl != 0 launches with programmatic stream serialization: the weight stream starts while the
  * previous kernel on the stream is still running (every kernel of this library that is launched
  * this way executes griddepcontrol.wait before touching its inputs/outputs). */

@@ -71,6 +71,11 @@ struct GemmParams {
   // requested, so the next launch streams from L2.
   const uint8_t* pf_ptr;
   unsigned long long pf_bytes;
+  int bsplit;                   // > 1: the cluster splits the BATCH, not K (then splits == 1): CTA r owns rows [r * mpad, (r + 1) * mpad)
+                                // of the chunk over the whole K range, and every weight tile is fetched once per cluster - each
+                                // CTA requests 1 / bsplit of it and the copy is multicast into all of them.  No partial sums, no
+                                // exchange, a TMEM drain of mpad = 16 / 32 columns: what K <= 1024 projections want, where a
+                                // CTA's whole K range (16 k-blocks of MMA issue, ~3 us) costs less than drain + exchange.
   int nchunks;                  // M > 128: the batch is cut into ceil(M / 128) row chunks, one CTA (cluster) per
                                 // (feature tile, chunk); blockIdx.y = tile * nchunks + chunk so that the chunks of one
                                 // weight tile are launched next to each other and share it through L2
@@ -104,10 +109,13 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);       // provably warp-uniform
   const int lane = threadIdx.x & 31;
   const int S = p.splits;
-  const int rank = blockIdx.x;                  // gridDim.x == S == cluster size: rank in cluster
+  const int BS = p.bsplit;                      // batch-split cluster (then S == 1)
+  const int rank = BS > 1 ? 0 : (int)blockIdx.x;                // gridDim.x == cluster size: K-split rank ...
+  const int brank = BS > 1 ? (int)blockIdx.x : 0;               // ... or batch-split rank
+  const uint16_t bmask = (uint16_t)((1u << BS) - 1u);
   const int tile = blockIdx.y / p.nchunks;
-  const int row0 = (blockIdx.y % p.nchunks) * G_MAX_M;          // first batch row of this CTA's chunk
-  const int m_loc = min(p.m - row0, G_MAX_M);                   // rows of the chunk (the last one may be short)
+  const int row0 = (blockIdx.y % p.nchunks) * G_MAX_M + brank * mpad;    // first batch row of this CTA
+  const int m_loc = max(0, min(p.m - row0, BS > 1 ? mpad : G_MAX_M));    // its rows (the last CTA may be short, or empty)
   const int kb_begin = (int)(((int64_t)rank * p.kblocks) / S);
   const int kb_end = (int)(((int64_t)(rank + 1) * p.kblocks) / S);
   const int nkb = kb_end - kb_begin;
@@ -122,7 +130,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       // fused norm: W producer (expect_tx arrive) + the 4 x warps that transform the landed tile; otherwise the x copy
       // completes straight on this barrier (two expect_tx arrivals: W's and x's) - no relay through the x warps
       mbar_init(full_bar + s, p.norm_w ? 1 + 4 : 2);
-      mbar_init(empty_bar + s, 1);              // tcgen05.commit
+      mbar_init(empty_bar + s, BS > 1 ? BS : 1);          // tcgen05.commit (of every CTA that received the multicast tile)
       mbar_init(raw_bar + s, 1);
     }
     mbar_init(accum_bar, 1);
@@ -135,7 +143,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  if (S > 1) cluster_arrive();                  // my receive barrier is initialised (waited on before the exchange)
+  if (S > 1 || BS > 1) cluster_arrive();        // my barriers are initialised (waited on before the exchange / the first multicast)
   if (threadIdx.x == 0) G_TRACE(1);
 
   if (warp == 0) {
@@ -149,10 +157,13 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
       const uint8_t* src = p.wp + ((int64_t)tile * p.kblocks + kb_begin) * G_WTILE_BYTES;
       const uint32_t xbytes = (uint32_t)mpad * 128u;
       const int first = min(nkb, NS);
+      const uint32_t wslice = G_WTILE_BYTES / (uint32_t)BS, woff = (uint32_t)brank * wslice;
+      if (BS > 1) cluster_wait();                 // every CTA of the cluster can receive (this warp's wait; the others' is below)
       if (elect_one()) {
         for (int i = 0; i < first; ++i) {
           mbar_expect_tx(full_bar + i, G_WTILE_BYTES);
-          bulk_g2s(smem + i * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + i);
+          if (BS > 1) bulk_g2s_multicast(smem + i * stage_bytes + woff, src + (int64_t)i * G_WTILE_BYTES + woff, wslice, full_bar + i, bmask);
+          else bulk_g2s(smem + i * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + i);
         }
       }
       __syncwarp();
@@ -171,7 +182,8 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
         mbar_wait(empty_bar + stage, ph ^ 1);
         if (elect_one()) {
           mbar_expect_tx(full_bar + stage, G_WTILE_BYTES);
-          bulk_g2s(smem + stage * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + stage);
+          if (BS > 1) bulk_g2s_multicast(smem + stage * stage_bytes + woff, src + (int64_t)i * G_WTILE_BYTES + woff, wslice, full_bar + stage, bmask);
+          else bulk_g2s(smem + stage * stage_bytes, src + (int64_t)i * G_WTILE_BYTES, G_WTILE_BYTES, full_bar + stage);
           uint64_t* landed = p.norm_w ? raw_bar + stage : full_bar + stage;
           mbar_expect_tx(landed, xbytes);
           tma_load_2d(smem + stage * stage_bytes + G_WTILE_BYTES, &tmap_x, (kb_begin + i) * G_BK, row0, landed);
@@ -209,7 +221,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
           // stage reusable once these MMAs have read it - but only a k-block NS later ever waits for that: the
           // commits of the last NS k-blocks (ALL of them for the split-K decode shapes, whose K range fits the ring)
           // would be ~0.2 us of issue time each for a barrier nobody reads
-          if (i + NS < nkb) umma_commit(empty_bar + stage);
+          if (i + NS < nkb) { if (BS > 1) umma_commit_multicast(empty_bar + stage, bmask); else umma_commit(empty_bar + stage); }
           else if (i == nkb - 1) umma_commit(accum_bar);      // accumulator complete
         }
         __syncwarp();
@@ -300,7 +312,9 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   // for it, i.e. while the last MMAs are still running: the (long complete) cluster barrier that says every peer has
   // initialised its receive barrier (~0.25 us of instruction latency), and the first residual / bias vector.
   if (warp < 2) pdl_wait();                     // the epilogue below reads res / writes out
-  if (S > 1) cluster_wait();
+  if (S > 1 || (BS > 1 && warp != 0)) cluster_wait();
+  // batch split: nobody leaves while a peer may still signal one of its barriers (arrival now, wait at the very end)
+  if (BS > 1) cluster_arrive();
   const int rows_own = G_BN / S;
   const int rstride = mpad + 4;
   const int groups = rows_own >> 3;
@@ -473,6 +487,7 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
     }
   }
   if (S > 1 && !p.ssq_out) cluster_wait();      // peers' copies out of my staging area have completed
+  if (BS > 1) cluster_wait();
   __syncthreads();
   if (threadIdx.x == 0) G_TRACE(7);
   if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
@@ -538,6 +553,24 @@ static int choose_splits(int n_tiles, int kblocks, int mpad) {
   return best;
 }
 
+// Batch split instead of K split (GemmParams::bsplit): for K ranges short enough that one CTA issuing all of their MMAs
+// (~0.16 us per k-block) is cheaper than the drain + DSMEM exchange + closing barrier of a K split (~3 us).
+static int choose_bsplit(int n_tiles, int kblocks, int mpad, int nchunks) {
+  static int mode = -1, max_kb = 16;
+  if (mode < 0) {
+    // Off unless asked for: measured in the frame (64 streams) the batch split LOSES - 6.01 ms per frame against 5.26 -
+    // because one issuing thread needs ~0.2 us per k-block (0.4 us with the fused-norm hand-over), so a CTA's 16 k-blocks
+    // of K = 1024 take 6.4 us where 4 k-blocks + drain + exchange take 4.5 us.
+    const char* e = getenv("B2TTS_GEMM_BSPLIT");
+    mode = e ? atoi(e) : 0;
+    if (const char* k = getenv("B2TTS_GEMM_BSPLIT_MAX_KB")) max_kb = atoi(k);
+  }
+  if (!mode || nchunks != 1 || kblocks > max_kb || kblocks < 2) return 1;
+  for (int bs : {4, 2})
+    if (mpad % (16 * bs) == 0 && n_tiles * bs <= 2 * sm_count()) return bs;
+  return 1;
+}
+
 template <int NCH>
 static int launch_gemm(const GemmParams& p, const CUtensorMap& tmap, cudaStream_t st, int pdl) {
   static bool configured = false;
@@ -549,15 +582,16 @@ static int launch_gemm(const GemmParams& p, const CUtensorMap& tmap, cudaStream_
     configured = true;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(p.splits, (p.n / G_BN) * p.nchunks, 1);
+  const int cluster = p.bsplit > 1 ? p.bsplit : p.splits;
+  cfg.gridDim = dim3(cluster, (p.n / G_BN) * p.nchunks, 1);
   cfg.blockDim = dim3(G_THREADS, 1, 1);
   cfg.dynamicSmemBytes = gemm_smem_bytes(p.mpad, p.stages, p.splits);
   cfg.stream = st;
   cudaLaunchAttribute attrs[2];
   int na = 0;
-  if (p.splits > 1) {
+  if (cluster > 1) {
     attrs[na].id = cudaLaunchAttributeClusterDimension;
-    attrs[na].val.clusterDim.x = p.splits;
+    attrs[na].val.clusterDim.x = cluster;
     attrs[na].val.clusterDim.y = 1;
     attrs[na].val.clusterDim.z = 1;
     ++na;
@@ -677,11 +711,31 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
   p.kblocks = k / G_BK;
   p.epilogue = epilogue;
   p.rounding = rounding;
-  int s = splits > 0 ? splits : choose_splits((n / G_BN) * p.nchunks, p.kblocks, p.mpad);
+  // splits < 0: a batch split of -splits CTAs (see GemmParams::bsplit); 0: chosen here
+  int bs = 1;
+  if (splits < 0) {
+    bs = -splits;
+    B2_REQUIRE((bs == 2 || bs == 4) && p.nchunks == 1 && p.mpad % (16 * bs) == 0, B2TTS_EINVAL,
+               "%s: batch split %d needs 2 or 4 and a padded batch (%d rows) that is a multiple of %d", what, bs, p.mpad, 16 * bs);
+  } else if (splits == 0) {
+    bs = choose_bsplit((n / G_BN), p.kblocks, p.mpad, p.nchunks);
+  }
+  int s = bs > 1 ? 1 : (splits > 0 ? splits : choose_splits((n / G_BN) * p.nchunks, p.kblocks, p.mpad));
   B2_REQUIRE((s == 1 || s == 2 || s == 4 || s == 8 || s == 16) && s <= p.kblocks, B2TTS_EINVAL,
              "%s: splits %d must be 1,2,4,8,16 and <= k/64", what, s);
   p.splits = s;
-  p.stages = choose_stages(p.mpad, s);
+  p.bsplit = bs;
+  if (bs > 1) {
+    p.mpad /= bs;                                 // rows per CTA: 16 or 32
+    // the deepest ring that still lets two CTAs share an SM, at most the whole K range
+    int st = G_MAX_STAGES;
+    static int deep = -1;
+    if (deep < 0) { const char* e = getenv("B2TTS_GEMM_BSPLIT_DEEP"); deep = e ? atoi(e) : 0; }     // experiments: one CTA per SM
+    while (st > 2 && gemm_smem_bytes(p.mpad, st, 1) > (deep ? 227 : 113) * 1024) --st;
+    p.stages = st < p.kblocks ? st : (p.kblocks < 2 ? 2 : p.kblocks);
+  } else {
+    p.stages = choose_stages(p.mpad, s);
+  }
   B2_REQUIRE(p.stages >= 2, B2TTS_EUNSUPPORTED, "%s: no shared-memory plan for m=%d", what, m);
   p.tmem_cols = 32;
   while (p.tmem_cols < p.mpad) p.tmem_cols <<= 1;

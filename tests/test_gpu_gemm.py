@@ -273,3 +273,63 @@ def test_gemm_prefetch_next_weights_changes_nothing(native):
     assert torch.equal(native.gemm_bf16(x, pk, n, prefetch=nxt), y)
     with pytest.raises(RuntimeError):
         native.gemm_bf16(x, pk, n, prefetch=nxt.view(-1)[8:8 + 16384])        # not 16-byte aligned
+
+
+# ------------------------------------------------------------------ batch split (splits < 0): W multicast, no K split
+@pytest.mark.parametrize("m,bs", [(64, 4), (50, 4), (32, 2), (17, 2), (128, 4), (96, 2), (64, 2)])
+@pytest.mark.parametrize("n,k", [(4096, 1024), (2048, 1024), (1024, 2048), (256, 128), (128, 64)])
+def test_gemm_batch_split_plain_bias_residual(native, m, bs, n, k):
+    """The cluster splits the batch (each CTA: 16 - 48 rows x the whole K, weight tiles multicast): one fp32 accumulator
+    over K in order, so against fp64 it obeys the same bound as the K-split kernel; run-to-run identical."""
+    g = torch.Generator(device="cuda").manual_seed(m * 13 + n + k + bs)
+    x = torch.randn(m, k, device="cuda", generator=g).to(BF16)
+    w = (torch.randn(n, k, device="cuda", generator=g) * 0.05).to(BF16)
+    b = torch.randn(n, device="cuda", generator=g).to(BF16)
+    res = torch.randn(m, n, device="cuda", generator=g).to(BF16)
+    packed = native.gemm_pack_weight(w)
+    y = native.gemm_bf16(x, packed, n, splits=-bs)
+    _check(y, _ref_linear(x, w), f"batch-split gemm m={m} n={n} k={k} bs={bs}")
+    assert torch.equal(y, native.gemm_bf16(x, packed, n, splits=-bs, pdl=True))
+    _check(native.gemm_bf16(x, packed, n, bias=b, splits=-bs), _ref_linear(x, w, b), "batch-split gemm + bias")
+    # residual epilogue: bf16(res + bf16(acc)); identical to the K-split kernel's wherever bf16(acc) is
+    yr = native.gemm_bf16(x, packed, n, residual=res, epilogue=native.GEMM_RESIDUAL, splits=-bs)
+    want = (res.float() + _ref_linear(x, w).to(BF16).float()).to(BF16)
+    assert ((yr.float() - want.float()).abs() > 0).float().mean().item() < 5e-3
+    ssq = torch.full((m, native.gemm_ssq_slots(m, n, k)), float("nan"), device="cuda")
+    yr2 = native.gemm_bf16(x, packed, n, residual=res, epilogue=native.GEMM_RESIDUAL, splits=-bs, ssq_out=ssq)
+    assert torch.equal(yr, yr2)
+    torch.testing.assert_close(ssq.sum(1), yr.float().pow(2).sum(1), rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("m,bs", [(64, 4), (40 + 24, 4), (32, 2), (128, 4), (20, 2)])
+@pytest.mark.parametrize("rounding", [0, 1])
+def test_gemm_batch_split_fused_norm_and_silu_mul(native, m, bs, rounding):
+    """Fused input RMSNorm (ssq_in) and the SiLU*mul epilogue in batch-split mode against the separate kernels."""
+    h, inter, eps = 1024, 3072, 1e-6
+    g = torch.Generator(device="cuda").manual_seed(m + 7 * rounding + bs)
+    x = torch.randn(m, h, device="cuda", generator=g).to(BF16)
+    nw = (1 + 0.1 * torch.randn(h, device="cuda", generator=g)).to(BF16)
+    w = (torch.randn(2 * inter, h, device="cuda", generator=g) * 0.03).to(BF16)
+    wq = (torch.randn(4096, h, device="cuda", generator=g) * 0.03).to(BF16)
+    pk, pq = native.gemm_pack_weight(w, native.PACK_GATE_UP), native.gemm_pack_weight(wq)
+    ssq = x.float().pow(2).view(m, 8, -1).sum(2).contiguous()
+    normed = native.rmsnorm(x, nw, eps, rounding)
+    for packed, n, epi in ((pk, 2 * inter, native.GEMM_SILU_MUL), (pq, 4096, native.GEMM_BIAS)):
+        y = native.gemm_bf16(x, packed, n, epilogue=epi, rounding=rounding, norm_weight=nw, ssq_in=ssq, eps=eps, splits=-bs)
+        want = native.gemm_bf16(normed, packed, n, epilogue=epi, rounding=rounding, splits=-bs)
+        diff = (y.float() - want.float()).abs()
+        assert diff.max().item() <= 2e-2 * want.float().abs().max().item()
+        assert (diff > 0).float().mean().item() < 0.02
+        ksplit = native.gemm_bf16(normed, packed, n, epilogue=epi, rounding=rounding, splits=4)
+        d2 = (want.float() - ksplit.float()).abs()
+        assert d2.max().item() <= 2e-2 * ksplit.float().abs().max().item()
+        assert torch.equal(y, native.gemm_bf16(x, packed, n, epilogue=epi, rounding=rounding, norm_weight=nw, ssq_in=ssq,
+                                               eps=eps, splits=-bs, pdl=True))
+
+
+def test_gemm_batch_split_argument_errors(native):
+    x = torch.zeros(40, 1024, device="cuda", dtype=BF16)
+    w = native.gemm_pack_weight(torch.zeros(128, 1024, device="cuda", dtype=BF16))
+    for bad in (-4, -2, -3, -8):            # 40 rows pad to 48: not a multiple of 32 / 64; 3 and 8 are not cluster sizes
+        with pytest.raises(RuntimeError):
+            native.gemm_bf16(x, w, 128, splits=bad)
