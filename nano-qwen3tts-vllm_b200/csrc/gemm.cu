@@ -76,6 +76,7 @@ struct GemmParams {
                                 // CTA requests 1 / bsplit of it and the copy is multicast into all of them.  No partial sums, no
                                 // exchange, a TMEM drain of mpad = 16 / 32 columns: what K <= 1024 projections want, where a
                                 // CTA's whole K range (16 k-blocks of MMA issue, ~3 us) costs less than drain + exchange.
+  int chunk_rows;               // rows per chunk when the batch is cut (<= G_MAX_M)
   int nchunks;                  // M > 128: the batch is cut into ceil(M / 128) row chunks, one CTA (cluster) per
                                 // (feature tile, chunk); blockIdx.y = tile * nchunks + chunk so that the chunks of one
                                 // weight tile are launched next to each other and share it through L2
@@ -114,8 +115,8 @@ gemm_stream_kernel(const GemmParams p, const __grid_constant__ CUtensorMap tmap_
   const int brank = BS > 1 ? (int)blockIdx.x : 0;               // ... or batch-split rank
   const uint16_t bmask = (uint16_t)((1u << BS) - 1u);
   const int tile = blockIdx.y / p.nchunks;
-  const int row0 = (blockIdx.y % p.nchunks) * G_MAX_M + brank * mpad;    // first batch row of this CTA
-  const int m_loc = max(0, min(p.m - row0, BS > 1 ? mpad : G_MAX_M));    // its rows (the last CTA may be short, or empty)
+  const int row0 = (blockIdx.y % p.nchunks) * p.chunk_rows + brank * mpad;   // first batch row of this CTA
+  const int m_loc = max(0, min(p.m - row0, BS > 1 ? mpad : p.chunk_rows));   // its rows (the last CTA may be short, or empty)
   const int kb_begin = (int)(((int64_t)rank * p.kblocks) / S);
   const int kb_end = (int)(((int64_t)(rank + 1) * p.kblocks) / S);
   const int nkb = kb_end - kb_begin;
@@ -706,8 +707,19 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
   p.out = static_cast<__nv_bfloat16*>(out);
   p.out_stride = out_row_stride;
   p.m = m; p.n = n; p.k = k;
-  p.nchunks = (m + G_MAX_M - 1) / G_MAX_M;
-  p.mpad = p.nchunks > 1 ? G_MAX_M : (m + 15) & ~15;
+  // batches above the chunk size are cut into row chunks (one cluster per (feature tile, chunk)).  The per-CTA costs that
+  // grow with the rows - x tile, in-place norm transform, TMEM drain, split-K exchange - make 64-row chunks the better cut
+  // (B2TTS_GEMM_CHUNK_ROWS overrides: 16 .. 128, a multiple of 16)
+  static int chunk_cfg = -1;
+  if (chunk_cfg < 0) {
+    const char* e = getenv("B2TTS_GEMM_CHUNK_ROWS");
+    chunk_cfg = e ? atoi(e) : 64;                 // measured: 128 streams 7.81 -> 6.39 ms per frame, 256: 10.3 -> 8.7, 64: 5.24 -> 5.20
+    if (chunk_cfg < 16 || chunk_cfg > G_MAX_M || chunk_cfg % 16) chunk_cfg = G_MAX_M;
+  }
+  p.chunk_rows = (splits >= 0 && m > chunk_cfg) ? chunk_cfg : G_MAX_M;      // an explicit batch split takes the whole batch
+  p.nchunks = (m + p.chunk_rows - 1) / p.chunk_rows;
+  B2_REQUIRE((int64_t)(n / G_BN) * p.nchunks <= 65535, B2TTS_EUNSUPPORTED, "%s: m=%d n=%d: too many tiles", what, m, n);
+  p.mpad = p.nchunks > 1 ? p.chunk_rows : (m + 15) & ~15;
   p.kblocks = k / G_BK;
   p.epilogue = epilogue;
   p.rounding = rounding;
@@ -781,9 +793,7 @@ extern "C" int b2tts_gemm_bf16(const void* x, int64_t x_row_stride, const void* 
 
 extern "C" int b2tts_gemm_ssq_slots(int m, int n, int k, int splits) {
   if (n <= 0 || k <= 0 || n % b2::G_BN || k % b2::G_BK) return 0;
-  const int nchunks = (m + b2::G_MAX_M - 1) / b2::G_MAX_M;
-  const int mpad = nchunks > 1 ? b2::G_MAX_M : (m + 15) & ~15;
-  (void)m; (void)splits;                        // one slot per 128-feature tile, whatever the K split
+  (void)m; (void)splits;                        // one slot per 128-feature tile, whatever the K split or the row chunks
   return n / b2::G_BN;
 }
 

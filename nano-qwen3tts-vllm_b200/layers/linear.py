@@ -5,8 +5,8 @@ and no collective follows any GEMM.
 ``linear()`` is the one GEMM entry of the hot path: y[M,N] = x[M,K] @ W[N,K]^T (+ b).  In decode
 M is the number of streams, so the GEMM streams W once from HBM: the hand-written sm_100a kernel
 (``b2tts_gemm_bf16``: weights as the 128-row tcgen05 operand, the batch as the N tile, accumulators
-in TMEM).  Larger row counts (decode batches above 128 streams, the predictor's 2-token prefill) run the
-same kernel over 128-row chunks of x with the same fused epilogues; the chunks of one weight tile are
+in TMEM).  Larger row counts (decode batches above 64 streams, the predictor's 2-token prefill) run the
+same kernel over 64-row chunks of x with the same fused epilogues; the chunks of one weight tile are
 launched next to each other and share it through L2.  Beyond ``GEMM_NATIVE_MAX_M`` rows (long prompt
 prefills) the product is compute-bound and goes to the plain library GEMM
 (``torch.nn.functional.linear`` = cuBLAS), as it does for shapes the kernel cannot tile
