@@ -37,6 +37,10 @@ FUSED_DECODE_ATTENTION = True     # False: separate qknorm_rope_kvwrite + paged_
 GEMM_CHAIN = False                # decode: the 4 projections between two attention calls as ONE persistent launch
 # experiments: RMSNorms applied by a separate launch instead of inside the consuming GEMM ("gate_up", "qkv", "gate_up,qkv")
 UNFUSED_NORMS = os.environ.get("B2TTS_UNFUSED_NORMS", "")
+# rows up to which the RMSNorms ride inside the consuming GEMM; above, the per-k-block hand-over of the in-place transform
+# costs more than a separate launch (measured per frame: 128 streams 6.36 fused / 6.69 separate, 256: 8.68 / 8.20,
+# 512: 12.4 / 10.95)
+FUSED_NORM_MAX_ROWS = int(os.environ.get("B2TTS_FUSED_NORM_MAX_ROWS", "192"))
 # decode of a small stack (the code predictor) as ONE persistent dataflow launch (csrc/decoder_stack.cu).  Opt-in:
 # bit-identical to the separate launches, but measured at 260 us per 5-layer pass against their 246 us at 64 rows
 # (every hand-over between phases costs a gpu-scope release + an L2 poll, ~2.5 us, 7 per layer)
@@ -148,7 +152,8 @@ class Qwen3TTSDecoderLayer(nn.Module):
         ``in_place`` False keeps the caller's tensor (the first layer's input embeddings) intact.
         ``nxt``: the weight the GEMM after this layer streams (the next layer's qkv_proj, or the LM head): every GEMM
         here pulls its successor's weights into L2 while it runs.  Returns (residual, ssq)."""
-        if ssq is None or "qkv" in UNFUSED_NORMS:
+        wide = residual.shape[0] > FUSED_NORM_MAX_ROWS
+        if ssq is None or wide or "qkv" in UNFUSED_NORMS:
             h = nat.rmsnorm(residual, self.input_layernorm.weight, self.eps, self.rounding)
             o = self.self_attn.attend(positions, h)
         else:
@@ -156,7 +161,7 @@ class Qwen3TTSDecoderLayer(nn.Module):
                                       RowNorm(self.input_layernorm.weight, ssq, self.eps, self.rounding))
         residual, ssq = linear_residual(o, self.self_attn.o_proj.weight, residual, out=residual if in_place else None,
                                         want_ssq=True, nxt=(self.mlp.gate_up_proj.weight, nat.PACK_GATE_UP))
-        if "gate_up" in UNFUSED_NORMS:
+        if wide or "gate_up" in UNFUSED_NORMS:
             h = nat.rmsnorm(residual, self.post_attention_layernorm.weight, self.eps, self.rounding)
             act = linear_silu_mul(h, self.mlp.gate_up_proj.weight, self.rounding, nxt=self.mlp.down_proj.weight)
         else:
