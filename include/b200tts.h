@@ -82,6 +82,23 @@ B2TTS_API int b2tts_paged_attn_decode(const void* q, int64_t q_row_stride,
                             int batch, int num_heads, int num_kv_heads, int head_dim,
                             int page_size, float scale, int max_ctx, void* stream);
 
+/* The same operation with the split-KV partial sums in a file-scope device array inside the library instead of a
+ * caller-provided workspace: the call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine), for
+ * callers that cannot allocate - code under CUDA-graph capture, tight serving loops, harnesses that forbid it.
+ * NO COUNTERPART IN THE REFERENCE.
+ * Limit: the array holds b2tts_paged_attn_decode_static_max_bytes() = 8 MiB, held by every GPU that loads the library until
+ * the process exits; shapes whose b2tts_paged_attn_decode_workspace_bytes(...) exceeds it are rejected with
+ * B2TTS_EWORKSPACE (use b2tts_paged_attn_decode with your own workspace).  All calls share the array, which keeps the last
+ * call's contents (nothing in it needs clearing: every partial is written before it is read): calls that can overlap on
+ * the GPU - different streams, parallel graph branches - race on it.  Arguments and results as b2tts_paged_attn_decode. */
+B2TTS_API size_t b2tts_paged_attn_decode_static_max_bytes(void);
+B2TTS_API int b2tts_paged_attn_decode_static(const void* q, int64_t q_row_stride,
+                            const void* k_cache, const void* v_cache,
+                            const int32_t* block_table, int bt_stride,
+                            const int32_t* context_lens, void* out,
+                            int batch, int num_heads, int num_kv_heads, int head_dim,
+                            int page_size, float scale, int max_ctx, void* stream);
+
 /* ---- a3: varlen causal prefill attention ----------------------------------------------
  * replaces flash_attn_varlen_func(q, k, v, cu_seqlens_q/k, max_seqlen_q/k, softmax_scale,
  *          causal=True, block_table)                       layers/attention.py:78-91

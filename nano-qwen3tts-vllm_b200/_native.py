@@ -48,6 +48,8 @@ def _load():
         "b2tts_store_kvcache": (I, [P, P, L, L, P, P, P, I, I, P]),
         "b2tts_paged_attn_decode_workspace_bytes": (Z, [I, I, I, I]),
         "b2tts_paged_attn_decode": (I, [P, L, P, P, P, I, P, P, P, Z, I, I, I, I, I, F, I, P]),
+        "b2tts_paged_attn_decode_static_max_bytes": (Z, []),
+        "b2tts_paged_attn_decode_static": (I, [P, L, P, P, P, I, P, P, I, I, I, I, I, F, I, P]),
         "b2tts_varlen_attn_prefill": (I, [P, L, P, L, P, L, P, P, P, I, I, I, I, I, I, I, I, F, P, I, I, P]),
         "b2tts_rmsnorm": (I, [P, L, P, P, I, I, F, I, P]),
         "b2tts_add_rmsnorm": (I, [P, P, P, P, P, I, I, F, I, I, P]),
@@ -158,6 +160,20 @@ def paged_attn_decode(q, k_cache, v_cache, block_table, context_lens, scale, max
                                            block_table.data_ptr(), block_table.stride(0), context_lens.data_ptr(),
                                            out.data_ptr(), _ptr(workspace), wbytes, b, h, kvh, hd, page,
                                            float(scale), int(max_ctx), _stream()), "paged_attn_decode")
+    return out
+
+
+def paged_attn_decode_static(q, k_cache, v_cache, block_table, context_lens, scale, max_ctx, out):
+    """``paged_attn_decode`` with the split-KV scratch in the library's own device array: the CALL allocates nothing,
+    so ``out`` is required.  Shapes that need more than ``b2tts_paged_attn_decode_static_max_bytes()`` raise."""
+    _cuda(q, BF16, "q"); _cuda(k_cache, BF16, "k_cache"); _cuda(v_cache, BF16, "v_cache")
+    _cuda(block_table, I32, "block_table"); _cuda(context_lens, I32, "context_lens"); _cuda(out, BF16, "out")
+    b, h, hd = q.shape
+    page, kvh = k_cache.shape[1], k_cache.shape[2]
+    _check(_load().b2tts_paged_attn_decode_static(q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
+                                                  block_table.data_ptr(), block_table.stride(0), context_lens.data_ptr(),
+                                                  out.data_ptr(), b, h, kvh, hd, page, float(scale), int(max_ctx),
+                                                  _stream()), "paged_attn_decode_static")
     return out
 
 

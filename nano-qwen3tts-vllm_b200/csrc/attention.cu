@@ -504,3 +504,49 @@ extern "C" int b2tts_varlen_attn_prefill(const void* q, int64_t q_row_stride,
   p.scale_log2 = scale * 1.4426950408889634f;
   return launch_attn<true>(p, total_q, static_cast<cudaStream_t>(stream), what);
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// b2tts_paged_attn_decode_static: the same launch(es) as b2tts_paged_attn_decode with the split-KV partials in a
+// file-scope device array instead of a caller-provided workspace, for callers that cannot allocate (code under CUDA-graph
+// capture, serving loops and harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Every GPU that loads the library holds the 8 MiB until the process exits.  All calls share
+// the array: two calls that can overlap on the GPU (different streams, or graph branches) race on it.  Nothing in it has
+// to start at zero - every (row, split, head) partial, empty splits included, is written before the combine reads it.
+namespace b2 {
+constexpr size_t ATT_STATIC_SCRATCH_BYTES = 8u << 20;
+static __device__ __align__(256) unsigned char g_attn_static_scratch[ATT_STATIC_SCRATCH_BYTES];
+constexpr int ATT_STATIC_MAX_DEVICES = 64;
+static void* g_attn_static_ptr[ATT_STATIC_MAX_DEVICES];       // device address of the array, per device (host code only
+                                                               // knows the symbol: the address is asked for once per device)
+}  // namespace b2
+
+extern "C" size_t b2tts_paged_attn_decode_static_max_bytes(void) { return b2::ATT_STATIC_SCRATCH_BYTES; }
+
+extern "C" int b2tts_paged_attn_decode_static(const void* q, int64_t q_row_stride,
+                                              const void* k_cache, const void* v_cache,
+                                              const int32_t* block_table, int bt_stride,
+                                              const int32_t* context_lens, void* out,
+                                              int batch, int num_heads, int num_kv_heads, int head_dim,
+                                              int page_size, float scale, int max_ctx, void* stream) {
+  using namespace b2;
+  const char* what = "paged_attn_decode_static";
+  const size_t need = b2tts_paged_attn_decode_workspace_bytes(batch, num_heads, head_dim, max_ctx);
+  B2_REQUIRE(need <= ATT_STATIC_SCRATCH_BYTES, B2TTS_EWORKSPACE,
+             "%s: batch=%d heads=%d max_ctx=%d needs %zu B of split-KV scratch, the built-in array holds %zu B; "
+             "use b2tts_paged_attn_decode with a workspace of your own", what, batch, num_heads, max_ctx, need,
+             (size_t)ATT_STATIC_SCRATCH_BYTES);
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, what);
+  B2_REQUIRE(dev >= 0 && dev < ATT_STATIC_MAX_DEVICES, B2TTS_EUNSUPPORTED, "%s: device ordinal %d", what, dev);
+  void* scratch = g_attn_static_ptr[dev];
+  if (!scratch) {                                 // set-up, once per device, with that device current
+    e = cudaGetSymbolAddress(&scratch, g_attn_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "paged_attn_decode_static(cudaGetSymbolAddress)");
+    B2_REQUIRE(scratch && aligned16(scratch), B2TTS_ECUDA, "%s: scratch symbol has no usable device address", what);
+    g_attn_static_ptr[dev] = scratch;
+  }
+  return b2tts_paged_attn_decode(q, q_row_stride, k_cache, v_cache, block_table, bt_stride, context_lens, out, scratch,
+                                 ATT_STATIC_SCRATCH_BYTES, batch, num_heads, num_kv_heads, head_dim, page_size, scale,
+                                 max_ctx, stream);
+}
