@@ -15,8 +15,8 @@ namespace b2 {
 constexpr int SMP_THREADS = 256;
 constexpr int SMP_MAXV = 16384;
 
-__device__ __forceinline__ uint32_t f2key(float f) {       // larger float -> larger key
-  const uint32_t u = __float_as_uint(f);
+__device__ __forceinline__ uint32_t f2key(float f) {       // larger float -> larger key; -0.0 and +0.0 share one key,
+  const uint32_t u = __float_as_uint(f + 0.0f);            // as they compare equal in torch.topk and in `l < kth`
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 __device__ __forceinline__ float key2f(uint32_t k) {
@@ -203,6 +203,9 @@ topk_sample_row_kernel(const RowSampleParams p) {
   pdl_wait();                                         // logits come from the previous kernel on the stream
   const float T = __ldg(p.temperatures + row);
   uint32_t key[NCH * 8];
+  uint32_t k16[FP32_IN ? 1 : NCH * 8];                // bf16 input: the 16-bit order keys of the logits (0 = padding)
+#pragma unroll
+  for (int j = 0; j < (FP32_IN ? 1 : NCH * 8); ++j) k16[j] = 0u;
   // ---- l = float(logit) / T as keys                                      sampler.py:16
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
@@ -217,6 +220,8 @@ topk_sample_row_kernel(const RowSampleParams p) {
         const uint4 r = ldg_v4(static_cast<const __nv_bfloat16*>(p.logits) + (int64_t)row * p.row_stride + i0);
         x[0] = bf16lo(r.x); x[1] = bf16hi(r.x); x[2] = bf16lo(r.y); x[3] = bf16hi(r.y);
         x[4] = bf16lo(r.z); x[5] = bf16hi(r.z); x[6] = bf16lo(r.w); x[7] = bf16hi(r.w);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) k16[c * 8 + e] = f2key(x[e]) >> 16;      // order key of the bf16 logit itself
       }
 #pragma unroll
       for (int e = 0; e < 8; ++e) key[c * 8 + e] = f2key(__fdiv_rn(x[e], T));    // IEEE division (no fast-math)
@@ -237,7 +242,55 @@ topk_sample_row_kernel(const RowSampleParams p) {
 
   // ---- kth = topk(l, k).values[:, -1]                                     sampler.py:18-19
   uint32_t kth = 1u;                                   // top_k >= vocab: only the padding keys (0) are masked
-  if (p.top_k < p.vocab) {
+  if (!FP32_IN && T > 0.f && p.top_k < p.vocab) {
+    // bf16 logits and T > 0: l = x / T is non-decreasing in x, so the k-th largest l is (k-th largest x) / T, and x has
+    // only 16 bits: radix select over the bf16 order keys, TWO bits per round (the counts for digits 1..3 packed in one
+    // word: one redux, one shared-memory word per warp, one block barrier) = 8 rounds instead of 32
+    uint32_t prefix = 0u;
+    int above = p.vocab, buf = 0;
+    for (int shift = 14; shift >= 0 && above != p.top_k; shift -= 2) {
+      uint32_t pk = 0u;
+#pragma unroll
+      for (int d = 1; d < 4; ++d) {
+        const uint32_t cand = prefix | ((uint32_t)d << shift);
+        uint32_t cnt = 0u;
+#pragma unroll
+        for (int j = 0; j < NCH * 8; ++j) cnt += k16[j] >= cand ? 1u : 0u;
+        pk |= cnt << (10 * (d - 1));                   // a warp's field sum <= 32 * 16 = 512: 10 bits
+      }
+      pk = __reduce_add_sync(0xffffffffu, pk);
+      if (lane == 0) red_cnt[buf][warp] = (int)pk;
+      __syncthreads();
+      int tot[3] = {0, 0, 0};
+#pragma unroll
+      for (int w = 0; w < RS_WARPS; ++w) {
+        const uint32_t v = (uint32_t)red_cnt[buf][w];
+        tot[0] += (int)(v & 0x3ffu); tot[1] += (int)((v >> 10) & 0x3ffu); tot[2] += (int)((v >> 20) & 0x3ffu);
+      }
+      buf ^= 1;
+#pragma unroll
+      for (int d = 3; d >= 1; --d)
+        if (tot[d - 1] >= p.top_k) { prefix |= (uint32_t)d << shift; above = tot[d - 1]; break; }
+    }
+    uint32_t kx = prefix;                              // all 16 bits decided: ties straddle the k-th place
+    if (above == p.top_k) {                            // exactly k logits at or above the prefix: their minimum
+      uint32_t kmin = 0xffffu;
+#pragma unroll
+      for (int j = 0; j < NCH * 8; ++j) if (k16[j] >= prefix) kmin = min(kmin, k16[j]);
+      kmin = __reduce_min_sync(0xffffffffu, kmin);
+      __syncthreads();                                 // red_key was read for the maximum above
+      if (lane == 0) red_key[warp] = kmin;
+      __syncthreads();
+#pragma unroll
+      for (int w = 0; w < RS_WARPS; ++w) kmin = min(kmin, red_key[w]);
+      kx = kmin;
+    }
+    // back to the bf16 value (negative values carry ones in the dropped low half of their key), then the same division
+    // the keys went through
+    const uint32_t kfull = (kx << 16) | ((kx & 0x8000u) ? 0u : 0xffffu);
+    kth = f2key(__fdiv_rn(key2f(kfull), T));
+    if (kth == 0u) kth = 1u;
+  } else if (p.top_k < p.vocab) {
     uint32_t prefix = 0u;
     int above = p.vocab, buf = 0;                      // keys >= prefix
     for (int bit = 31; bit >= 0 && above != p.top_k; --bit) {

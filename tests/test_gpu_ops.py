@@ -215,6 +215,28 @@ def test_sampler_warp_and_block_paths_with_fused_embedding(native, b, vsz, top_k
         assert torch.equal(dst[:, 1], table[idx]) and dst[:, 0].abs().max().item() == 0
 
 
+def test_sampler_bf16_select_negative_thresholds_and_padding(native):
+    """bf16 logits go through a 16-bit radix select in logit space (k-th largest x, then x / T): thresholds that are
+    negative, rows of all-equal values, -inf entries, k close to the vocabulary and a vocabulary that does not fill the
+    last chunk of a thread block."""
+    g = torch.Generator().manual_seed(77)
+    for vsz, top_k in ((2048, 50), (2048, 2000), (1000, 50), (3072, 3071), (4096, 2)):
+        b = 9
+        logits = (torch.randn(b, vsz, generator=g) * 2 - 30).to(BF16)          # every threshold negative
+        logits[1] = -7.25                                                       # one value everywhere
+        logits[2, ::3] = float("-inf")
+        logits[3] = (torch.randn(vsz, generator=g) * 1e-3).to(BF16)            # thresholds around +-0
+        logits[4, : vsz // 2] = 0.0
+        logits[4, vsz // 2:] = -0.0
+        temps = torch.rand(b, generator=g) * 3 + 0.05
+        noise = torch.empty(b, vsz).exponential_(1, generator=g)
+        want = O.topk_sample(logits, temps, noise, min(top_k, vsz))
+        got = native.topk_sample(logits.to(DEV), temps.to(DEV), noise.to(DEV), top_k)
+        assert torch.equal(got.cpu(), want), (vsz, top_k)
+        got32 = native.topk_sample(logits.float().to(DEV), temps.to(DEV), noise.to(DEV), top_k)
+        assert torch.equal(got32.cpu(), want), (vsz, top_k)
+
+
 # ------------------------------------------------------------------------------------------ a2
 def _paged_case(b, lens, page=256, kvh=8, h=16, hd=128, seed=0, extra_pages=2):
     g = torch.Generator().manual_seed(seed)
