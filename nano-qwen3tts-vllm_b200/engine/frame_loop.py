@@ -225,9 +225,9 @@ class DeviceFrameLoop:
             lay = self.p_dec[g - 1]
             set_context(False, slot_mapping=lay["slots"], context_lens=lay["ctx"], block_tables=self.p_tables,
                         max_context_len=g + 2)           # exact: no split-KV, no combine launch
-            h = predictor(self.p_emb, lay["pos"], head=g)   # p_emb = codec_embedding[g-1][code g], left by the sampler
             nxt = qkv0 if g + 1 < self.ncb - 1 else talker.model.layers[0].self_attn.qkv_proj.weight
-            self._sample(linear(h, predictor.lm_head[g], nxt=nxt), self.p_temp, g + 1)
+            # p_emb = codec_embedding[g-1][code g], left by the sampler
+            self._sample(predictor.decode_logits(self.p_emb, lay["pos"], g, nxt=nxt), self.p_temp, g + 1)
         # ---- emit the frame, build the next talker input                       interface.py:1269-1286
         self.codes.copy_(self.codes_t.t())
         self.frames.index_copy_(0, self.frame_idx, self.codes.unsqueeze(0))

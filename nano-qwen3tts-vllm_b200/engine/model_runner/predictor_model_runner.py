@@ -83,9 +83,9 @@ class PredictorModelRunner(ModelRunner):
         for g in range(1, n):
             set_context(False, slot_mapping=slots_all[g], context_lens=ctx_all[g], block_tables=tables,
                         max_context_len=g + 2)
-            h = model(self.burst_emb[:bs], self.burst_posg[g][:bs], head=g)
             last_pass = g == n - 1
-            nat.topk_sample(linear(h, model.lm_head[g], nxt=None if last_pass else qkv0), temps, noise[g], top_k=self.top_k,
+            logits = model.decode_logits(self.burst_emb[:bs], self.burst_posg[g][:bs], g, nxt=None if last_pass else qkv0)
+            nat.topk_sample(logits, temps, noise[g], top_k=self.top_k,
                             out=codes[g], embed_table=None if last_pass else model.model.codec_embedding[g],
                             embed_out=None if last_pass else self.burst_emb[:bs])
         reset_context()

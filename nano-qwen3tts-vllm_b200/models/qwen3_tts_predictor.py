@@ -91,6 +91,22 @@ class Qwen3TTSCodePredictorForCausalLM(nn.Module):
                 inputs_embeds = proj(inputs_embeds)
         return self.model(inputs_embeds, positions, ssq, tail)
 
+    def decode_logits(self, inputs_embeds: torch.Tensor, positions: torch.Tensor, head: int, nxt=None) -> torch.Tensor:
+        """One decode pass + LM head ``head`` (one row per sequence): logits [n, vocab].  The stack's final RMSNorm rides
+        inside the head GEMM (its input rows are normalised while they are staged) instead of being a launch of its own;
+        batches that do not take the fused path get ``forward`` + ``linear``: same rounding points either way."""
+        proj, ssq = self.small_to_mtp_projection, None
+        x = inputs_embeds
+        if proj is not None:
+            x2 = x.reshape(-1, x.shape[-1])
+            if not native_ok(x2.shape[0], proj.weight.shape[0], x2.shape[1]):
+                return linear(self.forward(inputs_embeds, positions, head=head), self.lm_head[head], nxt=nxt)
+            x, ssq = linear(x2, proj.weight, proj.bias, want_ssq=True, nxt=self.model.layers[0].self_attn.qkv_proj.weight)
+        raw = self.model.run_layers_unnormed(x, positions, ssq, self.lm_head[head])
+        if raw is None:
+            return linear(self.model(x, positions, ssq, self.lm_head[head]), self.lm_head[head], nxt=nxt)
+        return linear(raw[0], self.lm_head[head], norm=raw[1], nxt=nxt)
+
     def compute_logits(self, hidden_states: torch.Tensor, generation_steps: list[int]) -> torch.Tensor:
         """hidden_states [num_seqs * len, H] -> logits of the LAST position of every sequence through
         head ``generation_steps[i]`` (all sequences have equal length, predictor.py:118,124)."""

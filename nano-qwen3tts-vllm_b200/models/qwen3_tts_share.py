@@ -40,6 +40,7 @@ UNFUSED_NORMS = os.environ.get("B2TTS_UNFUSED_NORMS", "")
 # rows up to which the RMSNorms ride inside the consuming GEMM; above, the per-k-block hand-over of the in-place transform
 # costs more than a separate launch (measured per frame: 128 streams 6.36 fused / 6.69 separate, 256: 8.68 / 8.20,
 # 512: 12.4 / 10.95)
+FINAL_NORM_UNFUSED = os.environ.get("B2TTS_FINAL_NORM_UNFUSED", "0") != "0"      # experiments: the stack's final norm as its own launch
 FUSED_NORM_MAX_ROWS = int(os.environ.get("B2TTS_FUSED_NORM_MAX_ROWS", "192"))
 # decode of a small stack (the code predictor) as ONE persistent dataflow launch (csrc/decoder_stack.cu).  Opt-in:
 # bit-identical to the separate launches, but measured at 260 us per 5-layer pass against their 246 us at 64 rows
@@ -288,6 +289,26 @@ class DecoderStack(nn.Module):
             intermediate=c.intermediate_size, eps=c.rms_norm_eps, scale=self.layers[0].self_attn.scaling, workspace=ws,
             attention_scaling=rope.attention_scaling, rounding=self.rounding, layer_array=arr)
 
+    def _run_layers_native(self, input_embeds, positions, input_ssq, tail_weight):
+        residual, ssq = input_embeds, input_ssq
+        nl = len(self.layers)
+        for i, layer in enumerate(self.layers):
+            nxt = self.layers[i + 1].self_attn.qkv_proj.weight if i + 1 < nl else tail_weight
+            residual, ssq = layer.forward_decode(positions, residual, ssq, in_place=i > 0, nxt=nxt)
+        return residual, ssq
+
+    def run_layers_unnormed(self, input_embeds: torch.Tensor, positions: torch.Tensor,
+                            input_ssq: torch.Tensor | None = None, tail_weight=None):
+        """The layers WITHOUT the final norm: (residual stream, the final norm as a ``RowNorm`` for the GEMM that consumes
+        it), or None when this batch does not take the fused-epilogue path (the caller then uses ``run_layers``)."""
+        ctx = get_context()
+        m = input_embeds.shape[0]
+        if (DATAFLOW_STACK or GEMM_CHAIN or FINAL_NORM_UNFUSED or input_embeds.dim() != 2 or not 1 <= m <= FUSED_NORM_MAX_ROWS
+                or m > GEMM_NATIVE_MAX_M or not self._native_gemm_shapes()):
+            return None
+        residual, ssq = self._run_layers_native(input_embeds, positions, input_ssq, tail_weight)
+        return residual, RowNorm(self.norm.weight, ssq, self.config.rms_norm_eps, self.rounding)
+
     def run_layers(self, input_embeds: torch.Tensor, positions: torch.Tensor,
                    input_ssq: torch.Tensor | None = None, tail_weight=None) -> torch.Tensor:
         """``tail_weight``: the weight streamed right after the stack (the LM head), prefetched by the last layer."""
@@ -300,11 +321,7 @@ class DecoderStack(nn.Module):
             return self.run_layers_chained(input_embeds, positions, input_ssq)
         if 1 <= input_embeds.shape[0] <= GEMM_NATIVE_MAX_M and self._native_gemm_shapes():
             # decode and short prefills (<= GEMM_NATIVE_MAX_M rows): 5 launches per layer, norms / residual adds / SiLU*mul inside the GEMMs
-            residual, ssq = input_embeds, input_ssq
-            nl = len(self.layers)
-            for i, layer in enumerate(self.layers):
-                nxt = self.layers[i + 1].self_attn.qkv_proj.weight if i + 1 < nl else tail_weight
-                residual, ssq = layer.forward_decode(positions, residual, ssq, in_place=i > 0, nxt=nxt)
+            residual, _ = self._run_layers_native(input_embeds, positions, input_ssq, tail_weight)
             return nat.rmsnorm(residual, self.norm.weight, self.config.rms_norm_eps, self.rounding)
         hidden_states, residual = input_embeds, None
         for layer in self.layers:
