@@ -42,7 +42,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     for src in sources():
         obj = os.path.join(LIB_DIR, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
-        cmd = [nvcc, *NVCC_FLAGS, "-I", INCLUDE, "-c", src, "-o", obj]
+        # B2TTS_NVCC_EXTRA: extra flags for experiments (e.g. -DB2TTS_GEMM_XWARPS=4)
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("B2TTS_NVCC_EXTRA", "").split(), "-I", INCLUDE, "-c", src, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

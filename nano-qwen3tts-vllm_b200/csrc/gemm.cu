@@ -27,6 +27,7 @@
 //   * programmatic dependent launch: the W stream starts before the previous kernel has finished
 //     (weights do not depend on it); only the x producers / epilogue execute griddepcontrol.wait.
 #include <cuda.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "umma.cuh"
@@ -717,6 +718,53 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
     if (chunk_cfg < 16 || chunk_cfg > G_MAX_M || chunk_cfg % 16) chunk_cfg = G_MAX_M;
   }
   p.chunk_rows = (splits >= 0 && m > chunk_cfg) ? chunk_cfg : G_MAX_M;      // an explicit batch split takes the whole batch
+  // Plain x (no fused norm: above 192 rows the norms are separate launches) cut into chunks: a k-block costs ~0.2 us
+  // there (0.45 with the in-place norm transform), so (measured at 256 streams, tools/plan_sweep.py)
+  //   * K <= 1024 is not split at all: 16 k-blocks per CTA cost less than drain + DSMEM exchange of 64-row partials
+  //     (predictor qkv: -0.16 ms per frame);
+  //   * an unsplit launch takes the chunk size that fills ONE wave of 2 CTAs per SM best (predictor gate_up: 48 tiles x
+  //     6 chunks of 48 rows = 288 CTAs, -0.19 ms; talker gate_up: 96 tiles x 3 chunks of 96 rows = 288 CTAs instead of
+  //     384 in two waves, -0.23 ms); when nothing fits in one wave, the largest chunk (fewest waves, fewest L2 re-reads).
+  const bool auto_plan = splits == 0;
+  static const bool plain_rule = [] { const char* e = getenv("B2TTS_GEMM_PLAIN_RULE"); return !(e && e[0] == '0'); }();
+  if (plain_rule && splits == 0 && !norm_weight && !getenv("B2TTS_GEMM_CHUNK_ROWS") && m > G_MAX_M) {
+    const int tiles = n / G_BN, kb = k / G_BK;
+    const int units64 = tiles * ((m + 63) / 64);
+    if (kb <= 16 || choose_splits(units64, kb, 64) == 1) {
+      int best_chunk = G_MAX_M, best_ctas = 0;
+      for (int ch : {128, 96, 64, 48}) {
+        const int ctas = tiles * ((m + ch - 1) / ch);
+        if (ctas <= 2 * sm_count() && ctas > best_ctas) { best_ctas = ctas; best_chunk = ch; }
+      }
+      p.chunk_rows = best_chunk;
+      splits = 1;
+    }
+  }
+  // experiments: B2TTS_GEMM_PLAN="n,k,m_lo,m_hi,chunk,splits;..." overrides the cut and the K split of matching launches
+  {
+    struct PlanEntry { int n, k, mlo, mhi, chunk, splits; };
+    static PlanEntry plan[32];
+    static int nplan = -1;
+    if (nplan < 0) {
+      nplan = 0;
+      if (const char* e = getenv("B2TTS_GEMM_PLAN")) {
+        while (*e && nplan < 32) {
+          PlanEntry pe{};
+          int used = 0;
+          if (sscanf(e, "%d,%d,%d,%d,%d,%d%n", &pe.n, &pe.k, &pe.mlo, &pe.mhi, &pe.chunk, &pe.splits, &used) == 6) plan[nplan++] = pe;
+          else break;
+          e += used;
+          if (*e == ';') ++e;
+        }
+      }
+    }
+    for (int i = 0; i < nplan; ++i)
+      if (plan[i].n == n && plan[i].k == k && m >= plan[i].mlo && m <= plan[i].mhi && auto_plan) {
+        if (plan[i].chunk >= 16 && plan[i].chunk <= G_MAX_M && plan[i].chunk % 16 == 0) p.chunk_rows = m > plan[i].chunk ? plan[i].chunk : G_MAX_M;
+        splits = plan[i].splits;
+        break;
+      }
+  }
   p.nchunks = (m + p.chunk_rows - 1) / p.chunk_rows;
   B2_REQUIRE((int64_t)(n / G_BN) * p.nchunks <= 65535, B2TTS_EUNSUPPORTED, "%s: m=%d n=%d: too many tiles", what, m, n);
   p.mpad = p.nchunks > 1 ? p.chunk_rows : (m + 15) & ~15;
