@@ -495,7 +495,9 @@ def main():
         mean_ctx = float(ctx_now.float().mean())
         gemm_ms, gemm_alg, gemm_n = BK.gemm_stack(talker.model_runner, a.streams)
         pg_ms, pg_alg, pg_n = BK.gemm_stack(predictor.model_runner, a.streams)
-        pg2_ms, pg2_alg, _ = BK.gemm_stack(predictor.model_runner, 2 * a.streams)
+        from nano_qwen3tts_vllm_b200.layers.linear import GEMM_NATIVE_MAX_M
+        m2 = min(2 * a.streams, GEMM_NATIVE_MAX_M)                # longer prefills take cuBLAS (layers/linear.py)
+        pg2_ms, pg2_alg, _ = BK.gemm_stack(predictor.model_runner, m2)
         att_ms, att_alg = BK.decode_attention(a.streams, ctx_now, device, layers=8)
         a512_ms, a512_alg = BK.decode_attention(64, 512, device, layers=6)
         a4k_ms, a4k_alg = BK.decode_attention(64, 4096, device, layers=3)
@@ -527,7 +529,7 @@ def main():
                 f"graph of the predictor's {pg_n} projection launches at M={a.streams} (5 layers x 4; 31 MB of weights per "
                 "layer: latency-bound launches)"),
             hbm("gemm_stream_kernel, code-predictor shapes, 2-token prefill pass", pg2_ms, pg2_alg,
-                f"same at M={2 * a.streams} rows"),
+                f"same at M={m2} rows"),
             hbm("fused_decode_attn_kernel (qk-norm + M-RoPE + KV write + paged GQA attention + combine), bench contexts",
                 att_ms, att_alg, "graph of 8 launches over different caches at the run's end-of-run context lengths; "
                 "bytes = sum_b(4096*L_b + 8192)", mean_context=round(mean_ctx, 1)),
@@ -583,7 +585,7 @@ def main():
                         "GBps": round(alg_ / ms_ / 1e6, 1), "ours_launch_ms": round(st_ms, 5), "speedup": round(ms_ / st_ms, 3)}
             leg(f"gemm_talker_M{a.streams}", lambda: cublas(talker.model_runner, a.streams, gemm_ms))
             leg(f"gemm_predictor_M{a.streams}", lambda: cublas(predictor.model_runner, a.streams, pg_ms))
-            leg(f"gemm_predictor_M{2 * a.streams}", lambda: cublas(predictor.model_runner, 2 * a.streams, pg2_ms))
+            leg(f"gemm_predictor_M{m2}", lambda: cublas(predictor.model_runner, m2, pg2_ms))
             leg("decode_attention_bench_contexts", lambda: flash_dec(a.streams, ctx_now, 8, att_ms))
             leg("decode_attention_64x512", lambda: flash_dec(64, 512, 6, a512_ms))
             leg("decode_attention_64x4096", lambda: flash_dec(64, 4096, 3, a4k_ms))

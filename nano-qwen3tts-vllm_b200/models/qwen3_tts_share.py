@@ -160,8 +160,10 @@ class Qwen3TTSDecoderLayer(nn.Module):
         else:
             o = self.self_attn.attend(positions, residual,
                                       RowNorm(self.input_layernorm.weight, ssq, self.eps, self.rounding))
-        residual, ssq = linear_residual(o, self.self_attn.o_proj.weight, residual, out=residual if in_place else None,
-                                        want_ssq=True, nxt=(self.mlp.gate_up_proj.weight, nat.PACK_GATE_UP))
+        # wide batches: the norms are separate launches, so nobody reads the row sums of squares - the GEMMs skip that epilogue
+        residual = linear_residual(o, self.self_attn.o_proj.weight, residual, out=residual if in_place else None,
+                                   want_ssq=not wide, nxt=(self.mlp.gate_up_proj.weight, nat.PACK_GATE_UP))
+        residual, ssq = (residual, None) if wide else residual
         if wide or "gate_up" in UNFUSED_NORMS:
             h = nat.rmsnorm(residual, self.post_attention_layernorm.weight, self.eps, self.rounding)
             act = linear_silu_mul(h, self.mlp.gate_up_proj.weight, self.rounding, nxt=self.mlp.down_proj.weight)
@@ -169,6 +171,8 @@ class Qwen3TTSDecoderLayer(nn.Module):
             act = linear_silu_mul(residual, self.mlp.gate_up_proj.weight, self.rounding,
                                   norm=RowNorm(self.post_attention_layernorm.weight, ssq, self.eps, self.rounding),
                                   nxt=self.mlp.down_proj.weight)
+        if wide:
+            return linear_residual(act, self.mlp.down_proj.weight, residual, out=residual, nxt=nxt), None
         return linear_residual(act, self.mlp.down_proj.weight, residual, out=residual, want_ssq=True, nxt=nxt)
 
 
