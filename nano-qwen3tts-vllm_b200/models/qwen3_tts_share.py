@@ -38,10 +38,10 @@ GEMM_CHAIN = False                # decode: the 4 projections between two attent
 # experiments: RMSNorms applied by a separate launch instead of inside the consuming GEMM ("gate_up", "qkv", "gate_up,qkv")
 UNFUSED_NORMS = os.environ.get("B2TTS_UNFUSED_NORMS", "")
 # rows up to which the RMSNorms ride inside the consuming GEMM; above, the per-k-block hand-over of the in-place transform
-# costs more than a separate launch (measured per frame: 128 streams 6.36 fused / 6.69 separate, 256: 8.68 / 8.20,
-# 512: 12.4 / 10.95)
+# costs more than a separate launch (measured per frame: 96 streams 6.23 fused / 6.46 separate, 128: 6.16 / 6.56,
+# 160: 6.94 / 6.70, 192: 7.13 / 6.88, 256: 8.68 / 8.20, 512: 12.4 / 10.95)
 FINAL_NORM_UNFUSED = os.environ.get("B2TTS_FINAL_NORM_UNFUSED", "0") != "0"      # experiments: the stack's final norm as its own launch
-FUSED_NORM_MAX_ROWS = int(os.environ.get("B2TTS_FUSED_NORM_MAX_ROWS", "192"))
+FUSED_NORM_MAX_ROWS = int(os.environ.get("B2TTS_FUSED_NORM_MAX_ROWS", "128"))
 # decode of a small stack (the code predictor) as ONE persistent dataflow launch (csrc/decoder_stack.cu).  Opt-in:
 # bit-identical to the separate launches, but measured at 260 us per 5-layer pass against their 246 us at 64 rows
 # (every hand-over between phases costs a gpu-scope release + an L2 poll, ~2.5 us, 7 per layer)
