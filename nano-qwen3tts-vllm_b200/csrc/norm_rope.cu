@@ -10,6 +10,8 @@
 //                      to one rounding at the store, rstd = rsqrtf.
 // RoPE is never compiled in the reference, so it always keeps the three bf16 roundings of
 // `(x*cos) + (rotate_half(x)*sin)` (rotary_embedding.py:33-34) and bf16 cos/sin (:138-139).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b2 {
@@ -45,6 +47,10 @@ rmsnorm_kernel(const __nv_bfloat16* __restrict__ x, int64_t x_stride, const __nv
                const __nv_bfloat16* __restrict__ w, __nv_bfloat16* y, __nv_bfloat16* res_out, int cols, float eps,
                int round_sum_first) {
   __shared__ float red[32];
+  // programmatic dependent launch: between two GEMMs of a wide batch this kernel must neither drain the chain (the next
+  // GEMM's CTAs become resident and stream their first weight tiles while it runs) nor start late itself
+  pdl_launch();
+  pdl_wait();
   const int row = blockIdx.x;
   const int nvec = cols >> 3;
   const __nv_bfloat16* xr = x + (int64_t)row * x_stride;
@@ -247,10 +253,24 @@ extern "C" int b2tts_rmsnorm(const void* x, int64_t x_row_stride, const void* w,
     if (rounding == B2TTS_ROUND_EAGER) rmsnorm_narrow_kernel<true><<<grid, 256, 0, st>>>(xp, x_row_stride, wp, yp, rows, cols, eps);
     else rmsnorm_narrow_kernel<false><<<grid, 256, 0, st>>>(xp, x_row_stride, wp, yp, rows, cols, eps);
   } else {
-    if (rounding == B2TTS_ROUND_EAGER)
-      rmsnorm_kernel<false, true><<<rows, RMS_THREADS, 0, st>>>(xp, x_row_stride, nullptr, wp, yp, nullptr, cols, eps, 0);
-    else
-      rmsnorm_kernel<false, false><<<rows, RMS_THREADS, 0, st>>>(xp, x_row_stride, nullptr, wp, yp, nullptr, cols, eps, 0);
+    // launched as a programmatic dependent (B2TTS_PDL_NORM=0: a plain launch); correct after any kernel - one that never
+    // executes griddepcontrol.launch_dependents releases its dependents when it completes
+    static const bool pdl = [] { const char* e = getenv("B2TTS_PDL_NORM"); return !(e && e[0] == '0'); }();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(rows, 1, 1);
+    cfg.blockDim = dim3(RMS_THREADS, 1, 1);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    const __nv_bfloat16* nores = nullptr;
+    __nv_bfloat16* noout = nullptr;
+    cudaError_t e = rounding == B2TTS_ROUND_EAGER
+        ? cudaLaunchKernelEx(&cfg, rmsnorm_kernel<false, true>, xp, x_row_stride, nores, wp, yp, noout, cols, eps, 0)
+        : cudaLaunchKernelEx(&cfg, rmsnorm_kernel<false, false>, xp, x_row_stride, nores, wp, yp, noout, cols, eps, 0);
+    if (e != cudaSuccess) return cuda_fail(e, "rmsnorm");
   }
   B2_CHECK_LAUNCH("rmsnorm");
   return B2TTS_OK;
