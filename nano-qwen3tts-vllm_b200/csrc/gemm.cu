@@ -718,7 +718,7 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
     if (chunk_cfg < 16 || chunk_cfg > G_MAX_M || chunk_cfg % 16) chunk_cfg = G_MAX_M;
   }
   p.chunk_rows = (splits >= 0 && m > chunk_cfg) ? chunk_cfg : G_MAX_M;      // an explicit batch split takes the whole batch
-  // Plain x (no fused norm: above 192 rows the norms are separate launches) cut into chunks: a k-block costs ~0.2 us
+  // Plain x (no fused norm: above 128 rows the norms are separate launches) cut into chunks: a k-block costs ~0.2 us
   // there (0.45 with the in-place norm transform), so (measured at 256 streams, tools/plan_sweep.py)
   //   * K <= 1024 is not split at all: 16 k-blocks per CTA cost less than drain + DSMEM exchange of 64-row partials
   //     (predictor qkv: -0.16 ms per frame);
