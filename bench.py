@@ -591,6 +591,21 @@ def main():
             leg("decode_attention_64x4096", lambda: flash_dec(64, 4096, 3, a4k_ms))
             leg("prefill_attention_4096", flash_pre)
             leg("kv_store_4096", triton_store)
+
+            def frame_library():
+                # the layer-level answer to "the library GEMM is faster per launch": the same frame loop in a child process
+                # with every projection on F.linear (cuBLAS) and the norms / residual adds / SiLU*mul as separate launches
+                # of this repo's kernels (B2TTS_GEMM_NATIVE_MAX_M=0, tools/library_path_frame.py)
+                out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "library_path_frame.py"), "--child",
+                                      str(a.streams), "64"], env={**os.environ, "B2TTS_GEMM_NATIVE_MAX_M": "0"},
+                                     capture_output=True, text=True, timeout=600)
+                d = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+                return {"library": "cuBLAS via F.linear for every projection + separate RMSNorm / add / SiLU*mul launches "
+                                   "(measured only: not a product path)",
+                        "ms_per_step": round(d["ms_per_frame"], 4), "ours_ms_per_step": round(ms_per_step, 4),
+                        "speedup": round(d["ms_per_frame"] / ms_per_step, 3)}
+            if world == 1:
+                leg(f"frame_{a.streams}_streams_library_gemm", frame_library)
         step_roof = {"bound": "hbm", "achieved": round(step_bytes / (ms_per_step / 1e3) / 1e9, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(step_bytes / (ms_per_step / 1e3) / 1e9 / peak, 4), "algorithmic_bytes_per_step": step_bytes,
                      "note": "whole frame: weights streamed once per pass (talker + 15 predictor passes) + talker KV"}
