@@ -61,8 +61,9 @@ def gemm_stack(runner, m: int, impl: str = "ours"):
     act0 = (torch.randn(m, c.intermediate_size, device=dev) * 0.5).to(BF16)
     eps, rnd = c.rms_norm_eps, nat.ROUND_EAGER
 
-    from nano_qwen3tts_vllm_b200.models.qwen3_tts_share import FUSED_NORM_MAX_ROWS
-    wide = m > FUSED_NORM_MAX_ROWS        # the product then runs the norms as separate launches (not counted here) and plain GEMMs
+    from nano_qwen3tts_vllm_b200.models.qwen3_tts_share import FUSED_NORM_MAX_ROWS, FUSED_NORM_MIN_ROWS
+    # outside this range the product runs the norms as separate launches (not counted here) and plain GEMMs
+    wide = not FUSED_NORM_MIN_ROWS <= m <= FUSED_NORM_MAX_ROWS
 
     def ours_wide():
         x = resid.clone()

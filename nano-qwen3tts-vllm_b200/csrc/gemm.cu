@@ -718,10 +718,10 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
     if (chunk_cfg < 16 || chunk_cfg > G_MAX_M || chunk_cfg % 16) chunk_cfg = G_MAX_M;
   }
   p.chunk_rows = (splits >= 0 && m > chunk_cfg) ? chunk_cfg : G_MAX_M;      // an explicit batch split takes the whole batch
-  // Plain x (no fused norm: above 128 rows the norms are separate launches) cut into chunks: a k-block costs ~0.2 us
+  // Plain x (no fused norm: above 64 rows the norms are separate launches) cut into chunks: a k-block costs ~0.2 us
   // there (0.45 with the in-place norm transform), so (measured at 256 streams, tools/plan_sweep.py)
   //   * K <= 1024 is not split at all: 16 k-blocks per CTA cost less than drain + DSMEM exchange of 64-row partials
-  //     (predictor qkv: -0.16 ms per frame);
+  //     (predictor qkv: -0.16 ms per frame at 256 streams; 128 streams with separate norms 5.94 -> 5.70 ms);
   //   * an unsplit launch takes the chunk size that fills ONE wave of 2 CTAs per SM best (predictor gate_up: 48 tiles x
   //     6 chunks of 48 rows = 288 CTAs, -0.19 ms; talker gate_up: 96 tiles x 3 chunks of 96 rows = 288 CTAs instead of
   //     384 in two waves, -0.23 ms); when nothing fits in one wave, the largest chunk (fewest waves, fewest L2 re-reads).
@@ -731,7 +731,7 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
     // (the fill rule also holds with the fused norm: talker gate_up at 128 streams, 3 chunks of 48 rows, -0.12 ms)
     const int tiles = n / G_BN, kb = k / G_BK;
     const int units64 = tiles * ((m + 63) / 64);
-    if ((!norm_weight && m > G_MAX_M && kb <= 16) || choose_splits(units64, kb, 64) == 1) {
+    if ((!norm_weight && kb <= 16) || choose_splits(units64, kb, 64) == 1) {
       int best_chunk = G_MAX_M, best_ctas = 0;
       for (int ch : {128, 96, 64, 48}) {
         const int ctas = tiles * ((m + ch - 1) / ch);

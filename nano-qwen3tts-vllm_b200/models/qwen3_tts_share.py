@@ -38,10 +38,14 @@ GEMM_CHAIN = False                # decode: the 4 projections between two attent
 # experiments: RMSNorms applied by a separate launch instead of inside the consuming GEMM ("gate_up", "qkv", "gate_up,qkv")
 UNFUSED_NORMS = os.environ.get("B2TTS_UNFUSED_NORMS", "")
 # rows up to which the RMSNorms ride inside the consuming GEMM; above, the per-k-block hand-over of the in-place transform
-# costs more than a separate launch (measured per frame: 96 streams 6.23 fused / 6.46 separate, 128: 6.16 / 6.56,
-# 160: 6.94 / 6.70, 192: 7.13 / 6.88, 256: 8.68 / 8.20, 512: 12.4 / 10.95)
+# costs more than a separate launch.  Measured per frame with rmsnorm_kernel launched as a programmatic dependent (before
+# that a separate norm drained the PDL chain and the fused path won up to 128 rows): 32 streams 4.33 fused / 4.64
+# separate, 64: 5.15 / 5.51, 96: 6.17 / 5.79, 128: 6.12 / 5.70, 256: 8.68 / 8.20, 512: 12.4 / 10.95
 FINAL_NORM_UNFUSED = os.environ.get("B2TTS_FINAL_NORM_UNFUSED", "0") != "0"      # experiments: the stack's final norm as its own launch
-FUSED_NORM_MAX_ROWS = int(os.environ.get("B2TTS_FUSED_NORM_MAX_ROWS", "128"))
+FUSED_NORM_MAX_ROWS = int(os.environ.get("B2TTS_FUSED_NORM_MAX_ROWS", "64"))
+# ... and from which: below, the fixed cost of the fused path (rstd prologue + per-k-block hand-over) is not paid back
+# (1 stream 3.83 fused / 3.75 separate, 4: 3.95 / 3.86, 8: 3.99 / 3.88, 12: 4.05 / 4.06, 16: 4.03 / 4.17)
+FUSED_NORM_MIN_ROWS = int(os.environ.get("B2TTS_FUSED_NORM_MIN_ROWS", "9"))
 # decode of a small stack (the code predictor) as ONE persistent dataflow launch (csrc/decoder_stack.cu).  Opt-in:
 # bit-identical to the separate launches, but measured at 260 us per 5-layer pass against their 246 us at 64 rows
 # (every hand-over between phases costs a gpu-scope release + an L2 poll, ~2.5 us, 7 per layer)
@@ -153,7 +157,7 @@ class Qwen3TTSDecoderLayer(nn.Module):
         ``in_place`` False keeps the caller's tensor (the first layer's input embeddings) intact.
         ``nxt``: the weight the GEMM after this layer streams (the next layer's qkv_proj, or the LM head): every GEMM
         here pulls its successor's weights into L2 while it runs.  Returns (residual, ssq)."""
-        wide = residual.shape[0] > FUSED_NORM_MAX_ROWS
+        wide = not FUSED_NORM_MIN_ROWS <= residual.shape[0] <= FUSED_NORM_MAX_ROWS
         if ssq is None or wide or "qkv" in UNFUSED_NORMS:
             h = nat.rmsnorm(residual, self.input_layernorm.weight, self.eps, self.rounding)
             o = self.self_attn.attend(positions, h)
@@ -307,7 +311,7 @@ class DecoderStack(nn.Module):
         it), or None when this batch does not take the fused-epilogue path (the caller then uses ``run_layers``)."""
         ctx = get_context()
         m = input_embeds.shape[0]
-        if (DATAFLOW_STACK or GEMM_CHAIN or FINAL_NORM_UNFUSED or input_embeds.dim() != 2 or not 1 <= m <= FUSED_NORM_MAX_ROWS
+        if (DATAFLOW_STACK or GEMM_CHAIN or FINAL_NORM_UNFUSED or input_embeds.dim() != 2 or not max(1, FUSED_NORM_MIN_ROWS) <= m <= FUSED_NORM_MAX_ROWS
                 or m > GEMM_NATIVE_MAX_M or not self._native_gemm_shapes()):
             return None
         residual, ssq = self._run_layers_native(input_embeds, positions, input_ssq, tail_weight)
