@@ -727,7 +727,8 @@ static int gemm_impl(const char* what, const void* x, int64_t x_row_stride, cons
   //     384 in two waves, -0.23 ms); when nothing fits in one wave, the largest chunk (fewest waves, fewest L2 re-reads).
   const bool auto_plan = splits == 0;
   static const bool plain_rule = [] { const char* e = getenv("B2TTS_GEMM_PLAIN_RULE"); return !(e && e[0] == '0'); }();
-  if (plain_rule && splits == 0 && !getenv("B2TTS_GEMM_CHUNK_ROWS") && m > chunk_cfg) {
+  static const bool chunk_forced = getenv("B2TTS_GEMM_CHUNK_ROWS") != nullptr;
+  if (plain_rule && splits == 0 && !chunk_forced && m > chunk_cfg) {
     // (the fill rule also holds with the fused norm: talker gate_up at 128 streams, 3 chunks of 48 rows, -0.12 ms)
     const int tiles = n / G_BN, kb = k / G_BK;
     const int units64 = tiles * ((m + 63) / 64);
